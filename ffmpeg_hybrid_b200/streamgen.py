@@ -1,0 +1,411 @@
+"""Synthetic VP9 bitstream generator (IVF container) for the five BASELINE.json configs.
+
+What it writes, and why it is legal for the decoder on the other side:
+
+* the uncompressed header is written field by field in the order the reference reads it
+  (libavcodec/vp9.c:527-907, grammar in cbs_vp9_syntax_template.c:268-439);
+* the compressed header is produced by a real boolean *encoder* (the inverse of
+  libavcodec/vpx_rac.h:84-107): marker, tx_mode, "no probability update" flags and the
+  compound-prediction mode, in the read order of vp9.c:908-1110;
+* every tile payload is a seeded uniform byte string whose first decoded bool (the tile
+  marker, vp9.c:1345) is forced to 0.  An arithmetic decoder maps uniform bytes to symbols
+  distributed exactly according to its probability model, so the payload is a *sample from
+  the VP9 default/adapted model*: every partition, block size, tx size, intra mode, inter
+  mode, reference, interpolation filter, motion vector and coefficient token the model gives
+  non-zero probability appears, with natural-ish statistics.  The decoder never desyncs
+  because there is no second party: whatever it decodes *is* the stream.  Tiles are first
+  over-provisioned, then trimmed to the bytes the reference decoder actually consumed
+  (see tools in tests/golden/make_golden.py).
+
+Nothing here touches the reference tree; only numpy is needed.
+"""
+from __future__ import annotations
+
+import struct
+from dataclasses import dataclass, field
+from typing import List, Optional, Sequence
+
+import numpy as np
+
+VP9_SYNCCODE = 0x498342
+TX_4X4, TX_8X8, TX_16X16, TX_32X32, TX_SWITCHABLE = range(5)
+FILTER_SMOOTH, FILTER_REGULAR, FILTER_SHARP, FILTER_BILINEAR, FILTER_SWITCHABLE = range(5)
+# raw 2-bit header code -> FilterMode is remapped by the decoder (vp9.c:631, vp9shared.h);
+# the header literal order is: 0 EIGHTTAP_SMOOTH, 1 EIGHTTAP, 2 EIGHTTAP_SHARP, 3 BILINEAR
+PRED_SINGLEREF, PRED_COMPREF, PRED_SWITCHABLE = range(3)
+
+
+class BitWriter:
+    """MSB-first literal writer for the uncompressed header (get_bits order)."""
+
+    def __init__(self) -> None:
+        self.bits: List[int] = []
+
+    def u(self, n: int, v: int) -> None:
+        assert 0 <= v < (1 << n), (n, v)
+        for i in range(n - 1, -1, -1):
+            self.bits.append((v >> i) & 1)
+
+    def s_inv(self, n: int, v: int) -> None:
+        """magnitude then sign, as read by get_sbits_inv (vp9.c:379-383)."""
+        self.u(n, abs(v))
+        self.u(1, 1 if v < 0 else 0)
+
+    def bytes(self) -> bytes:
+        b = self.bits + [0] * (-len(self.bits) % 8)
+        out = bytearray()
+        for i in range(0, len(b), 8):
+            v = 0
+            for k in range(8):
+                v = (v << 1) | b[i + k]
+            out.append(v)
+        return bytes(out)
+
+    def patch_u16(self, bitpos: int, v: int) -> None:
+        for i in range(16):
+            self.bits[bitpos + i] = (v >> (15 - i)) & 1
+
+
+class BoolEncoder:
+    """Boolean arithmetic encoder matching the decoder in vpx_rac.h:84-107."""
+
+    def __init__(self) -> None:
+        self.low = 0
+        self.rng = 255
+        self.count = -24
+        self.buf = bytearray()
+
+    def put(self, bit: int, prob: int) -> None:
+        split = 1 + (((self.rng - 1) * prob) >> 8)
+        if bit:
+            self.low += split
+            self.rng -= split
+        else:
+            self.rng = split
+        shift = 0
+        while (self.rng << shift) < 128:
+            shift += 1
+        self.rng <<= shift
+        self.count += shift
+        if self.count >= 0:
+            offset = shift - self.count
+            if (self.low << (offset - 1)) & 0x80000000:
+                x = len(self.buf) - 1
+                while x >= 0 and self.buf[x] == 0xFF:
+                    self.buf[x] = 0
+                    x -= 1
+                self.buf[x] += 1
+            self.buf.append((self.low >> (24 - offset)) & 0xFF)
+            self.low = (self.low << offset) & 0xFFFFFF
+            shift = self.count
+            self.count -= 8
+        self.low = (self.low << shift) & 0xFFFFFFFF
+
+    def put_eq(self, bit: int) -> None:
+        self.put(bit, 128)
+
+    def put_uint(self, n: int, v: int) -> None:
+        for i in range(n - 1, -1, -1):
+            self.put_eq((v >> i) & 1)
+
+    def finish(self) -> bytes:
+        for _ in range(32):
+            self.put_eq(0)
+        return bytes(self.buf)
+
+
+@dataclass
+class FrameSpec:
+    """One coded frame. Field names follow VP9BitstreamHeader (vp9shared.h:103-166)."""
+    keyframe: bool = False
+    intraonly: bool = False
+    show: bool = True
+    errorres: bool = False
+    width: int = 0            # 0 = inherit stream size
+    height: int = 0
+    refreshrefmask: int = 0x01
+    refidx: Sequence[int] = (0, 0, 0)
+    signbias: Sequence[int] = (0, 0, 0)
+    size_from_ref: int = -1   # 0..2 = copy size from that ref, -1 = explicit size
+    highprecisionmvs: bool = True
+    filtermode: int = FILTER_SWITCHABLE   # header literal 0..3, or FILTER_SWITCHABLE
+    refreshctx: bool = True
+    parallelmode: bool = False
+    framectxid: int = 0
+    resetctx: int = 0
+    lf_level: int = 16
+    lf_sharpness: int = 0
+    lf_delta_enabled: bool = True
+    lf_ref_deltas: Optional[Sequence[int]] = None   # 4 values -> sent as updates
+    lf_mode_deltas: Optional[Sequence[int]] = None  # 2 values
+    yac_qi: int = 60
+    ydc_qdelta: int = 0
+    uvdc_qdelta: int = 0
+    uvac_qdelta: int = 0
+    log2_tile_cols: int = 0
+    log2_tile_rows: int = 0
+    txfmmode: int = TX_SWITCHABLE
+    comppredmode: int = PRED_SWITCHABLE   # used only when sign biases differ
+    bytes_per_sb: int = 1536              # over-provisioned payload per 64x64 superblock
+    tile_bytes: Optional[List[int]] = None  # exact per-tile sizes (after trimming)
+
+
+@dataclass
+class StreamSpec:
+    width: int
+    height: int
+    profile: int = 0          # 0: 8-bit 4:2:0, 2: 10/12-bit 4:2:0
+    bitdepth: int = 8
+    seed: int = 1
+    frames: List[FrameSpec] = field(default_factory=list)
+
+
+def _tile_bounds(idx: int, log2_n: int, n_sb: int) -> tuple:
+    """set_tile_offset (vp9.c:1244-1250), in superblocks."""
+    a = min((idx * n_sb) >> log2_n, n_sb)
+    b = min(((idx + 1) * n_sb) >> log2_n, n_sb)
+    return a, b
+
+
+def tile_col_limits(sb_cols: int) -> tuple:
+    """(min_log2, max_log2) for tile columns, vp9.c:800-804."""
+    mn = 0
+    while sb_cols > (64 << mn):
+        mn += 1
+    mx = 0
+    while (sb_cols >> mx) >= 4:
+        mx += 1
+    mx = max(0, mx - 1)
+    return mn, mx
+
+
+def _color_config(bw: BitWriter, st: StreamSpec) -> None:
+    # read_colorspace_details (vp9.c:457-517)
+    if st.profile >= 2:
+        bw.u(1, 0 if st.bitdepth == 10 else 1)
+    bw.u(3, 2)   # BT.709
+    bw.u(1, 0)   # studio range
+    assert st.profile in (0, 2), "4:2:0 profiles only"
+
+
+def _compressed_header(fs: FrameSpec, inter: bool, allowcomp: bool, lossless: bool) -> bytes:
+    be = BoolEncoder()
+    be.put(0, 128)                       # marker, vp9.c:912
+    txm = TX_4X4 if lossless else fs.txfmmode
+    if not lossless:                     # vp9.c:936-954
+        be.put_uint(2, min(txm, 3))
+        if txm >= 3:
+            be.put_eq(txm - 3)
+        if txm == TX_SWITCHABLE:
+            for _ in range(2 + 4 + 6):
+                be.put(0, 252)
+    for i in range(4):                   # coef updates, vp9.c:958-992
+        be.put_eq(0)
+        if txm == i:
+            break
+    for _ in range(3):                   # skip
+        be.put(0, 252)
+    if inter:
+        n = 21                           # mv_mode
+        if fs.filtermode == FILTER_SWITCHABLE:
+            n += 8
+        n += 4                           # intra
+        for _ in range(n):
+            be.put(0, 252)
+        cpm = PRED_SINGLEREF
+        if allowcomp:                    # vp9.c:1016-1027
+            cpm = fs.comppredmode
+            be.put_eq(1 if cpm else 0)
+            if cpm:
+                be.put_eq(cpm - 1)
+            if cpm == PRED_SWITCHABLE:
+                for _ in range(5):
+                    be.put(0, 252)
+        n = 0
+        if cpm != PRED_COMPREF:
+            n += 10
+        if cpm != PRED_SINGLEREF:
+            n += 5
+        n += 36 + 48 + 3 + 2 * 22 + 2 * 9
+        if fs.highprecisionmvs:
+            n += 4
+        for _ in range(n):
+            be.put(0, 252)
+    return be.finish()
+
+
+def encode_frame(st: StreamSpec, fs: FrameSpec, cur_w: int, cur_h: int,
+                 rng: np.random.Generator) -> bytes:
+    """Returns one frame's bytes. cur_w/cur_h is the resolved coded size."""
+    bw = BitWriter()
+    bw.u(2, 2)
+    bw.u(1, st.profile & 1)
+    bw.u(1, st.profile >> 1)
+    bw.u(1, 0)                            # show_existing_frame
+    bw.u(1, 0 if fs.keyframe else 1)
+    bw.u(1, 1 if fs.show else 0)
+    bw.u(1, 1 if fs.errorres else 0)
+    inter = False
+    allowcomp = False
+    if fs.keyframe:
+        bw.u(24, VP9_SYNCCODE)
+        _color_config(bw, st)
+        bw.u(16, cur_w - 1)
+        bw.u(16, cur_h - 1)
+        bw.u(1, 0)
+    else:
+        if not fs.show:
+            bw.u(1, 1 if fs.intraonly else 0)
+        else:
+            assert not fs.intraonly, "intra-only frames must be hidden (vp9.c:571)"
+        if not fs.errorres:
+            bw.u(2, fs.resetctx)
+        if fs.intraonly:
+            bw.u(24, VP9_SYNCCODE)
+            if st.profile >= 1:
+                _color_config(bw, st)
+            bw.u(8, fs.refreshrefmask)
+            bw.u(16, cur_w - 1)
+            bw.u(16, cur_h - 1)
+            bw.u(1, 0)
+        else:
+            inter = True
+            bw.u(8, fs.refreshrefmask)
+            for i in range(3):
+                bw.u(3, fs.refidx[i])
+                bw.u(1, fs.signbias[i])
+            if fs.size_from_ref >= 0:
+                for i in range(fs.size_from_ref):
+                    bw.u(1, 0)
+                bw.u(1, 1)
+            else:
+                bw.u(3, 0)
+                bw.u(16, cur_w - 1)
+                bw.u(16, cur_h - 1)
+            bw.u(1, 0)                    # display size
+            bw.u(1, 1 if fs.highprecisionmvs else 0)
+            if fs.filtermode == FILTER_SWITCHABLE:
+                bw.u(1, 1)
+            else:
+                bw.u(1, 0)
+                bw.u(2, fs.filtermode)
+            sb = [0 if fs.errorres else b for b in fs.signbias]
+            allowcomp = sb[0] != sb[1] or sb[0] != sb[2]
+    if not fs.errorres:
+        bw.u(1, 1 if fs.refreshctx else 0)
+        bw.u(1, 1 if fs.parallelmode else 0)
+    bw.u(2, fs.framectxid)
+    # loop filter (vp9.c:669-697)
+    bw.u(6, fs.lf_level)
+    bw.u(3, fs.lf_sharpness)
+    bw.u(1, 1 if fs.lf_delta_enabled else 0)
+    if fs.lf_delta_enabled:
+        upd = fs.lf_ref_deltas is not None or fs.lf_mode_deltas is not None
+        bw.u(1, 1 if upd else 0)
+        if upd:
+            for i in range(4):
+                if fs.lf_ref_deltas is not None:
+                    bw.u(1, 1)
+                    bw.s_inv(6, fs.lf_ref_deltas[i])
+                else:
+                    bw.u(1, 0)
+            for i in range(2):
+                if fs.lf_mode_deltas is not None:
+                    bw.u(1, 1)
+                    bw.s_inv(6, fs.lf_mode_deltas[i])
+                else:
+                    bw.u(1, 0)
+    # quantisation (vp9.c:700-705)
+    bw.u(8, fs.yac_qi)
+    for d in (fs.ydc_qdelta, fs.uvdc_qdelta, fs.uvac_qdelta):
+        if d:
+            bw.u(1, 1)
+            bw.s_inv(4, d)
+        else:
+            bw.u(1, 0)
+    lossless = fs.yac_qi == 0 and not (fs.ydc_qdelta or fs.uvdc_qdelta or fs.uvac_qdelta)
+    bw.u(1, 0)                            # segmentation disabled
+    # tiles (vp9.c:800-812)
+    sb_cols = (cur_w + 63) >> 6
+    sb_rows = (cur_h + 63) >> 6
+    mn, mx = tile_col_limits(sb_cols)
+    l2c = min(max(fs.log2_tile_cols, mn), mx)
+    for _ in range(l2c - mn):
+        bw.u(1, 1)
+    if l2c < mx:
+        bw.u(1, 0)
+    l2r = fs.log2_tile_rows
+    if l2r == 0:
+        bw.u(1, 0)
+    else:
+        bw.u(1, 1)
+        bw.u(1, l2r - 1)
+    comp = _compressed_header(fs, inter, allowcomp, lossless)
+    bw.u(16, len(comp))
+    out = bytearray(bw.bytes())
+    out += comp
+    # tile payloads (vp9.c:1325-1349)
+    ntr, ntc = 1 << l2r, 1 << l2c
+    k = 0
+    for tr in range(ntr):
+        r0, r1 = _tile_bounds(tr, l2r, sb_rows)
+        for tc in range(ntc):
+            c0, c1 = _tile_bounds(tc, l2c, sb_cols)
+            if fs.tile_bytes is not None:
+                n = fs.tile_bytes[k]
+            else:
+                n = 16 + (r1 - r0) * (c1 - c0) * fs.bytes_per_sb
+            # always draw the over-provisioned amount so trimming keeps the same prefix
+            full = 16 + (r1 - r0) * (c1 - c0) * fs.bytes_per_sb
+            payload = rng.integers(0, 256, size=max(full, n), dtype=np.uint8)
+            payload[0] &= 0x7F           # tile marker bool must decode to 0
+            payload = payload[:n]
+            if tr == ntr - 1 and tc == ntc - 1:
+                payload[-1] = 0          # never look like a superframe index (0b110xxxxx)
+            payload = payload.tobytes()
+            if not (tr == ntr - 1 and tc == ntc - 1):
+                out += struct.pack(">I", len(payload))
+            out += payload
+            k += 1
+    return bytes(out)
+
+
+def resolve_sizes(st: StreamSpec) -> List[tuple]:
+    """Coded size of each frame, tracking the 8 reference slots like vp9.c:1687-1692."""
+    slots = [(st.width, st.height)] * 8
+    sizes = []
+    for fs in st.frames:
+        if fs.keyframe or fs.intraonly:
+            w, h = fs.width or st.width, fs.height or st.height
+        elif fs.size_from_ref >= 0:
+            w, h = slots[fs.refidx[fs.size_from_ref]]
+        else:
+            w, h = fs.width or st.width, fs.height or st.height
+        sizes.append((w, h))
+        mask = 0xFF if fs.keyframe else fs.refreshrefmask
+        for i in range(8):
+            if mask & (1 << i):
+                slots[i] = (w, h)
+    return sizes
+
+
+def tile_counts(st: StreamSpec) -> List[int]:
+    out = []
+    for fs, (w, h) in zip(st.frames, resolve_sizes(st)):
+        mn, mx = tile_col_limits((w + 63) >> 6)
+        l2c = min(max(fs.log2_tile_cols, mn), mx)
+        out.append((1 << l2c) * (1 << fs.log2_tile_rows))
+    return out
+
+
+def encode_stream(st: StreamSpec) -> bytes:
+    sizes = resolve_sizes(st)
+    out = bytearray()
+    out += b"DKIF" + struct.pack("<HH4sHHIIII", 0, 32, b"VP90", st.width, st.height,
+                                 30, 1, len(st.frames), 0)
+    for i, (fs, (w, h)) in enumerate(zip(st.frames, sizes)):
+        rng = np.random.default_rng([st.seed, i])
+        fr = encode_frame(st, fs, w, h, rng)
+        out += struct.pack("<IQ", len(fr), i)
+        out += fr
+    return bytes(out)

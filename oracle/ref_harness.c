@@ -1,0 +1,133 @@
+/*
+ * ref_harness.c -- TEST INFRASTRUCTURE (oracle/): drives the UNMODIFIED reference
+ * software VP9 decoder (libavcodec "vp9", /root/reference/libavcodec/vp9.c:1965)
+ * through the public avcodec API and prints one MD5 per output frame.
+ *
+ * It stands in for `ffmpeg -i S.ivf -f framemd5 -` (reference tests/fate-run.sh:172-174):
+ * the hash covers the visible w x h crop of each plane, packed without stride,
+ * 10-bit samples as little-endian 16-bit -- the byte string libavcodec/rawenc.c:52-60
+ * hands to the framemd5 muxer.  IVF parsing follows libavformat/ivfdec.c:29-57.
+ *
+ * usage: ffvp9_ref [-threads N] [-thread_type frame|slice] [-null] [-raw out.yuv] in.ivf
+ */
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <time.h>
+
+#include "libavcodec/avcodec.h"
+#include "libavutil/frame.h"
+#include "libavutil/md5.h"
+#include "libavutil/pixdesc.h"
+
+static double now_s(void)
+{
+    struct timespec ts;
+    clock_gettime(CLOCK_MONOTONIC, &ts);
+    return ts.tv_sec + 1e-9 * ts.tv_nsec;
+}
+
+static unsigned rl32(const unsigned char *p) { return p[0] | p[1] << 8 | p[2] << 16 | (unsigned)p[3] << 24; }
+
+static int nframes;
+static int do_hash = 1;
+static FILE *raw;
+
+static void emit(AVFrame *f)
+{
+    const AVPixFmtDescriptor *d = av_pix_fmt_desc_get(f->format);
+    int bps = d->comp[0].depth > 8 ? 2 : 1;
+    if (do_hash || raw) {
+        struct AVMD5 *md5 = av_md5_alloc();
+        unsigned char dig[16];
+        av_md5_init(md5);
+        for (int p = 0; p < 3; p++) {
+            int w = p ? AV_CEIL_RSHIFT(f->width, d->log2_chroma_w) : f->width;
+            int h = p ? AV_CEIL_RSHIFT(f->height, d->log2_chroma_h) : f->height;
+            for (int y = 0; y < h; y++) {
+                const unsigned char *row = f->data[p] + (ptrdiff_t)y * f->linesize[p];
+                av_md5_update(md5, row, w * bps);
+                if (raw)
+                    fwrite(row, 1, w * bps, raw);
+            }
+        }
+        av_md5_final(md5, dig);
+        av_free(md5);
+        printf("%d %d %d %s ", nframes, f->width, f->height, d->name);
+        for (int i = 0; i < 16; i++)
+            printf("%02x", dig[i]);
+        printf("\n");
+    }
+    nframes++;
+}
+
+int main(int argc, char **argv)
+{
+    int threads = 1, ttype = 0;
+    const char *in = NULL;
+    for (int i = 1; i < argc; i++) {
+        if (!strcmp(argv[i], "-threads") && i + 1 < argc) threads = atoi(argv[++i]);
+        else if (!strcmp(argv[i], "-thread_type") && i + 1 < argc)
+            ttype = !strcmp(argv[++i], "slice") ? FF_THREAD_SLICE : FF_THREAD_FRAME;
+        else if (!strcmp(argv[i], "-null")) do_hash = 0;
+        else if (!strcmp(argv[i], "-raw") && i + 1 < argc) raw = fopen(argv[++i], "wb");
+        else in = argv[i];
+    }
+    if (!in) {
+        fprintf(stderr, "usage: %s [-threads N] [-thread_type frame|slice] [-null] [-raw f] in.ivf\n", argv[0]);
+        return 2;
+    }
+    FILE *fp = fopen(in, "rb");
+    if (!fp) { perror(in); return 2; }
+    fseek(fp, 0, SEEK_END);
+    long sz = ftell(fp);
+    fseek(fp, 0, SEEK_SET);
+    unsigned char *buf = malloc(sz + AV_INPUT_BUFFER_PADDING_SIZE);
+    if (fread(buf, 1, sz, fp) != (size_t)sz) return 2;
+    memset(buf + sz, 0, AV_INPUT_BUFFER_PADDING_SIZE);
+    fclose(fp);
+    if (sz < 32 || memcmp(buf, "DKIF", 4)) { fprintf(stderr, "not IVF\n"); return 2; }
+
+    const AVCodec *codec = avcodec_find_decoder(AV_CODEC_ID_VP9);
+    if (!codec) { fprintf(stderr, "no vp9 decoder\n"); return 2; }
+    AVCodecContext *c = avcodec_alloc_context3(codec);
+    c->thread_count = threads;
+    if (ttype) c->thread_type = ttype;
+    c->flags |= AV_CODEC_FLAG_BITEXACT;
+    c->err_recognition |= AV_EF_EXPLODE;
+    if (avcodec_open2(c, codec, NULL) < 0) { fprintf(stderr, "open failed\n"); return 2; }
+
+    AVPacket *pkt = av_packet_alloc();
+    AVFrame *fr = av_frame_alloc();
+    long pos = rl32(buf + 4) >> 16 ? 32 : 32; /* header length field is 16-bit at +6; always 32 */
+    int rc = 0;
+    double t0 = now_s();
+    while (pos + 12 <= sz) {
+        unsigned fsz = rl32(buf + pos);
+        if (pos + 12 + fsz > sz) { fprintf(stderr, "truncated IVF\n"); rc = 1; break; }
+        /* the packet payload must be padded: copy into an av_new_packet */
+        if (av_new_packet(pkt, fsz) < 0) return 2;
+        memcpy(pkt->data, buf + pos + 12, fsz);
+        pkt->pts = pkt->dts = rl32(buf + pos + 4);
+        pos += 12 + fsz;
+        int r = avcodec_send_packet(c, pkt);
+        av_packet_unref(pkt);
+        if (r < 0) { fprintf(stderr, "decode error %d at packet pts %ld\n", r, (long)pkt->pts); rc = 1; break; }
+        while ((r = avcodec_receive_frame(c, fr)) >= 0) { emit(fr); av_frame_unref(fr); }
+        if (r != AVERROR(EAGAIN) && r != AVERROR_EOF) { fprintf(stderr, "decode error %d\n", r); rc = 1; break; }
+    }
+    if (!rc) {
+        avcodec_send_packet(c, NULL);
+        int r;
+        while ((r = avcodec_receive_frame(c, fr)) >= 0) { emit(fr); av_frame_unref(fr); }
+        if (r != AVERROR_EOF && r != AVERROR(EAGAIN)) { fprintf(stderr, "decode error %d at drain\n", r); rc = 1; }
+    }
+    double dt = now_s() - t0;
+    fprintf(stderr, "frames=%d seconds=%.6f fps=%.3f threads=%d\n", nframes, dt, nframes / dt, threads);
+    if (raw) fclose(raw);
+    av_frame_free(&fr);
+    av_packet_free(&pkt);
+    avcodec_free_context(&c);
+    free(buf);
+    return rc;
+}
