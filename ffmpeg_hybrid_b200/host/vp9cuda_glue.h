@@ -1,0 +1,38 @@
+/*
+ * vp9cuda_glue.h -- host side of the vp9cuda back end, compiled INTO libavcodec next to vp9.c
+ * (it takes the place of the fork's vp9_webgpu.[ch]; same seam).
+ *
+ * The hooks below are called from the sites where the reference's fork attached its WebGPU
+ * prototype (vp9.c:1319-1324, 1839-1845, 1905-1917, 1281-1292; vp9block.c:1389-1405;
+ * vp9lpf.c:188-208).  With the back end active no pixel is touched on the host: the hooks only
+ * write records into the pinned lane rings of include/vp9cuda.h.
+ */
+#ifndef AVCODEC_VP9CUDA_GLUE_H
+#define AVCODEC_VP9CUDA_GLUE_H
+
+#include <stddef.h>
+
+struct AVCodecContext;
+struct AVFrame;
+struct VP9Context;
+struct VP9TileData;
+struct VP9Filter;
+typedef struct VP9CudaGlue VP9CudaGlue;
+
+/* vp9_decode_init: attach the back end.  Fails (negative AVERROR) when libvp9cuda.so or a
+ * B200 is missing -- there is deliberately no software fallback. */
+int  ff_vp9cuda_init(struct AVCodecContext *avctx);
+/* vp9_decode_free */
+void ff_vp9cuda_uninit(struct AVCodecContext *avctx);
+/* vp9_decode_flush */
+void ff_vp9cuda_flush(struct AVCodecContext *avctx);
+/* vp9_decode_frame, after the header is parsed and CUR_FRAME allocated, before the tile loop */
+int  ff_vp9cuda_begin_frame(struct AVCodecContext *avctx);
+/* ff_vp9_decode_block, in place of ff_vp9_{intra,inter}_recon_{8,16}bpp + overhang copies */
+void ff_vp9cuda_emit_block(struct VP9TileData *td);
+/* ff_vp9_loopfilter_sb, in place of filter_plane_cols/rows */
+void ff_vp9cuda_emit_lf(struct VP9Context *s, const struct VP9Filter *lflvl, int row, int col);
+/* vp9_decode_frame, after the tile loop: submit, reconstruct, copy CUR_FRAME back, wait */
+int  ff_vp9cuda_end_frame(struct AVCodecContext *avctx);
+
+#endif /* AVCODEC_VP9CUDA_GLUE_H */

@@ -1,0 +1,203 @@
+/*
+ * vp9cuda.h -- C ABI of libvp9cuda.so, the B200 (sm_100a) VP9 reconstruction back end.
+ *
+ * This is the drop-in boundary for the reference's per-block reconstruction path
+ * (SURVEY.md section 8b).  The host keeps libavcodec's serial entropy decode
+ * (vp9.c decode_frame / vp9block.c decode_coeffs) and, instead of calling the
+ * VP9DSPContext slots, writes records into pinned "lane rings" and hands them over here.
+ * Every entry point names the reference interface it replaces (paths relative to the
+ * reference tree).  Plain pointers and sizes only; no CUDA or torch types.
+ *
+ * Error model: 0 on success, negative errno-style code otherwise (AVERROR-compatible:
+ * -EINVAL, -ENOMEM, -EIO for a CUDA failure, -ENODEV when no sm_100 GPU is present).
+ * Nothing here ever falls back to a CPU implementation.
+ *
+ * Threading: one Vp9CudaCtx per decoder instance (= per stream), bound to one GPU and its own
+ * CUDA streams.  begin_frame / finish_frame / wait / flush come from the decode thread.
+ * A lane ring has exactly one producer thread; submit_tile may be called concurrently for
+ * DIFFERENT lanes (libavcodec slice threading, vp9.c:1442-1520, runs one lane per tile column).
+ */
+#ifndef VP9CUDA_H
+#define VP9CUDA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VP9CUDA_ABI_VERSION 1
+#define VP9CUDA_MAX_LANES   64   /* max tile columns, vp9.c:800-810 */
+
+typedef struct Vp9CudaCtx Vp9CudaCtx;
+
+/* ---- records (host writes, GPU reads) -------------------------------------------------- */
+
+/* One per inter-coded block: what inter_pred() reads from VP9Block (vp9_mc_template.c:30-464,
+ * vp9dec.h:89-97).  Sub-block / chroma motion vectors are derived on the GPU. */
+typedef struct Vp9CudaInterBlock {
+    uint16_t col, row;       /* td->col, td->row: position in 8x8 units */
+    uint8_t  bs;             /* enum BlockSize, BS_64x64=0 .. BS_4x4=12 (vp9shared.h:86-101) */
+    uint8_t  filter;         /* enum FilterMode 0 smooth, 1 regular, 2 sharp, 3 bilinear */
+    uint8_t  comp;           /* compound prediction */
+    uint8_t  ref[2];         /* b->ref[]: 0..2, index into Vp9CudaFrameHeader.ref_slot */
+    uint8_t  pad[3];
+    int16_t  mv[4][2][2];    /* b->mv[sub-block][ref] as {x, y}, 1/8 luma pel */
+    uint32_t reserved;
+} Vp9CudaInterBlock;         /* 48 bytes */
+
+/* One per transform block with eob > 0 of an INTER block: the itxfm_add call of
+ * inter_recon() (vp9recon.c:707-763).  Kept in four lists by transform size. */
+typedef struct Vp9CudaTx {
+    uint16_t x4, y4;         /* position inside the plane, in 4-pixel units */
+    uint16_t eob;
+    uint8_t  plane;          /* 0 Y, 1 U, 2 V */
+    uint8_t  txtp;           /* enum TxfmType | 0x80 when lossless (WHT, slot index 4) */
+    uint32_t coef_off;       /* first coefficient in the lane's coefficient ring */
+} Vp9CudaTx;                 /* 12 bytes */
+
+/* One per transform block of an INTRA block, in the order intra_recon() walks them
+ * (vp9recon.c:269-358): prediction (check_intra_mode, vp9recon.c:37-221) then itxfm_add. */
+typedef struct Vp9CudaIntraTx {
+    uint16_t x4, y4;
+    uint16_t eob;            /* 0 = prediction only */
+    uint8_t  plane;          /* 0 Y, 1 U, 2 V */
+    uint8_t  tx;             /* enum TxfmMode 0..3 */
+    uint8_t  mode;           /* signalled IntraPredMode 0..9 (edge remap happens on the GPU) */
+    uint8_t  txtp;           /* enum TxfmType | 0x80 when lossless */
+    uint8_t  flags;          /* VP9CUDA_ITX_* */
+    uint8_t  pad;
+    uint32_t coef_off;
+} Vp9CudaIntraTx;            /* 16 bytes */
+#define VP9CUDA_ITX_HAVE_LEFT  1   /* col > tile_col_start || x > 0  (vp9recon.c:46) */
+#define VP9CUDA_ITX_HAVE_RIGHT 2   /* x < w - 1 inside the coding block (vp9recon.c:47) */
+
+/* Per 64x64 superblock: where its intra transform blocks sit in the producing lane's list. */
+typedef struct Vp9CudaSbIndex {
+    uint32_t itx_start;
+    uint16_t itx_count;
+    uint8_t  lane;
+    uint8_t  pad;
+} Vp9CudaSbIndex;            /* 8 bytes */
+
+/* Byte-for-byte VP9Filter (vp9dec.h:83-87): level[64] then mask[2][2][8][4]. */
+typedef struct Vp9CudaLoopFilterSb {
+    uint8_t level[64];
+    uint8_t mask[2][2][8][4];
+} Vp9CudaLoopFilterSb;       /* 192 bytes */
+
+/* ---- per-frame header ------------------------------------------------------------------- */
+
+/* What the GPU needs from VP9BitstreamHeader / VP9Context after decode_frame_header()
+ * (vp9.c:519-1113).  Replaces the fork's ff_vp9_webgpu_begin_frame (vp9_webgpu.h:477). */
+typedef struct Vp9CudaFrameHeader {
+    uint32_t w, h;               /* coded frame size in pixels */
+    uint8_t  bpp;                /* 8, 10 or 12 */
+    uint8_t  ss_h, ss_v;         /* only 4:2:0 (1,1) is implemented in this round */
+    uint8_t  keyframe, intraonly, lossless, invisible;
+    uint8_t  lf_level;           /* s->s.h.filter.level; 0 = loop filter off */
+    uint8_t  refreshrefmask;     /* vp9.c:1687-1692 */
+    uint8_t  ref_slot[3];        /* s->s.h.refidx[0..2]: reference slot 0..7 */
+    uint16_t mvscale[3][2];      /* s->mvscale, 0 = unscaled (vp9.c:857-872) */
+    uint8_t  mvstep[3][2];       /* s->mvstep */
+    uint8_t  n_lanes;            /* producer lanes this frame (1, or tile columns when slice-threaded) */
+    uint8_t  pad[3];
+    uint16_t lane_sbs[VP9CUDA_MAX_LANES]; /* superblocks each lane will produce (sizes its ring) */
+    uint8_t  lim_lut[64];        /* s->filter_lut (vp9.c:673-686) */
+    uint8_t  mblim_lut[64];
+} Vp9CudaFrameHeader;
+
+/* Pinned host memory of one producer lane for the current frame. */
+typedef struct Vp9CudaLaneRing {
+    Vp9CudaInterBlock *blk;  uint32_t blk_cap;
+    Vp9CudaTx *tx[4];        uint32_t tx_cap[4];   /* by transform size 4x4..32x32 */
+    Vp9CudaIntraTx *itx;     uint32_t itx_cap;
+    void *coef;              uint32_t coef_cap;    /* int16_t (8-bit) or int32_t (10/12-bit) units */
+} Vp9CudaLaneRing;
+
+typedef struct Vp9CudaLaneCounts {
+    uint32_t blk, tx[4], itx, coef;
+} Vp9CudaLaneCounts;
+
+/* Frame-level pinned arrays, one entry per superblock in raster order. */
+typedef struct Vp9CudaFrameRing {
+    Vp9CudaSbIndex *sb_index;
+    Vp9CudaLoopFilterSb *lf;
+    uint32_t n_sb;
+    uint32_t frame_id;       /* names this frame in the calls below (frames may overlap in time
+                                under libavcodec frame threading, pthread_frame.c) */
+} Vp9CudaFrameRing;
+
+/* ---- life cycle -------------------------------------------------------------------------- */
+
+/* Replaces ff_vp9_webgpu_init (vp9_webgpu.h:371; call site vp9.c:1905-1917).
+ * max_w/max_h bound every frame of the stream (all sizes); frames_in_flight >= 1. */
+int  vp9cuda_create(Vp9CudaCtx **out, int device, int max_w, int max_h, int max_bpp,
+                    int frames_in_flight);
+/* Replaces ff_vp9_webgpu_uninit (vp9_webgpu.h:374; call site vp9.c:1281-1292). */
+void vp9cuda_destroy(Vp9CudaCtx *ctx);
+/* Replaces vp9_decode_flush's reference drop (vp9.c:1865-1883). */
+int  vp9cuda_flush(Vp9CudaCtx *ctx);
+
+/* ---- per frame ----------------------------------------------------------------------------- */
+
+/* Call after decode_frame_header + vp9_frame_alloc (vp9.c:1657-1692), before the tile loop, in
+ * DECODE ORDER (reference slots are resolved here).  Blocks only if all frames_in_flight ring
+ * sets are still in use.  Fills *ring. */
+int  vp9cuda_begin_frame(Vp9CudaCtx *ctx, const Vp9CudaFrameHeader *hdr, Vp9CudaFrameRing *ring);
+/* Pinned ring of one lane of the current frame. */
+int  vp9cuda_tile_ring(Vp9CudaCtx *ctx, uint32_t frame_id, int lane, Vp9CudaLaneRing *ring);
+/* Records [previous counts, counts) of this lane are final: start their host->device copy.
+ * Called by the lane's producer at tile / superblock-row granularity (decode_tiles,
+ * vp9.c:1325-1395; decode_tiles_mt, vp9.c:1465-1518).  Counts are cumulative for the frame. */
+int  vp9cuda_submit_tile(Vp9CudaCtx *ctx, uint32_t frame_id, int lane,
+                         const Vp9CudaLaneCounts *counts);
+/* All lanes submitted: enqueue inter prediction -> residual -> intra wavefront -> loop filter
+ * -> reference refresh and, when out_planes != NULL, the async copy of the visible w x h crop
+ * (framemd5 layout: packed rows, 10-bit as little-endian 16-bit).  Replaces the reconstruction
+ * half of decode_tiles + ff_vp9_webgpu_end_frame (vp9.c:1839-1857).  Returns a ticket. */
+int  vp9cuda_finish_frame(Vp9CudaCtx *ctx, uint32_t frame_id, uint8_t *const out_planes[3],
+                          const ptrdiff_t out_strides[3], uint64_t *ticket);
+/* Block until the frame behind `ticket` is complete (pixels in out_planes valid). */
+int  vp9cuda_wait(Vp9CudaCtx *ctx, uint64_t ticket);
+/* show_existing_frame (vp9.c:1636-1653): copy reference slot `slot` to host. */
+int  vp9cuda_show_existing(Vp9CudaCtx *ctx, int slot, uint8_t *const out_planes[3],
+                           const ptrdiff_t out_strides[3], uint64_t *ticket);
+
+/* ---- measurement / test support ------------------------------------------------------------- */
+
+/* finish_frame split in two so a bench can keep records resident in HBM:
+ * stage = copy this frame's records host->device and keep them under `handle`;
+ * run   = reconstruct a staged frame (any number of times, in stream order). */
+int  vp9cuda_stage_frame(Vp9CudaCtx *ctx, uint32_t frame_id, int *handle);
+int  vp9cuda_run_staged(Vp9CudaCtx *ctx, int handle, uint8_t *const out_planes[3],
+                        const ptrdiff_t out_strides[3], uint64_t *ticket);
+/* Cumulative device time (CUDA events on the ctx's stream) and launch count per kernel family.
+ * names/ms/launches hold up to `cap` entries; returns the number filled. */
+int  vp9cuda_kernel_stats(Vp9CudaCtx *ctx, const char **names, double *ms, uint64_t *launches,
+                          uint64_t *bytes, int cap);
+int  vp9cuda_set_option(Vp9CudaCtx *ctx, const char *key, int value);
+const char *vp9cuda_version(void);
+
+/* ---- slot-level entry points: the batched equivalent of one VP9DSPContext slot -------------
+ * (vp9dsp.h:40-122).  Host buffers in and out; used by the checkasm-style parity tests
+ * (reference tests/checkasm/vp9dsp.c).  Item i works on its own 64x64-pixel tile at
+ * pix + i*64*64*bytes_per_pixel with a stride of 64 pixels. */
+int  vp9cuda_slot_itxfm_add(int device, int bpp, int n, const uint8_t *tx, const uint8_t *txtp,
+                            const uint16_t *eob, void *pix, const void *coef /* n*1024 */);
+int  vp9cuda_slot_intra_pred(int device, int bpp, int n, const uint8_t *tx, const uint8_t *mode,
+                             void *pix, const void *left /* n*64 */, const void *top /* n*(1+64+16) */);
+int  vp9cuda_slot_mc(int device, int bpp, int n, const uint8_t *w, const uint8_t *h,
+                     const uint8_t *filter, const uint8_t *avg, const uint8_t *mx,
+                     const uint8_t *my, const uint8_t *dx, const uint8_t *dy /* 0 = unscaled */,
+                     void *pix, const void *ref /* n tiles of 160x160 pixels, block origin at (8,8) */);
+int  vp9cuda_slot_loop_filter(int device, int bpp, int n, const uint8_t *wd /* 4,8,16 */,
+                              const uint8_t *dir, const uint8_t *len /* 8 or 16 */,
+                              const int32_t *E, const int32_t *I, const int32_t *H,
+                              void *pix /* edge at (32,32) of each tile */);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VP9CUDA_H */

@@ -1,7 +1,10 @@
 /*
- * ref_harness.c -- TEST INFRASTRUCTURE (oracle/): drives the UNMODIFIED reference
- * software VP9 decoder (libavcodec "vp9", /root/reference/libavcodec/vp9.c:1965)
- * through the public avcodec API and prints one MD5 per output frame.
+ * ivf_framemd5.c -- drives libavcodec's "vp9" decoder (reference libavcodec/vp9.c:1965)
+ * through the public avcodec API and prints one MD5 per output frame.  The same file is
+ * linked twice: by oracle/Makefile against the UNMODIFIED reference objects (-> the
+ * framemd5 oracle and timed CPU baseline, oracle/_ref/ffvp9_ref) and by
+ * ffmpeg_hybrid_b200/host/Makefile against the overlay build whose reconstruction runs in
+ * libvp9cuda.so (-> ffvp9_cuda).  It contains no decoding logic of its own.
  *
  * It stands in for `ffmpeg -i S.ivf -f framemd5 -` (reference tests/fate-run.sh:172-174):
  * the hash covers the visible w x h crop of each plane, packed without stride,
