@@ -1,0 +1,230 @@
+/*
+ * vp9_lf.h -- VP9 loop filter: the per-line filter and the decoding of one superblock's
+ * VP9Filter masks into an explicit table of edge operations.
+ *
+ * Reference behaviour reproduced:
+ *   filter arithmetic   libavcodec/vp9dsp_template.c:1780-1888 (loop_filter), wrappers :1890-1967
+ *   mask / level walk   libavcodec/vp9lpf.c:31-181 (filter_plane_cols / filter_plane_rows),
+ *                       order per superblock and plane: all column edges, then all row edges
+ *                       (vp9lpf.c:222-229)
+ *   E/I/H from level    vp9lpf.c:47-48 with s->filter_lut (vp9.c:673-686)
+ *
+ * An "op" says: on these 8 lines, at this edge position, run a filter of width wd (4, 8 or 16)
+ * with level L.  Ops on the same line are applied in increasing position, exactly the order
+ * in which the reference reaches them.
+ */
+#ifndef VP9_LF_H
+#define VP9_LF_H
+
+#include "vp9_itx.h"
+
+namespace vp9 {
+
+/* px[0..15] = p7..p0, q0..q7 across the edge (only px[4..11] are read for wd < 16).
+ * Returns a bit mask of modified entries (bit i = px[i] written).
+ * E, I, H are the 8-bit-domain thresholds (mblim_lut[L], lim_lut[L], L >> 4). */
+VP9_HD unsigned lf_line(int *px, int wd, int E, int I, int H, int bpp)
+{
+    const int sh = bpp - 8, F = 1 << sh;
+    E <<= sh; I <<= sh; H <<= sh;
+    const int p3 = px[4], p2 = px[5], p1 = px[6], p0 = px[7];
+    const int q0 = px[8], q1 = px[9], q2 = px[10], q3 = px[11];
+#define VP9_ABS(v) ((v) < 0 ? -(v) : (v))
+    bool fm = VP9_ABS(p3 - p2) <= I && VP9_ABS(p2 - p1) <= I && VP9_ABS(p1 - p0) <= I &&
+              VP9_ABS(q1 - q0) <= I && VP9_ABS(q2 - q1) <= I && VP9_ABS(q3 - q2) <= I &&
+              VP9_ABS(p0 - q0) * 2 + (VP9_ABS(p1 - q1) >> 1) <= E;
+    if (!fm)
+        return 0;
+    bool flat8out = false, flat8in = false;
+    if (wd >= 16) {
+        flat8out = VP9_ABS(px[0] - p0) <= F && VP9_ABS(px[1] - p0) <= F &&
+                   VP9_ABS(px[2] - p0) <= F && VP9_ABS(px[3] - p0) <= F &&
+                   VP9_ABS(px[12] - q0) <= F && VP9_ABS(px[13] - q0) <= F &&
+                   VP9_ABS(px[14] - q0) <= F && VP9_ABS(px[15] - q0) <= F;
+    }
+    if (wd >= 8)
+        flat8in = VP9_ABS(p3 - p0) <= F && VP9_ABS(p2 - p0) <= F && VP9_ABS(p1 - p0) <= F &&
+                  VP9_ABS(q1 - q0) <= F && VP9_ABS(q2 - q0) <= F && VP9_ABS(q3 - q0) <= F;
+    if (wd >= 16 && flat8out && flat8in) {
+        /* 15-tap: out[i] (i = 1..14) = (sum of the 15 inputs centred on i with the ends
+         * replicated, centre counted twice + 8) >> 4 */
+        int v[16];
+#pragma unroll
+        for (int i = 0; i < 16; i++) v[i] = px[i];
+#pragma unroll
+        for (int i = 1; i <= 14; i++) {
+            int s = v[i] + 8;
+#pragma unroll
+            for (int k = -7; k <= 7; k++) {
+                int j = i + k;
+                j = j < 0 ? 0 : (j > 15 ? 15 : j);
+                s += v[j];
+            }
+            px[i] = s >> 4;
+        }
+        return 0x7FFE;
+    }
+    if (wd >= 8 && flat8in) {
+        px[5]  = (p3 + p3 + p3 + 2 * p2 + p1 + p0 + q0 + 4) >> 3;
+        px[6]  = (p3 + p3 + p2 + 2 * p1 + p0 + q0 + q1 + 4) >> 3;
+        px[7]  = (p3 + p2 + p1 + 2 * p0 + q0 + q1 + q2 + 4) >> 3;
+        px[8]  = (p2 + p1 + p0 + 2 * q0 + q1 + q2 + q3 + 4) >> 3;
+        px[9]  = (p1 + p0 + q0 + 2 * q1 + q2 + q3 + q3 + 4) >> 3;
+        px[10] = (p0 + q0 + q1 + 2 * q2 + q3 + q3 + q3 + 4) >> 3;
+        return 0x07E0;
+    }
+    {
+        const int lim_hi = (1 << (bpp - 1)) - 1, lim_lo = -(1 << (bpp - 1));
+        bool hev = VP9_ABS(p1 - p0) > H || VP9_ABS(q1 - q0) > H;
+        if (hev) {
+            int f = iclamp(p1 - q1, lim_lo, lim_hi);
+            f = iclamp(3 * (q0 - p0) + f, lim_lo, lim_hi);
+            int f1 = (f + 4 < lim_hi ? f + 4 : lim_hi) >> 3;
+            int f2 = (f + 3 < lim_hi ? f + 3 : lim_hi) >> 3;
+            px[7] = clip_pixel(p0 + f2, bpp);
+            px[8] = clip_pixel(q0 - f1, bpp);
+            return 0x0180;
+        } else {
+            int f = iclamp(3 * (q0 - p0), lim_lo, lim_hi);
+            int f1 = (f + 4 < lim_hi ? f + 4 : lim_hi) >> 3;
+            int f2 = (f + 3 < lim_hi ? f + 3 : lim_hi) >> 3;
+            px[7] = clip_pixel(p0 + f2, bpp);
+            px[8] = clip_pixel(q0 - f1, bpp);
+            f = (f1 + 1) >> 1;
+            px[6] = clip_pixel(p1 + f, bpp);
+            px[9] = clip_pixel(q1 - f, bpp);
+            return 0x03C0;
+        }
+    }
+#undef VP9_ABS
+}
+
+/* byte-for-byte VP9Filter (vp9dec.h:83-87) */
+struct LfSb {
+    uint8_t level[64];
+    uint8_t mask[2][2][8][4];
+};
+
+/* One edge operation: wd = 0 (none), 4, 8, 16; L = filter level */
+struct LfOp {
+    uint8_t wd, L;
+};
+
+/* Edge-op tables of one superblock and one plane.
+ *   luma  : col[g][p]  g = 8-row group 0..7,  p = edge at x = 4p (p = 0..15)
+ *           row[e][c]  e = edge at y = 4e (0..15), c = 8-column group 0..7
+ *   chroma (4:2:0): col[g][p] g = 0..3 (8 chroma rows), p = edge at x = 4p (0..7)
+ *           row[e][c]  e = edge at y = 4e (0..7), c = 8-column group 0..3
+ * Unused entries have wd = 0. */
+struct LfOps {
+    LfOp col[8][16];
+    LfOp row[16][8];
+};
+
+VP9_HD void lf_set(LfOp &o, int wd, int L) { o.wd = (uint8_t)wd; o.L = (uint8_t)L; }
+
+/* filter_plane_cols, vp9lpf.c:31-107.  first_col: superblock is at the frame's left edge. */
+VP9_HD void lf_decode_cols(const LfSb &f, bool chroma, bool first_col, LfOps &ops)
+{
+    const int ss = chroma ? 1 : 0;
+    const uint8_t (*mask)[4] = f.mask[ss][0];
+    for (int g = 0; g < 8; g++)
+        for (int p = 0; p < 16; p++)
+            lf_set(ops.col[g][p], 0, 0);
+    int it = 0;
+    for (int y = 0; y < 8; y += 2 << ss, it++) {
+        const uint8_t *h1 = mask[y], *h2 = mask[y + 1 + ss];
+        const uint8_t *lvl = f.level + it * (16 << ss);
+        unsigned hm1 = h1[0] | h1[1] | h1[2], hm13 = h1[3];
+        unsigned hm2 = h2[1] | h2[2], hm23 = h2[3];
+        unsigned hm = hm1 | hm2 | hm13 | hm23;
+        int g1 = 2 * it, g2 = 2 * it + 1;   /* 8-line groups of the two halves */
+        int loff = 0;
+        for (int b = 0; b < 8 && (hm & ~((1u << b) - 1)); b++) {
+            unsigned x = 1u << b;
+            const uint8_t *l = lvl + loff;
+            int pm = chroma ? b : 2 * b;     /* position index of the main edge */
+            if (!first_col || b > 0) {
+                if (hm1 & x) {
+                    int L = l[0];
+                    if (h1[0] & x) {
+                        lf_set(ops.col[g1][pm], 16, L);
+                        if (h2[0] & x)
+                            lf_set(ops.col[g2][pm], 16, L);
+                    } else if (hm2 & x) {
+                        lf_set(ops.col[g1][pm], (h1[1] & x) ? 8 : 4, L);
+                        lf_set(ops.col[g2][pm], (h2[1] & x) ? 8 : 4, l[8 << ss]);
+                    } else {
+                        lf_set(ops.col[g1][pm], (h1[1] & x) ? 8 : 4, L);
+                    }
+                } else if (hm2 & x) {
+                    lf_set(ops.col[g2][pm], (h2[1] & x) ? 8 : 4, l[8 << ss]);
+                }
+            }
+            if (chroma) {
+                if (x & 0xAA)
+                    loff += 2;
+            } else {
+                if (hm13 & x)
+                    lf_set(ops.col[g1][pm + 1], 4, l[0]);
+                if (hm23 & x)
+                    lf_set(ops.col[g2][pm + 1], 4, l[8]);
+                loff++;
+            }
+        }
+    }
+}
+
+/* filter_plane_rows, vp9lpf.c:109-181.  first_row: superblock is at the frame's top edge. */
+VP9_HD void lf_decode_rows(const LfSb &f, bool chroma, bool first_row, LfOps &ops)
+{
+    const int ss = chroma ? 1 : 0;
+    const uint8_t (*mask)[4] = f.mask[ss][1];
+    for (int e = 0; e < 16; e++)
+        for (int c = 0; c < 8; c++)
+            lf_set(ops.row[e][c], 0, 0);
+    const uint8_t *lvl = f.level;
+    for (int y = 0; y < 8; y++) {
+        const uint8_t *vmask = mask[y];
+        unsigned vm = vmask[0] | vmask[1] | vmask[2], vm3 = vmask[3];
+        int em = chroma ? y : 2 * y;          /* edge index of the main edge (units of 4 rows) */
+        int j = 0;
+        for (int b = 0; b < 8 && (vm & ~((1u << b) - 1)); b += 2 << ss, j++) {
+            unsigned x = 1u << b, x2 = x << (1 + ss);
+            const uint8_t *l = lvl + j * (2 << ss);
+            int c1 = 2 * j, c2 = 2 * j + 1;   /* 8-column groups of the two halves */
+            if (!first_row || y) {
+                if (vm & x) {
+                    int L = l[0];
+                    if (vmask[0] & x) {
+                        lf_set(ops.row[em][c1], 16, L);
+                        if (vmask[0] & x2)
+                            lf_set(ops.row[em][c2], 16, L);
+                    } else if (vm & x2) {
+                        lf_set(ops.row[em][c1], (vmask[1] & x) ? 8 : 4, L);
+                        lf_set(ops.row[em][c2], (vmask[1] & x2) ? 8 : 4, l[1 + ss]);
+                    } else {
+                        lf_set(ops.row[em][c1], (vmask[1] & x) ? 8 : 4, L);
+                    }
+                } else if (vm & x2) {
+                    lf_set(ops.row[em][c2], (vmask[1] & x2) ? 8 : 4, l[1 + ss]);
+                }
+            }
+            if (!chroma) {
+                if (vm3 & x)
+                    lf_set(ops.row[em + 1][c1], 4, l[0]);
+                if (vm3 & x2)
+                    lf_set(ops.row[em + 1][c2], 4, l[1]);
+            }
+        }
+        if (chroma) {
+            if (y & 1)
+                lvl += 16;
+        } else {
+            lvl += 8;
+        }
+    }
+}
+
+} /* namespace vp9 */
+#endif /* VP9_LF_H */

@@ -79,7 +79,7 @@ static int dump_create(Vp9CudaCtx **out, int dev, int w, int h, int bpp, int nfl
         av_free(d);
         return -EIO;
     }
-    fwrite("V9R1", 1, 4, d->fp);
+    fwrite("V9R2", 1, 4, d->fp);
     {
         uint32_t sz[8] = { sizeof(Vp9CudaFrameHeader), sizeof(Vp9CudaLaneCounts),
                            sizeof(Vp9CudaInterBlock), sizeof(Vp9CudaTx), sizeof(Vp9CudaIntraTx),
@@ -130,6 +130,7 @@ static int dump_begin_frame(Vp9CudaCtx *c, const Vp9CudaFrameHeader *h, Vp9CudaF
     memset(d->sb_index, 0, n_sb * sizeof(*d->sb_index));
     memset(d->lf, 0, n_sb * sizeof(*d->lf));
     d->n_sb = n_sb;
+    uint32_t coef_base = 0;
     for (int l = 0; l < h->n_lanes; l++) {
         unsigned sbs = h->lane_sbs[l];
         Vp9CudaLaneRing *r = &d->ring[l];
@@ -152,6 +153,8 @@ static int dump_begin_frame(Vp9CudaCtx *c, const Vp9CudaFrameHeader *h, Vp9CudaF
             d->lane_sbs[l] = sbs;
         }
         (void)cb;
+        r->coef_base = coef_base;
+        coef_base += r->coef_cap;
         memset(&d->cnt[l], 0, sizeof(d->cnt[l]));
     }
     fr->sb_index = d->sb_index;
@@ -185,6 +188,7 @@ static int dump_finish_frame(Vp9CudaCtx *c, uint32_t id, uint8_t *const out[3],
         const Vp9CudaLaneRing *r = &d->ring[l];
         const Vp9CudaLaneCounts *n = &d->cnt[l];
         fwrite(n, sizeof(*n), 1, d->fp);
+        fwrite(&r->coef_base, 4, 1, d->fp);
         fwrite(r->blk, sizeof(*r->blk), n->blk, d->fp);
         for (int t = 0; t < 4; t++)
             fwrite(r->tx[t], sizeof(Vp9CudaTx), n->tx[t], d->fp);
@@ -343,7 +347,7 @@ static av_always_inline uint32_t take_coefs(VP9CudaGlue *g, int lane, int16_t *s
     memcpy((uint8_t *)r->coef + (size_t)off * 2 * bytesperpixel, src, bytes);
     memset(src, 0, bytes);
     c->coef = off + n_coefs;
-    return off;
+    return r->coef_base + off;
 }
 
 void ff_vp9cuda_emit_block(VP9TileData *td)

@@ -54,7 +54,8 @@ typedef struct Vp9CudaTx {
     uint16_t eob;
     uint8_t  plane;          /* 0 Y, 1 U, 2 V */
     uint8_t  txtp;           /* enum TxfmType | 0x80 when lossless (WHT, slot index 4) */
-    uint32_t coef_off;       /* first coefficient in the lane's coefficient ring */
+    uint32_t coef_off;       /* first coefficient in the frame's coefficient arena
+                                (= lane ring's coef_base + offset inside the lane) */
 } Vp9CudaTx;                 /* 12 bytes */
 
 /* One per transform block of an INTRA block, in the order intra_recon() walks them
@@ -114,6 +115,9 @@ typedef struct Vp9CudaLaneRing {
     Vp9CudaTx *tx[4];        uint32_t tx_cap[4];   /* by transform size 4x4..32x32 */
     Vp9CudaIntraTx *itx;     uint32_t itx_cap;
     void *coef;              uint32_t coef_cap;    /* int16_t (8-bit) or int32_t (10/12-bit) units */
+    uint32_t coef_base;      /* index of coef[0] in the frame's coefficient arena: every
+                                coef_off the producer writes is coef_base + offset-in-lane */
+    uint32_t reserved;
 } Vp9CudaLaneRing;
 
 typedef struct Vp9CudaLaneCounts {
@@ -165,14 +169,41 @@ int  vp9cuda_wait(Vp9CudaCtx *ctx, uint64_t ticket);
 int  vp9cuda_show_existing(Vp9CudaCtx *ctx, int slot, uint8_t *const out_planes[3],
                            const ptrdiff_t out_strides[3], uint64_t *ticket);
 
+/* ---- one-shot form: the caller owns the record memory ----------------------------------------- */
+
+/* All records of one frame, in caller memory laid out exactly like the lane rings above
+ * (lanes[i].coef_base places lane i in the coefficient arena; capacities are ignored). */
+typedef struct Vp9CudaFrameRecords {
+    const Vp9CudaLaneRing *lanes;        /* hdr->n_lanes entries */
+    const Vp9CudaLaneCounts *counts;     /* hdr->n_lanes entries */
+    const Vp9CudaSbIndex *sb_index;      /* one per superblock, raster order */
+    const Vp9CudaLoopFilterSb *lf;       /* one per superblock, raster order */
+} Vp9CudaFrameRecords;
+
+/* Page-locked host memory for records and output planes (pageable memory also works, slower). */
+void *vp9cuda_host_alloc(size_t bytes);
+void  vp9cuda_host_free(void *p);
+
+/* begin_frame + submit_tile (all lanes) + finish_frame in one call, from caller memory:
+ * host->device copy of the records, reconstruction, optional device->host copy of the
+ * picture.  The record memory may be reused once the ticket has been waited for. */
+int  vp9cuda_decode_frame(Vp9CudaCtx *ctx, const Vp9CudaFrameHeader *hdr,
+                          const Vp9CudaFrameRecords *recs, uint8_t *const out_planes[3],
+                          const ptrdiff_t out_strides[3], uint64_t *ticket);
+
 /* ---- measurement / test support ------------------------------------------------------------- */
 
-/* finish_frame split in two so a bench can keep records resident in HBM:
- * stage = copy this frame's records host->device and keep them under `handle`;
+/* decode_frame split in two so a bench can keep records resident in HBM:
+ * stage = copy one frame's records host->device and keep them under `handle`;
  * run   = reconstruct a staged frame (any number of times, in stream order). */
-int  vp9cuda_stage_frame(Vp9CudaCtx *ctx, uint32_t frame_id, int *handle);
+int  vp9cuda_stage_frame(Vp9CudaCtx *ctx, const Vp9CudaFrameHeader *hdr,
+                         const Vp9CudaFrameRecords *recs, int *handle);
 int  vp9cuda_run_staged(Vp9CudaCtx *ctx, int handle, uint8_t *const out_planes[3],
                         const ptrdiff_t out_strides[3], uint64_t *ticket);
+int  vp9cuda_free_staged(Vp9CudaCtx *ctx, int handle);
+/* MD5-free frame check: 64-bit FNV-style checksum of the visible planes of reference slot
+ * `slot` (or of the last reconstructed frame when slot < 0), computed on the GPU. */
+int  vp9cuda_frame_checksum(Vp9CudaCtx *ctx, int slot, uint64_t *sum);
 /* Cumulative device time (CUDA events on the ctx's stream) and launch count per kernel family.
  * names/ms/launches hold up to `cap` entries; returns the number filled. */
 int  vp9cuda_kernel_stats(Vp9CudaCtx *ctx, const char **names, double *ms, uint64_t *launches,
