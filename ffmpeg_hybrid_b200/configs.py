@@ -1,0 +1,106 @@
+"""The five BASELINE.json workloads (and small variants for the tests) as StreamSpec objects.
+
+Feature mix per config follows SURVEY.md section 8(d).  All streams are produced by
+streamgen.encode_stream (valid headers + seeded model-distributed tile payloads).
+"""
+from __future__ import annotations
+
+from typing import Dict
+
+from .streamgen import (FILTER_SWITCHABLE, PRED_SWITCHABLE, TX_SWITCHABLE, FrameSpec, StreamSpec)
+
+
+def _ippp(n: int, tile_cols: int = 0, compound: bool = False, **kw) -> list:
+    """key frame + (n-1) inter frames cycling through the three reference slots."""
+    frames = [FrameSpec(keyframe=True, refreshrefmask=0xFF, log2_tile_cols=tile_cols, **kw)]
+    for i in range(1, n):
+        frames.append(FrameSpec(
+            refreshrefmask=1 << (i % 3), refidx=(0, 1, 2),
+            signbias=(0, 0, 1) if compound else (0, 0, 0),
+            comppredmode=PRED_SWITCHABLE, filtermode=FILTER_SWITCHABLE,
+            txfmmode=TX_SWITCHABLE, log2_tile_cols=tile_cols, **kw))
+    return frames
+
+
+def c1(frames: int = 30, seed: int = 1) -> StreamSpec:
+    """352x288 8-bit profile 0, 1 key + inter, single tile."""
+    st = StreamSpec(352, 288, seed=seed)
+    st.frames = _ippp(frames)
+    return st
+
+
+def c2(frames: int = 60, seed: int = 2, w: int = 1920, h: int = 1080) -> StreamSpec:
+    """1080p 8-bit IPPP, 4 tile columns, compound prediction, switchable filters."""
+    st = StreamSpec(w, h, seed=seed)
+    st.frames = _ippp(frames, tile_cols=2, compound=True)
+    return st
+
+
+def c3(frames: int = 30, seed: int = 3, w: int = 3840, h: int = 2160) -> StreamSpec:
+    """4K 10-bit profile 2, 32x32 transforms, scaled-reference (resize) frames.
+
+    Every shown frame is w x h.  Every 6th coded frame is a HIDDEN half-size inter frame
+    (predicted from full-size references => down-scaled motion compensation) that refreshes
+    slot 3; the shown frames after it predict from slot 3 as their third reference
+    (=> up-scaled motion compensation, ratio 2x, within vp9.c:862)."""
+    st = StreamSpec(w, h, profile=2, bitdepth=10, seed=seed)
+    fr = [FrameSpec(keyframe=True, refreshrefmask=0xFF, log2_tile_cols=2)]
+    shown = 1
+    i = 1
+    while shown < frames:
+        if i % 6 == 3:
+            fr.append(FrameSpec(show=False, width=w // 2, height=h // 2, refreshrefmask=1 << 3,
+                                refidx=(0, 1, 2), log2_tile_cols=2))
+        else:
+            fr.append(FrameSpec(refreshrefmask=1 << (shown % 3), refidx=(0, 1, 3) if i > 3 else (0, 1, 2),
+                                log2_tile_cols=2))
+            shown += 1
+        i += 1
+    st.frames = fr
+    return st
+
+
+def c4(frames: int = 8, seed: int = 4, w: int = 7680, h: int = 4320) -> StreamSpec:
+    """8K 8-bit, all key frames (intra + loop-filter wavefront bound); second half at max LF level."""
+    st = StreamSpec(w, h, seed=seed)
+    st.frames = [FrameSpec(keyframe=True, refreshrefmask=0xFF, log2_tile_cols=3,
+                           lf_level=32 if i < frames // 2 else 63, lf_sharpness=0)
+                 for i in range(frames)]
+    return st
+
+
+def c5(rank: int, frames: int = 30, w: int = 3840, h: int = 2160) -> StreamSpec:
+    """one of eight independent 4K 8-bit C2-style streams (one per GPU)."""
+    return c2(frames=frames, seed=50 + rank, w=w, h=h)
+
+
+def small_variants() -> Dict[str, StreamSpec]:
+    """Reduced-size relatives of the five configs + edge cases, decoded in seconds on a CPU."""
+    out: Dict[str, StreamSpec] = {}
+    out["c1_small"] = c1(frames=6)
+    out["c2_small"] = c2(frames=5, w=456, h=264)           # non-multiple-of-8 size, 4 tile cols cap
+    out["c3_small"] = c3(frames=8, w=400, h=240)
+    out["c4_small"] = c4(frames=2, w=520, h=392)
+    st = StreamSpec(200, 136, profile=2, bitdepth=12, seed=7)  # 12-bit
+    st.frames = _ippp(4, compound=True)
+    out["hbd12"] = st
+    st = StreamSpec(328, 200, seed=8)                        # lossless (WHT) key + inter
+    st.frames = _ippp(3, yac_qi=0)
+    out["lossless"] = st
+    st = StreamSpec(296, 168, seed=9)                        # sharpness, deltas, high q
+    st.frames = _ippp(4, lf_level=40, lf_sharpness=5, yac_qi=200, ydc_qdelta=-3, uvdc_qdelta=4,
+                      uvac_qdelta=-5, lf_ref_deltas=(2, 0, -2, -4), lf_mode_deltas=(1, -1))
+    out["lf_q"] = st
+    st = StreamSpec(264, 264, seed=10)                       # loop filter off, fixed 8-tap sharp
+    st.frames = _ippp(3, lf_level=0)
+    for f in st.frames[1:]:
+        f.filtermode = 2
+    out["nolf"] = st
+    st = StreamSpec(200, 120, seed=12)                       # hidden intra-only frame mid-stream
+    st.frames = _ippp(5)
+    st.frames[2] = FrameSpec(intraonly=True, show=False, refreshrefmask=0x06, resetctx=0)
+    out["intraonly"] = st
+    st = StreamSpec(72, 40, seed=11)                         # tiny, single superblock column
+    st.frames = _ippp(4, compound=True)
+    out["tiny"] = st
+    return out
