@@ -1,0 +1,79 @@
+/*
+ * dev_common.cuh -- device-side view of one frame: surfaces, record arrays, frame scalars.
+ * Shared by every kernel of libvp9cuda.so.
+ */
+#ifndef VP9CUDA_DEV_COMMON_CUH
+#define VP9CUDA_DEV_COMMON_CUH
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "vp9cuda.h"
+#include "vp9_itx.h"
+#include "vp9_pred.h"
+#include "vp9_lf.h"
+
+namespace vp9 {
+
+/* One picture in HBM: three planes, 64-aligned padded size, stride in pixels.
+ * w,h are the frame's own luma size (what motion compensation clamps to). */
+struct SurfDesc {
+    void *pl[3];
+    int stride[3];
+    int w, h;
+};
+
+/* Everything a kernel needs to know about the frame being reconstructed. */
+struct FrameDesc {
+    SurfDesc cur;
+    SurfDesc ref[3];                 /* by b->ref index (LAST, GOLDEN, ALTREF) */
+    int w, h, cols, rows, sb_cols, sb_rows, bpp;
+    uint16_t mvscale[3][2];
+    uint8_t mvstep[3][2];
+    uint8_t lossless, lf_level;
+    /* records (device pointers), lanes already concatenated */
+    const Vp9CudaInterBlock *blk;  uint32_t n_blk;
+    const Vp9CudaTx *tx[4];        uint32_t n_tx[4];
+    const Vp9CudaIntraTx *itx;     uint32_t n_itx;
+    const void *coef;              /* int16_t (8-bit) or int32_t units, arena indexed by coef_off */
+    const Vp9CudaSbIndex *sb_index;
+    const Vp9CudaLoopFilterSb *lf;
+    uint32_t itx_lane_base[VP9CUDA_MAX_LANES];   /* first record of each lane in `itx` */
+    /* scratch */
+    int32_t *cellmap;              /* cols*rows: index into blk, -1 = not inter */
+    uint16_t *isched_order;        /* n_itx: per (superblock, plane) segment, record idx sorted by level */
+    uint16_t *isched_lvl_end;      /* [sb][plane][64] cumulative count per dependency level */
+    uint32_t *isched_seg;          /* [sb][plane]: segment start in isched_order */
+    uint8_t  *isched_nlvl;         /* [sb][plane]: number of levels (0 = no intra blocks) */
+    int *progress;                 /* [2 stages][3 planes][sb_rows] wavefront counters */
+    uint8_t lim_lut[64], mblim_lut[64];
+};
+
+__device__ __forceinline__ int bs_w8(int bs)
+{
+    /* ff_vp9_bwh_tab[1][bs][0] (vp9data.c:25-33): block width in 8-pixel units */
+    return (int)((0x1111122244488ull >> (4 * bs)) & 15);   /* 8,8,4,4,4,2,2,2,1,1,1,1,1 */
+}
+__device__ __forceinline__ int bs_h8(int bs)
+{
+    /* ff_vp9_bwh_tab[1][bs][1]: 8,4,8,4,2,4,2,1,2,1,1,1,1 */
+    return (int)((0x1111212424848ull >> (4 * bs)) & 15);
+}
+
+__device__ __forceinline__ int rounded_div(int a, int b)
+{
+    return a >= 0 ? (a + (b >> 1)) / b : (a - (b >> 1)) / b;
+}
+
+template <class P> __device__ __forceinline__ P ld_cg(const P *p);
+template <> __device__ __forceinline__ uint8_t ld_cg<uint8_t>(const uint8_t *p)
+{
+    return __ldcg(p);
+}
+template <> __device__ __forceinline__ uint16_t ld_cg<uint16_t>(const uint16_t *p)
+{
+    return __ldcg(p);
+}
+
+} /* namespace vp9 */
+#endif

@@ -1,0 +1,205 @@
+/*
+ * k_inter.cuh -- K2: inter prediction for a whole frame (frame-centric, no dependencies).
+ *
+ *   k_cellmap : one thread per inter block record, writes the record index into every 8x8
+ *               cell the block covers (the per-superblock mode / motion-vector map).
+ *   k_inter   : one CTA per 64x32 luma tile (+ the two 32x16 chroma tiles under it).  A thread
+ *               owns a vertical strip (8 luma or 4 chroma rows of one column): it filters the
+ *               rows it needs horizontally once, then slides the vertical 8-tap over them.
+ *               Reference samples are read with coordinate clamping (= the reference's
+ *               emulated_edge_mc, vp9recon.c:402-412).  Compound blocks average the two
+ *               predictions in registers (vp9dsp_template.c:2051: (dst + pred + 1) >> 1).
+ *               Scaled references and everything else the strip path does not cover go
+ *               through the per-pixel path (vp9::mc_pixel).
+ *
+ * Replaces inter_pred (vp9_mc_template.c:30-464) + mc_luma/chroma_{unscaled,scaled}
+ * (vp9recon.c:376-628) + the mc/smc slots (vp9dsp_template.c:1969-2569).
+ * Algorithmic bytes per frame: P (write) + r*P (reference reads), r = 1 or 2.
+ */
+#ifndef VP9CUDA_K_INTER_CUH
+#define VP9CUDA_K_INTER_CUH
+
+#include "dev_common.cuh"
+
+namespace vp9 {
+
+__global__ void k_cellmap(const Vp9CudaInterBlock *__restrict__ blk, uint32_t n, int32_t *cellmap,
+                          int cols, int rows)
+{
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n)
+        return;
+    int col = blk[i].col, row = blk[i].row, bs = blk[i].bs;
+    int w = min(bs_w8(bs), cols - col), h = min(bs_h8(bs), rows - row);
+    for (int y = 0; y < h; y++)
+        for (int x = 0; x < w; x++)
+            cellmap[(row + y) * cols + col + x] = (int32_t)i;
+}
+
+/* horizontal stage for one sample */
+template <class P>
+__device__ __forceinline__ int mc_hrow(const RefPlane<P> &r, int x, int y, int filter, int phx, int bpp)
+{
+    if (phx == 0)
+        return r.at(x, y);
+    int s[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++)
+        s[i] = r.at(x + i - 3, y);
+    return filt8(s, filter, phx, bpp);
+}
+
+/* NR vertically adjacent outputs at integer reference position (x, y), phases (phx, phy) */
+template <class P, int NR>
+__device__ __forceinline__ void mc_strip(const RefPlane<P> &r, int x, int y, int phx, int phy,
+                                         int filter, int bpp, int *out)
+{
+    if (phy == 0) {
+#pragma unroll
+        for (int j = 0; j < NR; j++)
+            out[j] = mc_hrow(r, x, y + j, filter, phx, bpp);
+    } else {
+        int hbuf[NR + 7];
+#pragma unroll
+        for (int j = 0; j < NR + 7; j++)
+            hbuf[j] = mc_hrow(r, x, y - 3 + j, filter, phx, bpp);
+#pragma unroll
+        for (int j = 0; j < NR; j++)
+            out[j] = filt8(&hbuf[j], filter, phy, bpp);
+    }
+}
+
+/* Prediction of pixel (X, Y) of plane pl from reference i of block b: the general path.
+ * Works out which prediction call of inter_pred() the pixel belongs to. */
+template <class P>
+__device__ int inter_px_general(const FrameDesc &f, const Vp9CudaInterBlock &b, int i, int pl, int X, int Y)
+{
+    const int ch = pl > 0;
+    const int sub8 = b.bs > 9;
+    int ox0, oy0, px = 0, py = 0, pw, ph, mvx, mvy;
+    if (sub8) {
+        if (!ch) {
+            int k = ((Y >> 2) & 1) * 2 + ((X >> 2) & 1);
+            px = 4 * (k & 1); py = 4 * (k >> 1); pw = ph = 8;
+            ox0 = b.col * 8 + px; oy0 = b.row * 8 + py;
+            mvx = b.mv[k][i][0]; mvy = b.mv[k][i][1];
+        } else {
+            pw = ph = 4;
+            ox0 = b.col * 4; oy0 = b.row * 4;
+            mvx = rounded_div(b.mv[0][i][0] + b.mv[1][i][0] + b.mv[2][i][0] + b.mv[3][i][0], 4);
+            mvy = rounded_div(b.mv[0][i][1] + b.mv[1][i][1] + b.mv[2][i][1] + b.mv[3][i][1], 4);
+        }
+    } else {
+        pw = (bs_w8(b.bs) * 8) >> ch; ph = (bs_h8(b.bs) * 8) >> ch;
+        ox0 = (b.col * 8) >> ch; oy0 = (b.row * 8) >> ch;
+        mvx = b.mv[0][i][0]; mvy = b.mv[0][i][1];
+    }
+    const int ri = b.ref[i];
+    const SurfDesc &rs = f.ref[ri];
+    RefPlane<P> rp;
+    rp.pix = (const P *)rs.pl[pl]; rp.stride = rs.stride[pl];
+    rp.w = (rs.w + ch) >> ch; rp.h = (rs.h + ch) >> ch;
+    McPos pos;
+    if (f.mvscale[ri][0])
+        pos = mc_pos_scaled(ox0, oy0, mvx, mvy, ch, px, py, pw, ph, f.cols, f.rows, f.mvscale[ri][0],
+                            f.mvscale[ri][1], f.mvstep[ri][0], f.mvstep[ri][1]);
+    else
+        pos = mc_pos_unscaled(ox0, oy0, mvx, mvy, ch);
+    return mc_pixel(rp, pos, X - ox0, Y - oy0, b.filter, f.bpp);
+}
+
+/* One strip of NR rows at column X starting at row Y of plane pl, all inside one 8x8 cell
+ * (NR = 8 luma, 4 chroma) and, for sub-8x8 luma, inside one 4x4 (NR = 4). */
+template <class P, int NR>
+__device__ __forceinline__ void inter_strip(const FrameDesc &f, const Vp9CudaInterBlock &b, int pl, int X,
+                                            int Y, int *out)
+{
+    const int ch = pl > 0;
+    const int sub8 = b.bs > 9;
+    const int nref = b.comp ? 2 : 1;
+    int acc[NR];
+    for (int i = 0; i < nref; i++) {
+        const int ri = b.ref[i];
+        int v[NR];
+        if (f.mvscale[ri][0]) {
+            for (int j = 0; j < NR; j++)
+                v[j] = inter_px_general<P>(f, b, i, pl, X, Y + j);
+        } else {
+            int mvx, mvy;
+            if (sub8) {
+                if (!ch) {
+                    int k = ((Y >> 2) & 1) * 2 + ((X >> 2) & 1);
+                    mvx = b.mv[k][i][0]; mvy = b.mv[k][i][1];
+                } else {
+                    mvx = rounded_div(b.mv[0][i][0] + b.mv[1][i][0] + b.mv[2][i][0] + b.mv[3][i][0], 4);
+                    mvy = rounded_div(b.mv[0][i][1] + b.mv[1][i][1] + b.mv[2][i][1] + b.mv[3][i][1], 4);
+                }
+            } else {
+                mvx = b.mv[0][i][0]; mvy = b.mv[0][i][1];
+            }
+            const SurfDesc &rs = f.ref[ri];
+            RefPlane<P> rp;
+            rp.pix = (const P *)rs.pl[pl]; rp.stride = rs.stride[pl];
+            rp.w = (rs.w + ch) >> ch; rp.h = (rs.h + ch) >> ch;
+            McPos pos = mc_pos_unscaled(X, Y, mvx, mvy, ch);
+            mc_strip<P, NR>(rp, pos.x0, pos.y0, pos.fx, pos.fy, b.filter, f.bpp, v);
+        }
+        if (i == 0) {
+#pragma unroll
+            for (int j = 0; j < NR; j++) acc[j] = v[j];
+        } else {
+#pragma unroll
+            for (int j = 0; j < NR; j++) acc[j] = (acc[j] + v[j] + 1) >> 1;
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < NR; j++) out[j] = acc[j];
+}
+
+template <class P>
+__global__ void __launch_bounds__(256) k_inter(const __grid_constant__ FrameDesc f)
+{
+    const int tid = threadIdx.x;
+    const int X0 = blockIdx.x * 64, Y0 = blockIdx.y * 32;
+    /* ---- luma: strip = column tid&63, rows (tid>>6)*8 .. +7 ---- */
+    {
+        const int X = X0 + (tid & 63), Y = Y0 + (tid >> 6) * 8;
+        if (X < f.cols * 8 && Y < f.rows * 8) {
+            int ci = f.cellmap[(Y >> 3) * f.cols + (X >> 3)];
+            if (ci >= 0) {
+                const Vp9CudaInterBlock &b = f.blk[ci];
+                P *dst = (P *)f.cur.pl[0] + (size_t)Y * f.cur.stride[0] + X;
+                int out[8];
+                if (b.bs > 9) {
+                    inter_strip<P, 4>(f, b, 0, X, Y, out);
+                    inter_strip<P, 4>(f, b, 0, X, Y + 4, out + 4);
+                } else {
+                    inter_strip<P, 8>(f, b, 0, X, Y, out);
+                }
+#pragma unroll
+                for (int j = 0; j < 8; j++)
+                    dst[(size_t)j * f.cur.stride[0]] = (P)out[j];
+            }
+        }
+    }
+    /* ---- chroma: plane 1 + (tid>>7), strip = column tid&31, rows ((tid>>5)&3)*4 .. +3 ---- */
+    {
+        const int pl = 1 + (tid >> 7);
+        const int X = (X0 >> 1) + (tid & 31), Y = (Y0 >> 1) + ((tid >> 5) & 3) * 4;
+        if (X < f.cols * 4 && Y < f.rows * 4) {
+            int ci = f.cellmap[(Y >> 2) * f.cols + (X >> 2)];
+            if (ci >= 0) {
+                const Vp9CudaInterBlock &b = f.blk[ci];
+                P *dst = (P *)f.cur.pl[pl] + (size_t)Y * f.cur.stride[pl] + X;
+                int out[4];
+                inter_strip<P, 4>(f, b, pl, X, Y, out);
+#pragma unroll
+                for (int j = 0; j < 4; j++)
+                    dst[(size_t)j * f.cur.stride[pl]] = (P)out[j];
+            }
+        }
+    }
+}
+
+} /* namespace vp9 */
+#endif

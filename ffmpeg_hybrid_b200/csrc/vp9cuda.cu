@@ -1,0 +1,991 @@
+/*
+ * vp9cuda.cu -- libvp9cuda.so: context, HBM frame / reference pool, record upload, kernel
+ * sequencing and the C ABI of include/vp9cuda.h.
+ *
+ * Frame pipeline on the context's stream (all asynchronous to the host):
+ *   H2D records -> k_cellmap -> k_inter (K2) -> k_itx x4 (K1) -> k_intra_sched + k_intra (K3)
+ *   -> k_lf (K4) -> reference-slot refresh -> optional D2H of the visible crop.
+ * The order is exact because nothing in reconstruction reads post-loop-filter pixels of the
+ * current frame (vp9.c:1404-1416) and intra blocks read their neighbours after those got
+ * their residual (vp9recon.c:109-120).
+ *
+ * There is no CPU implementation of anything in here: without a CUDA device every entry point
+ * fails with -ENODEV.
+ */
+#include <cuda_runtime.h>
+
+#include <errno.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <mutex>
+#include <vector>
+
+#include "vp9cuda.h"
+#include "dev_common.cuh"
+#include "k_inter.cuh"
+#include "k_itx.cuh"
+#include "k_intra.cuh"
+#include "k_lf.cuh"
+
+using namespace vp9;
+
+#define CK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { \
+    fprintf(stderr, "vp9cuda: %s failed at %s:%d: %s\n", #call, __FILE__, __LINE__, cudaGetErrorString(e_)); \
+    return -EIO; } } while (0)
+
+namespace {
+
+struct Surface {
+    void *pl[3] = { nullptr, nullptr, nullptr };
+    int stride[3] = { 0, 0, 0 };       /* pixels */
+    int w = 0, h = 0, bpp = 0, aw = 0, ah = 0;
+    int refs = 0;                      /* reference slots + "current" holding this surface */
+};
+
+/* growable device buffer */
+struct DBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+    int reserve(size_t n)
+    {
+        if (n <= cap)
+            return 0;
+        if (p)
+            cudaFree(p);
+        p = nullptr;
+        cap = 0;
+        size_t want = n + n / 4 + 256;
+        if (cudaMalloc(&p, want) != cudaSuccess) {
+            fprintf(stderr, "vp9cuda: cudaMalloc(%zu) failed\n", want);
+            return -ENOMEM;
+        }
+        cap = want;
+        return 0;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+
+/* growable pinned host buffer */
+struct HBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+    int reserve(size_t n)
+    {
+        if (n <= cap)
+            return 0;
+        if (p)
+            cudaFreeHost(p);
+        p = nullptr;
+        cap = 0;
+        if (cudaMallocHost(&p, n) != cudaSuccess)
+            return -ENOMEM;
+        cap = n;
+        return 0;
+    }
+    void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+};
+
+/* device-resident records + scratch of one frame */
+struct DevRecords {
+    DBuf blk, tx[4], itx, coef, sb_index, lf;
+    DBuf cellmap, isched_order, isched_lvl_end, isched_seg, isched_nlvl, progress;
+    Vp9CudaFrameHeader hdr;
+    uint32_t n_blk = 0, n_tx[4] = { 0, 0, 0, 0 }, n_itx = 0;
+    uint32_t itx_lane_base[VP9CUDA_MAX_LANES];
+    bool used = false;
+    void release()
+    {
+        blk.release(); itx.release(); coef.release(); sb_index.release(); lf.release();
+        for (auto &t : tx) t.release();
+        cellmap.release(); isched_order.release(); isched_lvl_end.release(); isched_seg.release();
+        isched_nlvl.release(); progress.release();
+    }
+};
+
+/* pinned rings of one frame in flight (begin_frame / tile_ring / submit_tile / finish_frame) */
+struct RingSet {
+    HBuf mem[VP9CUDA_MAX_LANES];           /* one slab per lane */
+    Vp9CudaLaneRing ring[VP9CUDA_MAX_LANES];
+    Vp9CudaLaneCounts counts[VP9CUDA_MAX_LANES];
+    HBuf sb_index, lf;
+    Vp9CudaFrameHeader hdr;
+    uint32_t frame_id = 0;
+    uint32_t n_sb = 0;
+    cudaEvent_t consumed = nullptr;        /* H2D of this set finished */
+    bool busy = false;
+    DevRecords dev;
+};
+
+struct KStat {
+    const char *name;
+    double ms = 0;
+    uint64_t launches = 0, bytes = 0;
+};
+enum { KS_CELLMAP, KS_INTER, KS_ITX, KS_ISCHED, KS_INTRA, KS_LF, KS_H2D, KS_D2H, KS_N };
+
+} /* namespace */
+
+struct Vp9CudaCtx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    std::vector<Surface *> pool;           /* every surface ever allocated */
+    Surface *ref[8] = { nullptr };
+    Surface *last = nullptr;               /* most recently reconstructed frame */
+    std::vector<RingSet *> rings;
+    std::vector<DevRecords *> staged;
+    uint32_t next_frame_id = 1;
+    uint64_t next_ticket = 1;
+    std::vector<cudaEvent_t> ticket_ev;    /* ring of events, ticket % size */
+    std::mutex mu;
+    KStat ks[KS_N];
+    bool timing = false;
+    cudaEvent_t tev[2] = { nullptr, nullptr };
+    DBuf sum_buf;
+};
+
+static Surface *surface_get(Vp9CudaCtx *c, int w, int h, int bpp)
+{
+    for (Surface *s : c->pool)
+        if (!s->refs && s->w == w && s->h == h && s->bpp == bpp) {
+            s->refs = 1;
+            return s;
+        }
+    /* drop unused surfaces of other sizes before growing */
+    for (size_t i = 0; i < c->pool.size();) {
+        Surface *s = c->pool[i];
+        if (!s->refs && (s->w != w || s->h != h || s->bpp != bpp)) {
+            for (int p = 0; p < 3; p++) cudaFree(s->pl[p]);
+            delete s;
+            c->pool.erase(c->pool.begin() + i);
+        } else {
+            i++;
+        }
+    }
+    Surface *s = new Surface;
+    s->w = w; s->h = h; s->bpp = bpp;
+    s->aw = (w + 63) & ~63; s->ah = (h + 63) & ~63;
+    const int bytes = bpp > 8 ? 2 : 1;
+    for (int p = 0; p < 3; p++) {
+        int sh = p ? 1 : 0;
+        s->stride[p] = s->aw >> sh;
+        size_t n = (size_t)s->stride[p] * (s->ah >> sh) * bytes;
+        if (cudaMalloc(&s->pl[p], n) != cudaSuccess) {
+            for (int q = 0; q < p; q++) cudaFree(s->pl[q]);
+            delete s;
+            return nullptr;
+        }
+        cudaMemsetAsync(s->pl[p], 0, n, c->stream);
+    }
+    s->refs = 1;
+    c->pool.push_back(s);
+    return s;
+}
+
+static void surface_unref(Surface *s)
+{
+    if (s && s->refs > 0)
+        s->refs--;
+}
+
+static SurfDesc surf_desc(const Surface *s)
+{
+    SurfDesc d;
+    memset(&d, 0, sizeof(d));
+    if (s) {
+        for (int p = 0; p < 3; p++) { d.pl[p] = s->pl[p]; d.stride[p] = s->stride[p]; }
+        d.w = s->w; d.h = s->h;
+    }
+    return d;
+}
+
+static void kstat_begin(Vp9CudaCtx *c)
+{
+    if (c->timing)
+        cudaEventRecord(c->tev[0], c->stream);
+}
+static void kstat_end(Vp9CudaCtx *c, int k, uint64_t launches, uint64_t bytes)
+{
+    c->ks[k].launches += launches;
+    c->ks[k].bytes += bytes;
+    if (c->timing) {
+        float ms = 0;
+        cudaEventRecord(c->tev[1], c->stream);
+        cudaEventSynchronize(c->tev[1]);
+        cudaEventElapsedTime(&ms, c->tev[0], c->tev[1]);
+        c->ks[k].ms += ms;
+    }
+}
+
+/* ------------------------------------------------------------------------------------------
+ * record upload: host (pinned or pageable) -> DevRecords, lanes concatenated per record type,
+ * coefficients placed at their lane's coef_base
+ * ---------------------------------------------------------------------------------------- */
+static int upload_records(Vp9CudaCtx *c, DevRecords &d, const Vp9CudaFrameHeader *hdr,
+                          const Vp9CudaFrameRecords *recs)
+{
+    const int cb = hdr->bpp > 8 ? 4 : 2;
+    const int nl = hdr->n_lanes;
+    if (nl < 1 || nl > VP9CUDA_MAX_LANES)
+        return -EINVAL;
+    const uint32_t n_sb = ((hdr->w + 63) >> 6) * ((hdr->h + 63) >> 6);
+    const int cols = (hdr->w + 7) >> 3, rows = (hdr->h + 7) >> 3, sb_rows = (hdr->h + 63) >> 6;
+    uint64_t n_blk = 0, n_tx[4] = { 0, 0, 0, 0 }, n_itx = 0, coef_extent = 0;
+    for (int l = 0; l < nl; l++) {
+        const Vp9CudaLaneCounts &n = recs->counts[l];
+        n_blk += n.blk; n_itx += n.itx;
+        for (int t = 0; t < 4; t++) n_tx[t] += n.tx[t];
+        uint64_t e = (uint64_t)recs->lanes[l].coef_base + n.coef;
+        if (n.coef && e > coef_extent) coef_extent = e;
+    }
+    if (coef_extent > 0xffffffffull)
+        return -EINVAL;
+    int r = 0;
+    r |= d.blk.reserve(n_blk * sizeof(Vp9CudaInterBlock));
+    for (int t = 0; t < 4; t++) r |= d.tx[t].reserve(n_tx[t] * sizeof(Vp9CudaTx));
+    r |= d.itx.reserve(n_itx * sizeof(Vp9CudaIntraTx));
+    r |= d.coef.reserve(coef_extent * cb);
+    r |= d.sb_index.reserve(n_sb * sizeof(Vp9CudaSbIndex));
+    r |= d.lf.reserve(n_sb * sizeof(Vp9CudaLoopFilterSb));
+    r |= d.cellmap.reserve((size_t)cols * rows * 4);
+    r |= d.isched_order.reserve(n_itx * 2);
+    r |= d.isched_lvl_end.reserve((size_t)n_sb * 3 * ISCHED_MAX_LVL * 2);
+    r |= d.isched_seg.reserve((size_t)n_sb * 3 * 4);
+    r |= d.isched_nlvl.reserve((size_t)n_sb * 3);
+    r |= d.progress.reserve((size_t)6 * sb_rows * 4);
+    if (r)
+        return -ENOMEM;
+    kstat_begin(c);
+    uint64_t o_blk = 0, o_tx[4] = { 0, 0, 0, 0 }, o_itx = 0, bytes = 0;
+    for (int l = 0; l < nl; l++) {
+        const Vp9CudaLaneCounts &n = recs->counts[l];
+        const Vp9CudaLaneRing &g = recs->lanes[l];
+        d.itx_lane_base[l] = (uint32_t)o_itx;
+        if (n.blk)
+            CK(cudaMemcpyAsync((char *)d.blk.p + o_blk * sizeof(Vp9CudaInterBlock), g.blk,
+                               n.blk * sizeof(Vp9CudaInterBlock), cudaMemcpyHostToDevice, c->stream));
+        for (int t = 0; t < 4; t++)
+            if (n.tx[t])
+                CK(cudaMemcpyAsync((char *)d.tx[t].p + o_tx[t] * sizeof(Vp9CudaTx), g.tx[t],
+                                   n.tx[t] * sizeof(Vp9CudaTx), cudaMemcpyHostToDevice, c->stream));
+        if (n.itx)
+            CK(cudaMemcpyAsync((char *)d.itx.p + o_itx * sizeof(Vp9CudaIntraTx), g.itx,
+                               n.itx * sizeof(Vp9CudaIntraTx), cudaMemcpyHostToDevice, c->stream));
+        if (n.coef)
+            CK(cudaMemcpyAsync((char *)d.coef.p + (size_t)g.coef_base * cb, g.coef, (size_t)n.coef * cb,
+                               cudaMemcpyHostToDevice, c->stream));
+        bytes += n.blk * sizeof(Vp9CudaInterBlock) + n.itx * sizeof(Vp9CudaIntraTx) + (uint64_t)n.coef * cb;
+        for (int t = 0; t < 4; t++) bytes += n.tx[t] * sizeof(Vp9CudaTx);
+        o_blk += n.blk; o_itx += n.itx;
+        for (int t = 0; t < 4; t++) o_tx[t] += n.tx[t];
+    }
+    CK(cudaMemcpyAsync(d.sb_index.p, recs->sb_index, n_sb * sizeof(Vp9CudaSbIndex), cudaMemcpyHostToDevice, c->stream));
+    CK(cudaMemcpyAsync(d.lf.p, recs->lf, n_sb * sizeof(Vp9CudaLoopFilterSb), cudaMemcpyHostToDevice, c->stream));
+    bytes += n_sb * (sizeof(Vp9CudaSbIndex) + sizeof(Vp9CudaLoopFilterSb));
+    kstat_end(c, KS_H2D, 0, bytes);
+    d.hdr = *hdr;
+    d.n_blk = (uint32_t)n_blk; d.n_itx = (uint32_t)n_itx;
+    for (int t = 0; t < 4; t++) d.n_tx[t] = (uint32_t)n_tx[t];
+    d.used = true;
+    return 0;
+}
+
+/* ------------------------------------------------------------------------------------------
+ * reconstruction of one frame from device-resident records
+ * ---------------------------------------------------------------------------------------- */
+template <class P, bool HBD>
+static int launch_frame(Vp9CudaCtx *c, const FrameDesc &f, const DevRecords &d)
+{
+    cudaStream_t s = c->stream;
+    const uint64_t P_bytes = (uint64_t)f.w * f.h * 3 / 2 * sizeof(P);
+    if (f.n_blk) {
+        kstat_begin(c);
+        CK(cudaMemsetAsync(f.cellmap, 0xff, (size_t)f.cols * f.rows * 4, s));
+        k_cellmap<<<(f.n_blk + 255) / 256, 256, 0, s>>>(f.blk, f.n_blk, f.cellmap, f.cols, f.rows);
+        kstat_end(c, KS_CELLMAP, 1, (uint64_t)f.n_blk * sizeof(Vp9CudaInterBlock) + (uint64_t)f.cols * f.rows * 4);
+        kstat_begin(c);
+        dim3 grid((f.cols * 8 + 63) / 64, (f.rows * 8 + 31) / 32);
+        k_inter<P><<<grid, 256, 0, s>>>(f);
+        kstat_end(c, KS_INTER, 1, 2 * P_bytes);
+    }
+    kstat_begin(c);
+    uint64_t itx_launches = 0, itx_bytes = 0;
+    if (f.n_tx[0]) { k_itx<P, HBD, 4><<<(f.n_tx[0] + 31) / 32, 128, 0, s>>>(f); itx_launches++; }
+    if (f.n_tx[1]) { k_itx<P, HBD, 8><<<(f.n_tx[1] + 15) / 16, 128, 0, s>>>(f); itx_launches++; }
+    if (f.n_tx[2]) { k_itx<P, HBD, 16><<<(f.n_tx[2] + 7) / 8, 128, 0, s>>>(f); itx_launches++; }
+    if (f.n_tx[3]) { k_itx<P, HBD, 32><<<(f.n_tx[3] + 3) / 4, 128, 0, s>>>(f); itx_launches++; }
+    for (int t = 0; t < 4; t++)
+        itx_bytes += (uint64_t)f.n_tx[t] * (16u << (2 * t)) * ((HBD ? 4 : 2) + 2 * sizeof(P));
+    if (itx_launches)
+        kstat_end(c, KS_ITX, itx_launches, itx_bytes);
+    if (f.n_itx) {
+        kstat_begin(c);
+        const int n = f.sb_cols * f.sb_rows * 3;
+        k_intra_sched<<<(n + 63) / 64, 64, 0, s>>>(f);
+        kstat_end(c, KS_ISCHED, 1, (uint64_t)f.n_itx * sizeof(Vp9CudaIntraTx));
+        kstat_begin(c);
+        CK(cudaMemsetAsync(f.progress, 0, (size_t)3 * f.sb_rows * 4, s));
+        k_intra<P, HBD><<<3 * f.sb_rows, INTRA_WARPS * 32, 0, s>>>(f);
+        kstat_end(c, KS_INTRA, 1, P_bytes);
+    }
+    if (f.lf_level) {
+        kstat_begin(c);
+        CK(cudaMemsetAsync(f.progress + 3 * f.sb_rows, 0, (size_t)3 * f.sb_rows * 4, s));
+        k_lf<P><<<3 * f.sb_rows, LF_THREADS, 0, s>>>(f);
+        kstat_end(c, KS_LF, 1, 2 * P_bytes);
+    }
+    CK(cudaGetLastError());
+    (void)d;
+    return 0;
+}
+
+static int copy_out(Vp9CudaCtx *c, const Surface *s, uint8_t *const out_planes[3], const ptrdiff_t out_strides[3])
+{
+    const int bytes = s->bpp > 8 ? 2 : 1;
+    uint64_t total = 0;
+    kstat_begin(c);
+    for (int p = 0; p < 3; p++) {
+        int sh = p ? 1 : 0;
+        int w = (s->w + sh) >> sh, h = (s->h + sh) >> sh;
+        CK(cudaMemcpy2DAsync(out_planes[p], out_strides[p], s->pl[p], (size_t)s->stride[p] * bytes,
+                             (size_t)w * bytes, h, cudaMemcpyDeviceToHost, c->stream));
+        total += (uint64_t)w * h * bytes;
+    }
+    kstat_end(c, KS_D2H, 0, total);
+    return 0;
+}
+
+static int make_ticket(Vp9CudaCtx *c, uint64_t *ticket)
+{
+    uint64_t t = c->next_ticket++;
+    cudaEvent_t ev = c->ticket_ev[t % c->ticket_ev.size()];
+    CK(cudaEventRecord(ev, c->stream));
+    if (ticket)
+        *ticket = t;
+    return 0;
+}
+
+static int reconstruct(Vp9CudaCtx *c, DevRecords &d, uint8_t *const out_planes[3],
+                       const ptrdiff_t out_strides[3], uint64_t *ticket)
+{
+    const Vp9CudaFrameHeader &h = d.hdr;
+    if (h.ss_h != 1 || h.ss_v != 1 || (h.bpp != 8 && h.bpp != 10 && h.bpp != 12) || !h.w || !h.h)
+        return -EINVAL;
+    Surface *cur = surface_get(c, h.w, h.h, h.bpp);
+    if (!cur)
+        return -ENOMEM;
+    FrameDesc f;
+    memset(&f, 0, sizeof(f));
+    f.cur = surf_desc(cur);
+    for (int i = 0; i < 3; i++) {
+        Surface *r = c->ref[h.ref_slot[i] & 7];
+        if (d.n_blk && (!r || r->bpp != h.bpp)) {
+            surface_unref(cur);
+            return -EINVAL;
+        }
+        f.ref[i] = surf_desc(r);
+        f.mvscale[i][0] = h.mvscale[i][0]; f.mvscale[i][1] = h.mvscale[i][1];
+        f.mvstep[i][0] = h.mvstep[i][0];   f.mvstep[i][1] = h.mvstep[i][1];
+    }
+    f.w = h.w; f.h = h.h; f.bpp = h.bpp;
+    f.cols = (h.w + 7) >> 3; f.rows = (h.h + 7) >> 3;
+    f.sb_cols = (h.w + 63) >> 6; f.sb_rows = (h.h + 63) >> 6;
+    f.lossless = h.lossless; f.lf_level = h.lf_level;
+    f.blk = (const Vp9CudaInterBlock *)d.blk.p; f.n_blk = d.n_blk;
+    for (int t = 0; t < 4; t++) { f.tx[t] = (const Vp9CudaTx *)d.tx[t].p; f.n_tx[t] = d.n_tx[t]; }
+    f.itx = (const Vp9CudaIntraTx *)d.itx.p; f.n_itx = d.n_itx;
+    f.coef = d.coef.p;
+    f.sb_index = (const Vp9CudaSbIndex *)d.sb_index.p;
+    f.lf = (const Vp9CudaLoopFilterSb *)d.lf.p;
+    memcpy(f.itx_lane_base, d.itx_lane_base, sizeof(f.itx_lane_base));
+    f.cellmap = (int32_t *)d.cellmap.p;
+    f.isched_order = (uint16_t *)d.isched_order.p;
+    f.isched_lvl_end = (uint16_t *)d.isched_lvl_end.p;
+    f.isched_seg = (uint32_t *)d.isched_seg.p;
+    f.isched_nlvl = (uint8_t *)d.isched_nlvl.p;
+    f.progress = (int *)d.progress.p;
+    memcpy(f.lim_lut, h.lim_lut, 64);
+    memcpy(f.mblim_lut, h.mblim_lut, 64);
+
+    int r = h.bpp > 8 ? launch_frame<uint16_t, true>(c, f, d) : launch_frame<uint8_t, false>(c, f, d);
+    if (r < 0) {
+        surface_unref(cur);
+        return r;
+    }
+    /* reference refresh (vp9.c:1687-1692, 1848-1851) */
+    for (int i = 0; i < 8; i++)
+        if (h.refreshrefmask >> i & 1) {
+            surface_unref(c->ref[i]);
+            c->ref[i] = cur;
+            cur->refs++;
+        }
+    surface_unref(c->last);
+    c->last = cur;             /* keeps the "current" hold until the next frame */
+    if (out_planes && out_planes[0]) {
+        r = copy_out(c, cur, out_planes, out_strides);
+        if (r < 0)
+            return r;
+    }
+    return make_ticket(c, ticket);
+}
+
+/* ------------------------------------------------------------------------------------------
+ * C ABI
+ * ---------------------------------------------------------------------------------------- */
+static const char *const ks_names[KS_N] = { "cellmap", "inter_pred", "itxfm_add", "intra_sched",
+                                            "intra_wavefront", "loop_filter", "h2d_records", "d2h_frame" };
+
+extern "C" const char *vp9cuda_version(void)
+{
+    return "vp9cuda 0.1 (sm_100a) abi " "1";
+}
+
+extern "C" int vp9cuda_create(Vp9CudaCtx **out, int device, int max_w, int max_h, int max_bpp,
+                              int frames_in_flight)
+{
+    (void)max_w; (void)max_h; (void)max_bpp;
+    int n = 0;
+    if (!out)
+        return -EINVAL;
+    *out = nullptr;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n <= 0) {
+        fprintf(stderr, "vp9cuda: no CUDA device; this back end has no CPU path\n");
+        return -ENODEV;
+    }
+    if (device < 0 || device >= n)
+        return -ENODEV;
+    CK(cudaSetDevice(device));
+    Vp9CudaCtx *c = new Vp9CudaCtx;
+    c->device = device;
+    CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    c->ticket_ev.resize(256);
+    for (auto &e : c->ticket_ev)
+        CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    CK(cudaEventCreate(&c->tev[0]));
+    CK(cudaEventCreate(&c->tev[1]));
+    if (frames_in_flight < 1) frames_in_flight = 1;
+    if (frames_in_flight > 16) frames_in_flight = 16;
+    for (int i = 0; i < frames_in_flight; i++) {
+        RingSet *r = new RingSet;
+        memset(r->ring, 0, sizeof(r->ring));
+        memset(r->counts, 0, sizeof(r->counts));
+        CK(cudaEventCreateWithFlags(&r->consumed, cudaEventDisableTiming));
+        c->rings.push_back(r);
+    }
+    for (int k = 0; k < KS_N; k++)
+        c->ks[k].name = ks_names[k];
+    *out = c;
+    return 0;
+}
+
+extern "C" int vp9cuda_flush(Vp9CudaCtx *c)
+{
+    if (!c)
+        return -EINVAL;
+    cudaSetDevice(c->device);
+    CK(cudaStreamSynchronize(c->stream));
+    for (int i = 0; i < 8; i++) {
+        surface_unref(c->ref[i]);
+        c->ref[i] = nullptr;
+    }
+    surface_unref(c->last);
+    c->last = nullptr;
+    for (RingSet *r : c->rings)
+        r->busy = false;
+    return 0;
+}
+
+extern "C" void vp9cuda_destroy(Vp9CudaCtx *c)
+{
+    if (!c)
+        return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    for (Surface *s : c->pool) {
+        for (int p = 0; p < 3; p++) cudaFree(s->pl[p]);
+        delete s;
+    }
+    for (RingSet *r : c->rings) {
+        for (auto &m : r->mem) m.release();
+        r->sb_index.release(); r->lf.release();
+        r->dev.release();
+        cudaEventDestroy(r->consumed);
+        delete r;
+    }
+    for (DevRecords *d : c->staged)
+        if (d) { d->release(); delete d; }
+    for (auto &e : c->ticket_ev) cudaEventDestroy(e);
+    cudaEventDestroy(c->tev[0]);
+    cudaEventDestroy(c->tev[1]);
+    c->sum_buf.release();
+    cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+extern "C" void *vp9cuda_host_alloc(size_t bytes)
+{
+    void *p = nullptr;
+    if (cudaMallocHost(&p, bytes ? bytes : 1) != cudaSuccess)
+        return nullptr;
+    return p;
+}
+
+extern "C" void vp9cuda_host_free(void *p)
+{
+    if (p)
+        cudaFreeHost(p);
+}
+
+static RingSet *ring_of(Vp9CudaCtx *c, uint32_t frame_id)
+{
+    for (RingSet *r : c->rings)
+        if (r->busy && r->frame_id == frame_id)
+            return r;
+    return nullptr;
+}
+
+extern "C" int vp9cuda_begin_frame(Vp9CudaCtx *c, const Vp9CudaFrameHeader *hdr, Vp9CudaFrameRing *ring)
+{
+    if (!c || !hdr || !ring || hdr->n_lanes < 1 || hdr->n_lanes > VP9CUDA_MAX_LANES)
+        return -EINVAL;
+    cudaSetDevice(c->device);
+    std::lock_guard<std::mutex> lk(c->mu);
+    RingSet *r = nullptr;
+    for (RingSet *q : c->rings)
+        if (!q->busy) { r = q; break; }
+    if (!r)
+        return -EBUSY;      /* caller must finish/wait a frame first */
+    /* the previous user's H2D must be over before the producer scribbles on the pinned slab */
+    CK(cudaEventSynchronize(r->consumed));
+    const int cb = hdr->bpp > 8 ? 4 : 2;
+    const uint32_t n_sb = ((hdr->w + 63) >> 6) * ((hdr->h + 63) >> 6);
+    uint32_t coef_base = 0;
+    for (int l = 0; l < hdr->n_lanes; l++) {
+        const size_t sbs = hdr->lane_sbs[l] ? hdr->lane_sbs[l] : 1;
+        Vp9CudaLaneRing &g = r->ring[l];
+        g.blk_cap = (uint32_t)(sbs * 64);
+        g.tx_cap[0] = (uint32_t)(sbs * 384); g.tx_cap[1] = (uint32_t)(sbs * 96);
+        g.tx_cap[2] = (uint32_t)(sbs * 24);  g.tx_cap[3] = (uint32_t)(sbs * 6);
+        g.itx_cap = (uint32_t)(sbs * 384);
+        g.coef_cap = (uint32_t)(sbs * 6144);
+        size_t off = 0, o_blk, o_tx[4], o_itx, o_coef;
+        o_blk = off;  off += (size_t)g.blk_cap * sizeof(Vp9CudaInterBlock);
+        for (int t = 0; t < 4; t++) { o_tx[t] = off; off += (size_t)g.tx_cap[t] * sizeof(Vp9CudaTx); }
+        o_itx = off;  off += (size_t)g.itx_cap * sizeof(Vp9CudaIntraTx);
+        off = (off + 63) & ~(size_t)63;
+        o_coef = off; off += (size_t)g.coef_cap * cb;
+        if (r->mem[l].reserve(off))
+            return -ENOMEM;
+        char *base = (char *)r->mem[l].p;
+        g.blk = (Vp9CudaInterBlock *)(base + o_blk);
+        for (int t = 0; t < 4; t++) g.tx[t] = (Vp9CudaTx *)(base + o_tx[t]);
+        g.itx = (Vp9CudaIntraTx *)(base + o_itx);
+        g.coef = base + o_coef;
+        g.coef_base = coef_base;
+        g.reserved = 0;
+        coef_base += g.coef_cap;
+        memset(&r->counts[l], 0, sizeof(r->counts[l]));
+    }
+    if (r->sb_index.reserve(n_sb * sizeof(Vp9CudaSbIndex)) || r->lf.reserve(n_sb * sizeof(Vp9CudaLoopFilterSb)))
+        return -ENOMEM;
+    memset(r->sb_index.p, 0, n_sb * sizeof(Vp9CudaSbIndex));
+    memset(r->lf.p, 0, n_sb * sizeof(Vp9CudaLoopFilterSb));
+    r->hdr = *hdr;
+    r->n_sb = n_sb;
+    r->frame_id = c->next_frame_id++;
+    r->busy = true;
+    ring->sb_index = (Vp9CudaSbIndex *)r->sb_index.p;
+    ring->lf = (Vp9CudaLoopFilterSb *)r->lf.p;
+    ring->n_sb = n_sb;
+    ring->frame_id = r->frame_id;
+    return 0;
+}
+
+extern "C" int vp9cuda_tile_ring(Vp9CudaCtx *c, uint32_t frame_id, int lane, Vp9CudaLaneRing *ring)
+{
+    if (!c || !ring)
+        return -EINVAL;
+    std::lock_guard<std::mutex> lk(c->mu);
+    RingSet *r = ring_of(c, frame_id);
+    if (!r || lane < 0 || lane >= r->hdr.n_lanes)
+        return -EINVAL;
+    *ring = r->ring[lane];
+    return 0;
+}
+
+extern "C" int vp9cuda_submit_tile(Vp9CudaCtx *c, uint32_t frame_id, int lane, const Vp9CudaLaneCounts *counts)
+{
+    if (!c || !counts)
+        return -EINVAL;
+    std::lock_guard<std::mutex> lk(c->mu);
+    RingSet *r = ring_of(c, frame_id);
+    if (!r || lane < 0 || lane >= r->hdr.n_lanes)
+        return -EINVAL;
+    const Vp9CudaLaneRing &g = r->ring[lane];
+    if (counts->blk > g.blk_cap || counts->itx > g.itx_cap || counts->coef > g.coef_cap)
+        return -EINVAL;
+    for (int t = 0; t < 4; t++)
+        if (counts->tx[t] > g.tx_cap[t])
+            return -EINVAL;
+    r->counts[lane] = *counts;
+    return 0;
+}
+
+extern "C" int vp9cuda_finish_frame(Vp9CudaCtx *c, uint32_t frame_id, uint8_t *const out_planes[3],
+                                    const ptrdiff_t out_strides[3], uint64_t *ticket)
+{
+    if (!c)
+        return -EINVAL;
+    cudaSetDevice(c->device);
+    std::lock_guard<std::mutex> lk(c->mu);
+    RingSet *r = ring_of(c, frame_id);
+    if (!r)
+        return -EINVAL;
+    Vp9CudaFrameRecords recs;
+    recs.lanes = r->ring;
+    recs.counts = r->counts;
+    recs.sb_index = (const Vp9CudaSbIndex *)r->sb_index.p;
+    recs.lf = (const Vp9CudaLoopFilterSb *)r->lf.p;
+    int ret = upload_records(c, r->dev, &r->hdr, &recs);
+    if (ret == 0)
+        CK(cudaEventRecord(r->consumed, c->stream));
+    r->busy = false;
+    if (ret < 0)
+        return ret;
+    return reconstruct(c, r->dev, out_planes, out_strides, ticket);
+}
+
+extern "C" int vp9cuda_wait(Vp9CudaCtx *c, uint64_t ticket)
+{
+    if (!c || !ticket || ticket >= c->next_ticket)
+        return -EINVAL;
+    cudaSetDevice(c->device);
+    if (c->next_ticket - ticket > c->ticket_ev.size()) {
+        CK(cudaStreamSynchronize(c->stream));     /* event slot already recycled: everything older is done */
+        return 0;
+    }
+    CK(cudaEventSynchronize(c->ticket_ev[ticket % c->ticket_ev.size()]));
+    CK(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int vp9cuda_show_existing(Vp9CudaCtx *c, int slot, uint8_t *const out_planes[3],
+                                     const ptrdiff_t out_strides[3], uint64_t *ticket)
+{
+    if (!c || slot < 0 || slot > 7 || !c->ref[slot] || !out_planes)
+        return -EINVAL;
+    cudaSetDevice(c->device);
+    std::lock_guard<std::mutex> lk(c->mu);
+    int r = copy_out(c, c->ref[slot], out_planes, out_strides);
+    return r < 0 ? r : make_ticket(c, ticket);
+}
+
+extern "C" int vp9cuda_decode_frame(Vp9CudaCtx *c, const Vp9CudaFrameHeader *hdr, const Vp9CudaFrameRecords *recs,
+                                    uint8_t *const out_planes[3], const ptrdiff_t out_strides[3], uint64_t *ticket)
+{
+    if (!c || !hdr || !recs)
+        return -EINVAL;
+    cudaSetDevice(c->device);
+    std::lock_guard<std::mutex> lk(c->mu);
+    /* use the device records of ring set (frame_id round robin) as the landing zone */
+    RingSet *r = c->rings[c->next_frame_id++ % c->rings.size()];
+    int ret = upload_records(c, r->dev, hdr, recs);
+    if (ret < 0)
+        return ret;
+    return reconstruct(c, r->dev, out_planes, out_strides, ticket);
+}
+
+extern "C" int vp9cuda_stage_frame(Vp9CudaCtx *c, const Vp9CudaFrameHeader *hdr, const Vp9CudaFrameRecords *recs,
+                                   int *handle)
+{
+    if (!c || !hdr || !recs || !handle)
+        return -EINVAL;
+    cudaSetDevice(c->device);
+    std::lock_guard<std::mutex> lk(c->mu);
+    DevRecords *d = new DevRecords;
+    int ret = upload_records(c, *d, hdr, recs);
+    if (ret < 0) {
+        d->release();
+        delete d;
+        return ret;
+    }
+    CK(cudaStreamSynchronize(c->stream));
+    c->staged.push_back(d);
+    *handle = (int)c->staged.size() - 1;
+    return 0;
+}
+
+extern "C" int vp9cuda_run_staged(Vp9CudaCtx *c, int handle, uint8_t *const out_planes[3],
+                                  const ptrdiff_t out_strides[3], uint64_t *ticket)
+{
+    if (!c || handle < 0 || handle >= (int)c->staged.size() || !c->staged[handle])
+        return -EINVAL;
+    cudaSetDevice(c->device);
+    std::lock_guard<std::mutex> lk(c->mu);
+    return reconstruct(c, *c->staged[handle], out_planes, out_strides, ticket);
+}
+
+extern "C" int vp9cuda_free_staged(Vp9CudaCtx *c, int handle)
+{
+    if (!c || handle < 0 || handle >= (int)c->staged.size() || !c->staged[handle])
+        return -EINVAL;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    c->staged[handle]->release();
+    delete c->staged[handle];
+    c->staged[handle] = nullptr;
+    return 0;
+}
+
+extern "C" int vp9cuda_kernel_stats(Vp9CudaCtx *c, const char **names, double *ms, uint64_t *launches,
+                                    uint64_t *bytes, int cap)
+{
+    if (!c)
+        return -EINVAL;
+    int n = cap < KS_N ? cap : KS_N;
+    for (int k = 0; k < n; k++) {
+        if (names) names[k] = c->ks[k].name;
+        if (ms) ms[k] = c->ks[k].ms;
+        if (launches) launches[k] = c->ks[k].launches;
+        if (bytes) bytes[k] = c->ks[k].bytes;
+    }
+    return n;
+}
+
+extern "C" int vp9cuda_set_option(Vp9CudaCtx *c, const char *key, int value)
+{
+    if (!c || !key)
+        return -EINVAL;
+    if (!strcmp(key, "timing")) {          /* per-stage CUDA-event timing (serialises the stream) */
+        c->timing = value != 0;
+        return 0;
+    }
+    if (!strcmp(key, "reset_stats")) {
+        for (int k = 0; k < KS_N; k++) { c->ks[k].ms = 0; c->ks[k].launches = 0; c->ks[k].bytes = 0; }
+        return 0;
+    }
+    return -EINVAL;
+}
+
+/* ---- checksum of a frame in HBM ----------------------------------------------------------------- */
+template <class P>
+__global__ void k_checksum(const P *pl, int stride, int w, int h, unsigned long long *sum, unsigned salt)
+{
+    unsigned long long acc = 0;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < w * h; i += gridDim.x * blockDim.x) {
+        int x = i % w, y = i / w;
+        unsigned long long v = pl[(size_t)y * stride + x];
+        acc += (v + 1) * (0x9E3779B97F4A7C15ull ^ ((unsigned long long)(i + salt) * 0xD6E8FEB86659FD93ull));
+    }
+    for (int o = 16; o; o >>= 1)
+        acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if ((threadIdx.x & 31) == 0)
+        atomicAdd(sum, acc);
+}
+
+extern "C" int vp9cuda_frame_checksum(Vp9CudaCtx *c, int slot, uint64_t *sum)
+{
+    if (!c || !sum || slot > 7)
+        return -EINVAL;
+    cudaSetDevice(c->device);
+    std::lock_guard<std::mutex> lk(c->mu);
+    Surface *s = slot < 0 ? c->last : c->ref[slot];
+    if (!s)
+        return -EINVAL;
+    if (c->sum_buf.reserve(8))
+        return -ENOMEM;
+    CK(cudaMemsetAsync(c->sum_buf.p, 0, 8, c->stream));
+    for (int p = 0; p < 3; p++) {
+        int sh = p ? 1 : 0, w = (s->w + sh) >> sh, h = (s->h + sh) >> sh;
+        if (s->bpp > 8)
+            k_checksum<uint16_t><<<296, 256, 0, c->stream>>>((const uint16_t *)s->pl[p], s->stride[p], w, h,
+                                                             (unsigned long long *)c->sum_buf.p, p * 0x01000000u);
+        else
+            k_checksum<uint8_t><<<296, 256, 0, c->stream>>>((const uint8_t *)s->pl[p], s->stride[p], w, h,
+                                                            (unsigned long long *)c->sum_buf.p, p * 0x01000000u);
+    }
+    CK(cudaMemcpyAsync(sum, c->sum_buf.p, 8, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+/* ------------------------------------------------------------------------------------------
+ * slot-level entry points (tests): the batched equivalent of one VP9DSPContext slot.
+ * Same device functions as the frame kernels.
+ * ---------------------------------------------------------------------------------------- */
+template <class P, bool HBD>
+__global__ void k_slot_itx(int n, const uint8_t *tx, const uint8_t *txtp, const uint16_t *eob, P *pix,
+                           const typename ItxTypes<HBD>::C *coef, int bpp)
+{
+    typedef typename ItxTypes<HBD>::C C;
+    __shared__ C tmp[4][32 * 33];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int i = blockIdx.x * 4 + warp;
+    if (i >= n)
+        return;
+    GlobalPix<P> g = { pix + (size_t)i * 4096, 64 };
+    const C *cf = coef + (size_t)i * 1024;
+    switch (tx[i]) {
+    case 0: if (lane < 4)  itx_block<HBD, 4>(cf, tmp[warp], lane, txtp[i], eob[i], bpp, g, 0xfu); break;
+    case 1: if (lane < 8)  itx_block<HBD, 8>(cf, tmp[warp], lane, txtp[i], eob[i], bpp, g, 0xffu); break;
+    case 2: if (lane < 16) itx_block<HBD, 16>(cf, tmp[warp], lane, txtp[i], eob[i], bpp, g, 0xffffu); break;
+    default: itx_block<HBD, 32>(cf, tmp[warp], lane, txtp[i], eob[i], bpp, g, 0xffffffffu); break;
+    }
+}
+
+template <class P>
+__global__ void k_slot_intra(int n, const uint8_t *tx, const uint8_t *mode, P *pix, const P *left,
+                             const P *top, int bpp)
+{
+    const int i = blockIdx.x;
+    if (i >= n)
+        return;
+    __shared__ int T[65], L[32];
+    const int N = 4 << tx[i], m = mode[i];
+    const P *tp = top + (size_t)i * 81, *lp = left + (size_t)i * 64;
+    if (threadIdx.x == 0) {
+        T[0] = tp[0];
+        for (int k = 0; k < 2 * N; k++) {
+            int src = k;
+            if (N == 4) src = k;                     /* 4x4 may read top[4..7] */
+            else if (k >= N) src = N - 1;
+            T[1 + k] = tp[1 + src];
+        }
+        for (int y = 0; y < N; y++)
+            L[y] = m == HOR_UP_PRED ? lp[y] : lp[N - 1 - y];
+    }
+    __syncthreads();
+    int dc = intra_dc(m, N, T, L, bpp);
+    for (int k = threadIdx.x; k < N * N; k += blockDim.x)
+        pix[(size_t)i * 4096 + (k / N) * 64 + k % N] = (P)intra_pixel(m, N, k % N, k / N, T, L, dc, bpp);
+}
+
+template <class P>
+__global__ void k_slot_mc(int n, const uint8_t *w, const uint8_t *h, const uint8_t *filter, const uint8_t *avg,
+                          const uint8_t *mx, const uint8_t *my, const uint8_t *dx, const uint8_t *dy, P *pix,
+                          const P *ref, int bpp)
+{
+    const int i = blockIdx.x;
+    if (i >= n)
+        return;
+    RefPlane<P> rp = { ref + (size_t)i * 160 * 160, 160, 160, 160 };
+    McPos pos = { 8, 8, mx[i], my[i], dx[i] ? dx[i] : 16, dy[i] ? dy[i] : 16 };
+    for (int k = threadIdx.x; k < w[i] * h[i]; k += blockDim.x) {
+        int ox = k % w[i], oy = k / w[i];
+        int v = mc_pixel(rp, pos, ox, oy, filter[i], bpp);
+        P *d = pix + (size_t)i * 4096 + oy * 64 + ox;
+        *d = (P)(avg[i] ? (*d + v + 1) >> 1 : v);
+    }
+}
+
+template <class P>
+__global__ void k_slot_lf(int n, const uint8_t *wd, const uint8_t *dir, const uint8_t *len, const int32_t *E,
+                          const int32_t *I, const int32_t *H, P *pix, int bpp)
+{
+    const int i = blockIdx.x;
+    if (i >= n || threadIdx.x >= len[i])
+        return;
+    P *e = pix + (size_t)i * 4096 + 32 * 64 + 32;
+    const int sa = dir[i] ? 1 : 64, sb = dir[i] ? 64 : 1;    /* dir 0: column edge, lines go down */
+    e += threadIdx.x * sa;
+    int px[16];
+    for (int k = 0; k < 16; k++) px[k] = e[(k - 8) * sb];
+    unsigned m = lf_line(px, wd[i], E[i], I[i], H[i], bpp);
+    for (int k = 0; k < 16; k++)
+        if (m >> k & 1) e[(k - 8) * sb] = (P)px[k];
+}
+
+namespace {
+struct SlotBufs {
+    std::vector<void *> d;
+    ~SlotBufs() { for (void *p : d) cudaFree(p); }
+    template <class T> T *up(const T *h, size_t n)
+    {
+        void *p = nullptr;
+        if (cudaMalloc(&p, n * sizeof(T) + 16) != cudaSuccess) return nullptr;
+        d.push_back(p);
+        if (h) cudaMemcpy(p, h, n * sizeof(T), cudaMemcpyHostToDevice);
+        return (T *)p;
+    }
+};
+int slot_dev(int device)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || device < 0 || device >= n)
+        return -ENODEV;
+    return cudaSetDevice(device) == cudaSuccess ? 0 : -EIO;
+}
+}
+
+extern "C" int vp9cuda_slot_itxfm_add(int device, int bpp, int n, const uint8_t *tx, const uint8_t *txtp,
+                                      const uint16_t *eob, void *pix, const void *coef)
+{
+    if (slot_dev(device)) return -ENODEV;
+    SlotBufs b;
+    const int pb = bpp > 8 ? 2 : 1, cb = bpp > 8 ? 4 : 2;
+    uint8_t *dtx = b.up(tx, n), *dtp = b.up(txtp, n);
+    uint16_t *de = b.up(eob, n);
+    uint8_t *dp = b.up((const uint8_t *)pix, (size_t)n * 4096 * pb);
+    uint8_t *dc = b.up((const uint8_t *)coef, (size_t)n * 1024 * cb);
+    if (!dtx || !dtp || !de || !dp || !dc) return -ENOMEM;
+    if (bpp > 8) k_slot_itx<uint16_t, true><<<(n + 3) / 4, 128>>>(n, dtx, dtp, de, (uint16_t *)dp, (const int32_t *)dc, bpp);
+    else         k_slot_itx<uint8_t, false><<<(n + 3) / 4, 128>>>(n, dtx, dtp, de, dp, (const int16_t *)dc, bpp);
+    CK(cudaMemcpy(pix, dp, (size_t)n * 4096 * pb, cudaMemcpyDeviceToHost));
+    CK(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int vp9cuda_slot_intra_pred(int device, int bpp, int n, const uint8_t *tx, const uint8_t *mode,
+                                       void *pix, const void *left, const void *top)
+{
+    if (slot_dev(device)) return -ENODEV;
+    SlotBufs b;
+    const int pb = bpp > 8 ? 2 : 1;
+    uint8_t *dtx = b.up(tx, n), *dm = b.up(mode, n);
+    uint8_t *dp = b.up((const uint8_t *)pix, (size_t)n * 4096 * pb);
+    uint8_t *dl = b.up((const uint8_t *)left, (size_t)n * 64 * pb), *dt = b.up((const uint8_t *)top, (size_t)n * 81 * pb);
+    if (!dtx || !dm || !dp || !dl || !dt) return -ENOMEM;
+    if (bpp > 8) k_slot_intra<uint16_t><<<n, 128>>>(n, dtx, dm, (uint16_t *)dp, (const uint16_t *)dl, (const uint16_t *)dt, bpp);
+    else         k_slot_intra<uint8_t><<<n, 128>>>(n, dtx, dm, dp, dl, dt, bpp);
+    CK(cudaMemcpy(pix, dp, (size_t)n * 4096 * pb, cudaMemcpyDeviceToHost));
+    CK(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int vp9cuda_slot_mc(int device, int bpp, int n, const uint8_t *w, const uint8_t *h, const uint8_t *filter,
+                               const uint8_t *avg, const uint8_t *mx, const uint8_t *my, const uint8_t *dx,
+                               const uint8_t *dy, void *pix, const void *ref)
+{
+    if (slot_dev(device)) return -ENODEV;
+    SlotBufs b;
+    const int pb = bpp > 8 ? 2 : 1;
+    uint8_t *dw = b.up(w, n), *dh = b.up(h, n), *df = b.up(filter, n), *da = b.up(avg, n), *dmx = b.up(mx, n),
+            *dmy = b.up(my, n), *ddx = b.up(dx, n), *ddy = b.up(dy, n);
+    uint8_t *dp = b.up((const uint8_t *)pix, (size_t)n * 4096 * pb);
+    uint8_t *dr = b.up((const uint8_t *)ref, (size_t)n * 160 * 160 * pb);
+    if (!dw || !dh || !df || !da || !dmx || !dmy || !ddx || !ddy || !dp || !dr) return -ENOMEM;
+    if (bpp > 8) k_slot_mc<uint16_t><<<n, 256>>>(n, dw, dh, df, da, dmx, dmy, ddx, ddy, (uint16_t *)dp, (const uint16_t *)dr, bpp);
+    else         k_slot_mc<uint8_t><<<n, 256>>>(n, dw, dh, df, da, dmx, dmy, ddx, ddy, dp, dr, bpp);
+    CK(cudaMemcpy(pix, dp, (size_t)n * 4096 * pb, cudaMemcpyDeviceToHost));
+    CK(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int vp9cuda_slot_loop_filter(int device, int bpp, int n, const uint8_t *wd, const uint8_t *dir,
+                                        const uint8_t *len, const int32_t *E, const int32_t *I, const int32_t *H,
+                                        void *pix)
+{
+    if (slot_dev(device)) return -ENODEV;
+    SlotBufs b;
+    const int pb = bpp > 8 ? 2 : 1;
+    uint8_t *dwd = b.up(wd, n), *dd = b.up(dir, n), *dl = b.up(len, n);
+    int32_t *dE = b.up(E, n), *dI = b.up(I, n), *dH = b.up(H, n);
+    uint8_t *dp = b.up((const uint8_t *)pix, (size_t)n * 4096 * pb);
+    if (!dwd || !dd || !dl || !dE || !dI || !dH || !dp) return -ENOMEM;
+    if (bpp > 8) k_slot_lf<uint16_t><<<n, 32>>>(n, dwd, dd, dl, dE, dI, dH, (uint16_t *)dp, bpp);
+    else         k_slot_lf<uint8_t><<<n, 32>>>(n, dwd, dd, dl, dE, dI, dH, dp, bpp);
+    CK(cudaMemcpy(pix, dp, (size_t)n * 4096 * pb, cudaMemcpyDeviceToHost));
+    CK(cudaGetLastError());
+    return 0;
+}

@@ -26,6 +26,9 @@
 #ifdef __cplusplus
 extern "C" {
 #endif
+#if defined(__GNUC__)
+#pragma GCC visibility push(default)   /* the library is built with -fvisibility=hidden */
+#endif
 
 #define VP9CUDA_ABI_VERSION 1
 #define VP9CUDA_MAX_LANES   64   /* max tile columns, vp9.c:800-810 */
@@ -228,6 +231,9 @@ int  vp9cuda_slot_loop_filter(int device, int bpp, int n, const uint8_t *wd /* 4
                               const int32_t *E, const int32_t *I, const int32_t *H,
                               void *pix /* edge at (32,32) of each tile */);
 
+#if defined(__GNUC__)
+#pragma GCC visibility pop
+#endif
 #ifdef __cplusplus
 }
 #endif
