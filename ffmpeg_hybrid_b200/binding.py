@@ -1,0 +1,230 @@
+"""ctypes binding of libvp9cuda.so (include/vp9cuda.h) + helpers to feed it .v9r record dumps.
+
+This is plumbing for the tests and bench.py: the product is the shared library and the
+libavcodec glue.  Loading fails loudly when the library is missing -- there is no fallback.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from pathlib import Path
+from typing import List, Optional, Sequence
+
+import numpy as np
+
+from . import v9r
+
+LIB_PATH = Path(__file__).resolve().parent / "libvp9cuda.so"
+MAX_LANES = 64
+
+API = [
+    "vp9cuda_version", "vp9cuda_create", "vp9cuda_destroy", "vp9cuda_flush", "vp9cuda_begin_frame",
+    "vp9cuda_tile_ring", "vp9cuda_submit_tile", "vp9cuda_finish_frame", "vp9cuda_wait",
+    "vp9cuda_show_existing", "vp9cuda_host_alloc", "vp9cuda_host_free", "vp9cuda_decode_frame",
+    "vp9cuda_stage_frame", "vp9cuda_run_staged", "vp9cuda_free_staged", "vp9cuda_frame_checksum",
+    "vp9cuda_kernel_stats", "vp9cuda_set_option", "vp9cuda_elapsed_ms", "vp9cuda_slot_itxfm_add",
+    "vp9cuda_slot_intra_pred", "vp9cuda_slot_mc", "vp9cuda_slot_loop_filter",
+]
+
+
+class LaneRing(C.Structure):
+    _fields_ = [("blk", C.c_void_p), ("blk_cap", C.c_uint32),
+                ("tx", C.c_void_p * 4), ("tx_cap", C.c_uint32 * 4),
+                ("itx", C.c_void_p), ("itx_cap", C.c_uint32),
+                ("coef", C.c_void_p), ("coef_cap", C.c_uint32),
+                ("coef_base", C.c_uint32), ("reserved", C.c_uint32)]
+
+
+class LaneCounts(C.Structure):
+    _fields_ = [("blk", C.c_uint32), ("tx", C.c_uint32 * 4), ("itx", C.c_uint32), ("coef", C.c_uint32)]
+
+
+class FrameRecords(C.Structure):
+    _fields_ = [("lanes", C.POINTER(LaneRing)), ("counts", C.POINTER(LaneCounts)),
+                ("sb_index", C.c_void_p), ("lf", C.c_void_p)]
+
+
+_lib = None
+
+
+def load() -> C.CDLL:
+    """dlopen libvp9cuda.so; raises if it is not built (no CPU fallback exists)."""
+    global _lib
+    if _lib is None:
+        if not LIB_PATH.exists():
+            raise RuntimeError(f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'`")
+        lib = C.CDLL(str(LIB_PATH))
+        lib.vp9cuda_version.restype = C.c_char_p
+        lib.vp9cuda_host_alloc.restype = C.c_void_p
+        lib.vp9cuda_host_alloc.argtypes = [C.c_size_t]
+        lib.vp9cuda_host_free.argtypes = [C.c_void_p]
+        lib.vp9cuda_create.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]
+        lib.vp9cuda_destroy.argtypes = [C.c_void_p]
+        lib.vp9cuda_destroy.restype = None
+        lib.vp9cuda_flush.argtypes = [C.c_void_p]
+        lib.vp9cuda_wait.argtypes = [C.c_void_p, C.c_uint64]
+        lib.vp9cuda_decode_frame.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(FrameRecords),
+                                             C.POINTER(C.c_void_p), C.POINTER(C.c_ssize_t), C.POINTER(C.c_uint64)]
+        lib.vp9cuda_stage_frame.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(FrameRecords), C.POINTER(C.c_int)]
+        lib.vp9cuda_run_staged.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_ssize_t),
+                                           C.POINTER(C.c_uint64)]
+        lib.vp9cuda_free_staged.argtypes = [C.c_void_p, C.c_int]
+        lib.vp9cuda_frame_checksum.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_uint64)]
+        lib.vp9cuda_set_option.argtypes = [C.c_void_p, C.c_char_p, C.c_int]
+        lib.vp9cuda_elapsed_ms.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_double)]
+        lib.vp9cuda_kernel_stats.argtypes = [C.c_void_p, C.POINTER(C.c_char_p), C.POINTER(C.c_double),
+                                             C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.c_int]
+        _lib = lib
+    return _lib
+
+
+def check(rc: int, what: str) -> None:
+    if rc < 0:
+        raise RuntimeError(f"{what} failed with {rc}")
+
+
+class HostFrame:
+    """One frame's records in page-locked host memory, laid out like the lane rings."""
+
+    def __init__(self, lib: C.CDLL, fr: v9r.Frame, pinned: bool = True):
+        self.lib = lib
+        self.pinned = pinned
+        self._allocs: List[int] = []
+        self._keep: List[object] = []
+        self.hdr_buf = (C.c_char * v9r.HDR_DTYPE.itemsize).from_buffer_copy(fr.hdr.tobytes())
+        n = len(fr.lanes)
+        self.lanes = (LaneRing * n)()
+        self.counts = (LaneCounts * n)()
+        self.h2d_bytes = fr.record_bytes
+        for i, l in enumerate(fr.lanes):
+            r = self.lanes[i]
+            r.blk = self._put(l.blk)
+            for t in range(4):
+                r.tx[t] = self._put(l.tx[t])
+            r.itx = self._put(l.itx)
+            r.coef = self._put(l.coef)
+            r.coef_base = l.coef_base
+            c = self.counts[i]
+            c.blk = int(l.counts["blk"])
+            for t in range(4):
+                c.tx[t] = int(l.counts["tx"][t])
+            c.itx = int(l.counts["itx"])
+            c.coef = int(l.counts["coef"])
+        self.recs = FrameRecords()
+        self.recs.lanes = C.cast(self.lanes, C.POINTER(LaneRing))
+        self.recs.counts = C.cast(self.counts, C.POINTER(LaneCounts))
+        self.recs.sb_index = self._put(fr.sb_index)
+        self.recs.lf = self._put(fr.lf)
+        self.w, self.h, self.bpp = int(fr.hdr["w"]), int(fr.hdr["h"]), int(fr.hdr["bpp"])
+        self.invisible = bool(fr.hdr["invisible"])
+
+    def _put(self, data: bytes) -> int:
+        n = max(len(data), 16)
+        if self.pinned:
+            p = self.lib.vp9cuda_host_alloc(n)
+            if not p:
+                raise MemoryError("vp9cuda_host_alloc")
+            self._allocs.append(p)
+            C.memmove(p, data, len(data))
+            return p
+        buf = C.create_string_buffer(data, n)
+        self._keep.append(buf)
+        return C.addressof(buf)
+
+    def free(self) -> None:
+        for p in self._allocs:
+            self.lib.vp9cuda_host_free(p)
+        self._allocs = []
+
+
+class OutFrame:
+    """Pinned host planes for the visible crop of one picture (framemd5 layout)."""
+
+    def __init__(self, lib: C.CDLL, w: int, h: int, bpp: int):
+        self.lib = lib
+        bps = 2 if bpp > 8 else 1
+        self.shape = [(h, w), ((h + 1) // 2, (w + 1) // 2), ((h + 1) // 2, (w + 1) // 2)]
+        self.bps = bps
+        self.sizes = [r * c * bps for r, c in self.shape]
+        self.base = lib.vp9cuda_host_alloc(sum(self.sizes))
+        if not self.base:
+            raise MemoryError("vp9cuda_host_alloc")
+        self.planes = (C.c_void_p * 3)()
+        self.strides = (C.c_ssize_t * 3)()
+        off = 0
+        for i in range(3):
+            self.planes[i] = self.base + off
+            self.strides[i] = self.shape[i][1] * bps
+            off += self.sizes[i]
+        self.nbytes = off
+
+    def bytes(self) -> bytes:
+        return C.string_at(self.base, self.nbytes)
+
+    def free(self) -> None:
+        if self.base:
+            self.lib.vp9cuda_host_free(self.base)
+            self.base = None
+
+
+class Context:
+    def __init__(self, device: int = 0, frames_in_flight: int = 2):
+        self.lib = load()
+        self.ctx = C.c_void_p()
+        check(self.lib.vp9cuda_create(C.byref(self.ctx), device, 0, 0, 12, frames_in_flight), "vp9cuda_create")
+
+    def close(self) -> None:
+        if self.ctx:
+            self.lib.vp9cuda_destroy(self.ctx)
+            self.ctx = C.c_void_p()
+
+    def decode(self, hf: HostFrame, out: Optional[OutFrame]) -> int:
+        t = C.c_uint64()
+        planes = out.planes if out is not None else None
+        strides = out.strides if out is not None else None
+        check(self.lib.vp9cuda_decode_frame(self.ctx, C.addressof(hf.hdr_buf), C.byref(hf.recs), planes, strides,
+                                            C.byref(t)), "vp9cuda_decode_frame")
+        return t.value
+
+    def stage(self, hf: HostFrame) -> int:
+        h = C.c_int()
+        check(self.lib.vp9cuda_stage_frame(self.ctx, C.addressof(hf.hdr_buf), C.byref(hf.recs), C.byref(h)),
+              "vp9cuda_stage_frame")
+        return h.value
+
+    def run_staged(self, handle: int, out: Optional[OutFrame] = None) -> int:
+        t = C.c_uint64()
+        planes = out.planes if out is not None else None
+        strides = out.strides if out is not None else None
+        check(self.lib.vp9cuda_run_staged(self.ctx, handle, planes, strides, C.byref(t)), "vp9cuda_run_staged")
+        return t.value
+
+    def wait(self, ticket: int) -> None:
+        check(self.lib.vp9cuda_wait(self.ctx, ticket), "vp9cuda_wait")
+
+    def option(self, key: str, value: int = 1) -> None:
+        check(self.lib.vp9cuda_set_option(self.ctx, key.encode(), value), f"set_option({key})")
+
+    def elapsed_ms(self, a: int, b: int) -> float:
+        ms = C.c_double()
+        check(self.lib.vp9cuda_elapsed_ms(self.ctx, a, b, C.byref(ms)), "vp9cuda_elapsed_ms")
+        return ms.value
+
+    def checksum(self, slot: int = -1) -> int:
+        s = C.c_uint64()
+        check(self.lib.vp9cuda_frame_checksum(self.ctx, slot, C.byref(s)), "vp9cuda_frame_checksum")
+        return s.value
+
+    def kernel_stats(self) -> dict:
+        n = 16
+        names = (C.c_char_p * n)()
+        ms = (C.c_double * n)()
+        launches = (C.c_uint64 * n)()
+        nbytes = (C.c_uint64 * n)()
+        k = self.lib.vp9cuda_kernel_stats(self.ctx, names, ms, launches, nbytes, n)
+        check(k, "vp9cuda_kernel_stats")
+        return {names[i].decode(): {"ms": ms[i], "launches": int(launches[i]), "bytes": int(nbytes[i])}
+                for i in range(k)}
+
+
+def load_stream(lib: C.CDLL, path: Path, pinned: bool = True) -> List[HostFrame]:
+    return [HostFrame(lib, fr, pinned) for fr in v9r.read_v9r(path)]

@@ -141,7 +141,11 @@ struct Vp9CudaCtx {
     std::mutex mu;
     KStat ks[KS_N];
     bool timing = false;
-    cudaEvent_t tev[2] = { nullptr, nullptr };
+    /* per-stage timing without host syncs: event pairs from a pool, resolved in kernel_stats() */
+    std::vector<cudaEvent_t> tpool;        /* 2 events per timed stage */
+    std::vector<int> tstage;               /* stage id of pair i */
+    size_t tused = 0;
+    cudaEvent_t marks[16] = { nullptr };
     DBuf sum_buf;
 };
 
@@ -202,20 +206,39 @@ static SurfDesc surf_desc(const Surface *s)
 
 static void kstat_begin(Vp9CudaCtx *c)
 {
-    if (c->timing)
-        cudaEventRecord(c->tev[0], c->stream);
+    if (!c->timing)
+        return;
+    if (c->tused * 2 + 2 > c->tpool.size()) {
+        cudaEvent_t a = nullptr, b = nullptr;
+        cudaEventCreate(&a);
+        cudaEventCreate(&b);
+        c->tpool.push_back(a);
+        c->tpool.push_back(b);
+        c->tstage.push_back(0);
+    }
+    cudaEventRecord(c->tpool[c->tused * 2], c->stream);
 }
 static void kstat_end(Vp9CudaCtx *c, int k, uint64_t launches, uint64_t bytes)
 {
     c->ks[k].launches += launches;
     c->ks[k].bytes += bytes;
     if (c->timing) {
-        float ms = 0;
-        cudaEventRecord(c->tev[1], c->stream);
-        cudaEventSynchronize(c->tev[1]);
-        cudaEventElapsedTime(&ms, c->tev[0], c->tev[1]);
-        c->ks[k].ms += ms;
+        cudaEventRecord(c->tpool[c->tused * 2 + 1], c->stream);
+        c->tstage[c->tused] = k;
+        c->tused++;
     }
+}
+static void kstat_resolve(Vp9CudaCtx *c)
+{
+    if (!c->tused)
+        return;
+    cudaStreamSynchronize(c->stream);
+    for (size_t i = 0; i < c->tused; i++) {
+        float ms = 0;
+        if (cudaEventElapsedTime(&ms, c->tpool[i * 2], c->tpool[i * 2 + 1]) == cudaSuccess)
+            c->ks[c->tstage[i]].ms += ms;
+    }
+    c->tused = 0;
 }
 
 /* ------------------------------------------------------------------------------------------
@@ -462,8 +485,8 @@ extern "C" int vp9cuda_create(Vp9CudaCtx **out, int device, int max_w, int max_h
     c->ticket_ev.resize(256);
     for (auto &e : c->ticket_ev)
         CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-    CK(cudaEventCreate(&c->tev[0]));
-    CK(cudaEventCreate(&c->tev[1]));
+    for (auto &e : c->marks)
+        CK(cudaEventCreate(&e));
     if (frames_in_flight < 1) frames_in_flight = 1;
     if (frames_in_flight > 16) frames_in_flight = 16;
     for (int i = 0; i < frames_in_flight; i++) {
@@ -516,8 +539,8 @@ extern "C" void vp9cuda_destroy(Vp9CudaCtx *c)
     for (DevRecords *d : c->staged)
         if (d) { d->release(); delete d; }
     for (auto &e : c->ticket_ev) cudaEventDestroy(e);
-    cudaEventDestroy(c->tev[0]);
-    cudaEventDestroy(c->tev[1]);
+    for (auto &e : c->marks) cudaEventDestroy(e);
+    for (auto &e : c->tpool) cudaEventDestroy(e);
     c->sum_buf.release();
     cudaStreamDestroy(c->stream);
     delete c;
@@ -743,6 +766,8 @@ extern "C" int vp9cuda_kernel_stats(Vp9CudaCtx *c, const char **names, double *m
 {
     if (!c)
         return -EINVAL;
+    cudaSetDevice(c->device);
+    kstat_resolve(c);
     int n = cap < KS_N ? cap : KS_N;
     for (int k = 0; k < n; k++) {
         if (names) names[k] = c->ks[k].name;
@@ -757,15 +782,41 @@ extern "C" int vp9cuda_set_option(Vp9CudaCtx *c, const char *key, int value)
 {
     if (!c || !key)
         return -EINVAL;
-    if (!strcmp(key, "timing")) {          /* per-stage CUDA-event timing (serialises the stream) */
+    if (!strcmp(key, "timing")) {          /* per-stage CUDA-event timing on the ctx stream */
         c->timing = value != 0;
         return 0;
     }
+    if (!strcmp(key, "mark")) {            /* record timing mark `value` (0..15) on the ctx stream */
+        if (value < 0 || value > 15)
+            return -EINVAL;
+        cudaSetDevice(c->device);
+        CK(cudaEventRecord(c->marks[value], c->stream));
+        return 0;
+    }
+    if (!strcmp(key, "sync")) {
+        cudaSetDevice(c->device);
+        CK(cudaStreamSynchronize(c->stream));
+        return 0;
+    }
     if (!strcmp(key, "reset_stats")) {
+        cudaSetDevice(c->device);
+        kstat_resolve(c);
         for (int k = 0; k < KS_N; k++) { c->ks[k].ms = 0; c->ks[k].launches = 0; c->ks[k].bytes = 0; }
         return 0;
     }
     return -EINVAL;
+}
+
+extern "C" int vp9cuda_elapsed_ms(Vp9CudaCtx *c, int mark_a, int mark_b, double *ms)
+{
+    if (!c || !ms || mark_a < 0 || mark_a > 15 || mark_b < 0 || mark_b > 15)
+        return -EINVAL;
+    cudaSetDevice(c->device);
+    float f = 0;
+    CK(cudaEventSynchronize(c->marks[mark_b]));
+    CK(cudaEventElapsedTime(&f, c->marks[mark_a], c->marks[mark_b]));
+    *ms = f;
+    return 0;
 }
 
 /* ---- checksum of a frame in HBM ----------------------------------------------------------------- */

@@ -68,11 +68,17 @@ def compare(a: List[str], b: List[str]) -> Tuple[bool, str]:
 
 
 def main(argv: List[str]) -> int:
-    from .configs import small_variants
+    from . import configs
     out = Path(argv[1]) if len(argv) > 1 else Path("/tmp/vp9cuda_parity")
     names = argv[2:]
     bad = 0
-    for n, spec in small_variants().items():
+    specs = dict(configs.small_variants())
+    full = {"c1": configs.c1, "c2": configs.c2, "c3": configs.c3, "c4": configs.c4,
+            "c5": lambda: configs.c5(0)}
+    for n in names:
+        if n in full:
+            specs[n] = full[n]()
+    for n, spec in specs.items():
         if names and n not in names:
             continue
         ivf = write_stream(spec, out / f"{n}.ivf")

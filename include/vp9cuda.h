@@ -211,7 +211,11 @@ int  vp9cuda_frame_checksum(Vp9CudaCtx *ctx, int slot, uint64_t *sum);
  * names/ms/launches hold up to `cap` entries; returns the number filled. */
 int  vp9cuda_kernel_stats(Vp9CudaCtx *ctx, const char **names, double *ms, uint64_t *launches,
                           uint64_t *bytes, int cap);
+/* keys: "timing" 0/1 (per-stage CUDA events on the ctx stream, no host syncs),
+ * "reset_stats", "mark" = record timing mark 0..15 on the ctx stream, "sync" = drain the stream */
 int  vp9cuda_set_option(Vp9CudaCtx *ctx, const char *key, int value);
+/* device time between two marks (waits for mark_b) */
+int  vp9cuda_elapsed_ms(Vp9CudaCtx *ctx, int mark_a, int mark_b, double *ms);
 const char *vp9cuda_version(void);
 
 /* ---- slot-level entry points: the batched equivalent of one VP9DSPContext slot -------------
