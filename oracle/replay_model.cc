@@ -354,3 +354,112 @@ int main(int argc, char **argv)
     return 0;
 }
 #endif
+
+/* ------------------------------------------------------------------------------------------
+ * Slot-level entry points of the restatement (libreplay_model.so), same calling convention as
+ * oracle/slot_shim.c's ref_* functions so the tests can memcmp them against the real slots.
+ * Pixels are uint8_t (bpp 8) or uint16_t; strides in BYTES like the reference slots.
+ * ---------------------------------------------------------------------------------------- */
+template <class P> static void load_px(std::vector<uint16_t> &v, const uint8_t *src, ptrdiff_t stride, int w, int h)
+{
+    v.resize((size_t)w * h);
+    for (int y = 0; y < h; y++)
+        for (int x = 0; x < w; x++)
+            v[(size_t)y * w + x] = ((const P *)(src + y * stride))[x];
+}
+template <class P> static void store_px(const std::vector<uint16_t> &v, uint8_t *dst, ptrdiff_t stride, int w, int h)
+{
+    for (int y = 0; y < h; y++)
+        for (int x = 0; x < w; x++)
+            ((P *)(dst + y * stride))[x] = (P)v[(size_t)y * w + x];
+}
+
+extern "C" {
+
+void model_itxfm_add(int bpp, int tx, int txtp, uint8_t *dst, ptrdiff_t stride, void *block, int eob)
+{
+    const int lossless = tx == 4, t = lossless ? 0 : tx, N = 4 << t;
+    std::vector<uint16_t> v;
+    if (bpp > 8) load_px<uint16_t>(v, dst, stride, N, N); else load_px<uint8_t>(v, dst, stride, N, N);
+    itx_add(v.data(), N, block, t, (txtp & 3) | (lossless ? 0x80 : 0), eob, bpp);
+    if (bpp > 8) store_px<uint16_t>(v, dst, stride, N, N); else store_px<uint8_t>(v, dst, stride, N, N);
+    memset(block, 0, (size_t)N * N * (bpp > 8 ? 4 : 2));     /* the slot zeroes its input */
+}
+
+/* left: bottom-to-top (top-to-bottom for HOR_UP), top[-1] = top-left: the slot's convention */
+void model_intra_pred(int bpp, int tx, int mode, uint8_t *dst, ptrdiff_t stride, const uint8_t *left, const uint8_t *top)
+{
+    const int N = 4 << tx;
+    int T[65], L[32];
+    auto rd = [&](const uint8_t *p, int i) -> int { return bpp > 8 ? ((const uint16_t *)p)[i] : p[i]; };
+    T[0] = rd(top, -1);
+    for (int k = 0; k < 2 * N; k++)
+        T[1 + k] = rd(top, N == 4 ? k : (k < N ? k : N - 1));
+    for (int y = 0; y < N; y++)
+        L[y] = mode == HOR_UP_PRED ? rd(left, y) : rd(left, N - 1 - y);
+    int dc = intra_dc(mode, N, T, L, bpp);
+    for (int y = 0; y < N; y++)
+        for (int x = 0; x < N; x++) {
+            int v = intra_pixel(mode, N, x, y, T, L, dc, bpp);
+            if (bpp > 8) ((uint16_t *)(dst + y * stride))[x] = v; else dst[y * stride + x] = v;
+        }
+}
+
+/* mc / smc: ref points at the block's integer position inside a padded buffer, like the slots */
+void model_mc(int bpp, int w, int filter, int avg, uint8_t *dst, ptrdiff_t dst_stride, const uint8_t *ref,
+              ptrdiff_t ref_stride, int h, int mx, int my, int dx, int dy)
+{
+    const int bps = bpp > 8 ? 2 : 1;
+    McPos pos = { 0, 0, mx, my, dx ? dx : 16, dy ? dy : 16 };
+    for (int oy = 0; oy < h; oy++)
+        for (int ox = 0; ox < w; ox++) {
+            /* unclamped plane: reads reach up to 3 left/above and (step-scaled) beyond, all inside
+             * the caller's padding, so give RefPlane a window that never clamps */
+            int v;
+            if (bpp > 8) {
+                RefPlane<uint16_t> rp = { (const uint16_t *)ref - 64 * (ref_stride / bps) - 64, (int)(ref_stride / bps), 1 << 20, 1 << 20 };
+                McPos p2 = pos; p2.x0 = 64; p2.y0 = 64;
+                v = mc_pixel(rp, p2, ox, oy, filter, bpp);
+                uint16_t *d = (uint16_t *)(dst + oy * dst_stride) + ox;
+                *d = avg ? (*d + v + 1) >> 1 : v;
+            } else {
+                RefPlane<uint8_t> rp = { ref - 64 * ref_stride - 64, (int)ref_stride, 1 << 20, 1 << 20 };
+                McPos p2 = pos; p2.x0 = 64; p2.y0 = 64;
+                v = mc_pixel(rp, p2, ox, oy, filter, bpp);
+                uint8_t *d = dst + oy * dst_stride + ox;
+                *d = avg ? (*d + v + 1) >> 1 : v;
+            }
+        }
+}
+
+/* loop filter over `len` lines (8 or 16); dir 0 = column edge ("h" slots), 1 = row edge ("v") */
+void model_loop_filter(int bpp, int wd, int dir, int len, uint8_t *dst, ptrdiff_t stride, int E, int I, int H)
+{
+    const int bps = bpp > 8 ? 2 : 1;
+    for (int ln = 0; ln < len; ln++) {
+        int px[16];
+        auto at = [&](int k) -> uint8_t * {
+            return dir ? dst + (ptrdiff_t)(k - 8) * stride + ln * bps : dst + (ptrdiff_t)ln * stride + (k - 8) * bps;
+        };
+        for (int k = 0; k < 16; k++)
+            px[k] = bpp > 8 ? *(uint16_t *)at(k) : *at(k);
+        unsigned m = lf_line(px, wd, E, I, H, bpp);
+        for (int k = 0; k < 16; k++)
+            if (m >> k & 1) { if (bpp > 8) *(uint16_t *)at(k) = px[k]; else *at(k) = px[k]; }
+    }
+}
+
+/* mask walk of one superblock plane: fills wd/L tables (col[8][16], row[16][8]) */
+void model_lf_decode(const uint8_t *vp9filter /* 192 bytes */, int chroma, int first_col, int first_row,
+                     uint8_t *col_wd, uint8_t *col_L, uint8_t *row_wd, uint8_t *row_L)
+{
+    LfOps ops;
+    lf_decode_cols(*(const LfSb *)vp9filter, chroma, first_col, ops);
+    lf_decode_rows(*(const LfSb *)vp9filter, chroma, first_row, ops);
+    for (int g = 0; g < 8; g++)
+        for (int p = 0; p < 16; p++) { col_wd[g * 16 + p] = ops.col[g][p].wd; col_L[g * 16 + p] = ops.col[g][p].L; }
+    for (int e = 0; e < 16; e++)
+        for (int c = 0; c < 8; c++) { row_wd[e * 8 + c] = ops.row[e][c].wd; row_L[e * 8 + c] = ops.row[e][c].L; }
+}
+
+} /* extern "C" */
