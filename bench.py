@@ -225,6 +225,15 @@ def main():
     ctx.option("timing", 0)
     checksum_resident = ctx.checksum(-1)
 
+    if os.environ.get("VP9CUDA_PHASE"):
+        ctx.option("phase_clk", 1)
+        ctx.wait(step_resident())
+        pc = ctx.phase_clocks(5)
+        ctx.option("phase_clk", 0)
+        tot = max(sum(pc), 1)
+        print("loop-filter CTA phase share (wait, load, cols, rows, store):",
+              [round(x / tot, 3) for x in pc], "total Mcycles", tot / 1e6, file=sys.stderr)
+
     # ---- leg 2: end to end through the C ABI with host buffers ---------------------------------
     def step_e2e():
         t = 0

@@ -21,7 +21,7 @@ API = [
     "vp9cuda_tile_ring", "vp9cuda_submit_tile", "vp9cuda_finish_frame", "vp9cuda_wait",
     "vp9cuda_show_existing", "vp9cuda_host_alloc", "vp9cuda_host_free", "vp9cuda_decode_frame",
     "vp9cuda_stage_frame", "vp9cuda_run_staged", "vp9cuda_free_staged", "vp9cuda_frame_checksum",
-    "vp9cuda_kernel_stats", "vp9cuda_set_option", "vp9cuda_elapsed_ms", "vp9cuda_slot_itxfm_add",
+    "vp9cuda_kernel_stats", "vp9cuda_set_option", "vp9cuda_elapsed_ms", "vp9cuda_phase_clocks", "vp9cuda_slot_itxfm_add",
     "vp9cuda_slot_intra_pred", "vp9cuda_slot_mc", "vp9cuda_slot_loop_filter",
 ]
 
@@ -71,6 +71,7 @@ def load() -> C.CDLL:
         lib.vp9cuda_frame_checksum.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_uint64)]
         lib.vp9cuda_set_option.argtypes = [C.c_void_p, C.c_char_p, C.c_int]
         lib.vp9cuda_elapsed_ms.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_double)]
+        lib.vp9cuda_phase_clocks.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.c_int]
         lib.vp9cuda_kernel_stats.argtypes = [C.c_void_p, C.POINTER(C.c_char_p), C.POINTER(C.c_double),
                                              C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.c_int]
         _lib = lib
@@ -208,6 +209,11 @@ class Context:
         ms = C.c_double()
         check(self.lib.vp9cuda_elapsed_ms(self.ctx, a, b, C.byref(ms)), "vp9cuda_elapsed_ms")
         return ms.value
+
+    def phase_clocks(self, n: int = 8) -> list:
+        out = (C.c_uint64 * n)()
+        check(self.lib.vp9cuda_phase_clocks(self.ctx, out, n), "vp9cuda_phase_clocks")
+        return list(out)
 
     def checksum(self, slot: int = -1) -> int:
         s = C.c_uint64()

@@ -38,14 +38,17 @@ struct FrameDesc {
     const void *coef;              /* int16_t (8-bit) or int32_t units, arena indexed by coef_off */
     const Vp9CudaSbIndex *sb_index;
     const Vp9CudaLoopFilterSb *lf;
-    uint32_t itx_lane_base[VP9CUDA_MAX_LANES];   /* first record of each lane in `itx` */
     /* scratch */
     int32_t *cellmap;              /* cols*rows: index into blk, -1 = not inter */
-    uint16_t *isched_order;        /* n_itx: per (superblock, plane) segment, record idx sorted by level */
-    uint16_t *isched_lvl_end;      /* [sb][plane][64] cumulative count per dependency level */
-    uint32_t *isched_seg;          /* [sb][plane]: segment start in isched_order */
-    uint8_t  *isched_nlvl;         /* [sb][plane]: number of levels (0 = no intra blocks) */
-    int *progress;                 /* [2 stages][3 planes][sb_rows] wavefront counters */
+    uint32_t *ilvl_hist;           /* [65536] records per intra dependency level -> start offsets */
+    uint32_t *iorder;              /* n_itx record indices sorted by level */
+    uint32_t *icounter;            /* [0] work-claim counter of the intra kernel */
+    uint32_t *done[3];             /* per plane, per 4x4 cell: == gen when its intra block is final */
+    int done_w[3], done_h[3];
+    uint32_t gen;                  /* unique per reconstructed frame */
+    LfOps *lfops;                  /* [sb][plane] decoded loop-filter edge operations */
+    int *progress;                 /* [3 planes][sb_rows] loop-filter wavefront counters */
+    unsigned long long *phase_clk; /* optional: per-phase clock accumulation (profiling), or NULL */
     uint8_t lim_lut[64], mblim_lut[64];
 };
 

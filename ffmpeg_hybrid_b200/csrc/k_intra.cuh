@@ -1,24 +1,28 @@
 /*
- * k_intra.cuh -- K3: intra prediction + residual as a superblock wavefront.
+ * k_intra.cuh -- K3: intra prediction + residual as a dependency-driven wavefront.
  *
- *   k_intra_sched : one thread per (superblock, plane).  Walks the superblock's intra
- *                   transform-block records in coding order and gives each the depth of its
- *                   dependency chain INSIDE the superblock (left column, top-left, top row and,
- *                   for 4x4 blocks that may read it, top-right: vp9recon.c:45-47,96-98), then
- *                   counting-sorts the plane's records by that level.
- *   k_intra       : one CTA per (superblock row, plane), walking the row left to right.  A
- *                   superblock starts when the one above it is finished (its left neighbour
- *                   was done by this same CTA; tile-column starts and top-right never reach
- *                   outside the superblock, vp9recon.c:46-47), which makes the frame a
- *                   (left, top) wavefront across CTAs.  The superblock's pixels live in shared
- *                   memory while its levels are processed: all blocks of one level run in
- *                   parallel, one warp per transform block (edge build, per-pixel predictor,
- *                   then the same itx_block as K1), with a CTA barrier between levels.
+ * Every intra transform block depends on the reconstructed pixels left of, above (and for some
+ * 4x4 blocks above-right of) it (check_intra_mode, vp9recon.c:37-221).  The host records carry
+ * each block's depth in that dependency graph (Vp9CudaIntraTx.level).  Here:
+ *
+ *   k_ilvl_hist / k_ilvl_scan / k_ilvl_scatter : counting sort of the frame's records by level
+ *       (a topological order in which equal levels are mutually independent).
+ *   k_intra : persistent warps claim blocks in that order from a global counter.  A warp first
+ *       waits until the 4x4 cells it may read are final -- one lane polls one cell of the
+ *       per-plane "done" map, and only cells that hold intra blocks of this frame are waited
+ *       for -- then builds the edge arrays lane-parallel straight from the picture in L2,
+ *       predicts into shared memory, adds the residual there (the same itx_block as K1),
+ *       writes the block out once, fences, and marks its cells done.  Because claims are made
+ *       in level order, every block a claimed block waits for has already been claimed by a
+ *       running warp, so the scheme cannot deadlock whatever the grid size.
+ *
+ * The frame thus advances along its true dependency wavefront at 4x4-cell granularity instead
+ * of superblock by superblock; in inter frames the scattered intra clusters are independent.
  *
  * Replaces intra_recon + check_intra_mode (vp9recon.c:37-364) and the intra_pred slots
  * (vp9dsp_template.c:33-1153).  Reads the pre-loop-filter picture everywhere, which is what
  * the reference gets from intra_pred_data at superblock-row tops (vp9.c:1404-1416).
- * Algorithmic bytes: P (write) + coefficients.
+ * Algorithmic bytes: P_intra (write) + edges + coefficients.
  */
 #ifndef VP9CUDA_K_INTRA_CUH
 #define VP9CUDA_K_INTRA_CUH
@@ -28,199 +32,159 @@
 
 namespace vp9 {
 
-#define ISCHED_MAX_LVL 64
+#define ILVL_MAX 65536
 
-__global__ void k_intra_sched(const __grid_constant__ FrameDesc f)
+__global__ void k_ilvl_hist(const Vp9CudaIntraTx *__restrict__ itx, uint32_t n, uint32_t *hist)
 {
-    const int t = blockIdx.x * blockDim.x + threadIdx.x;
-    const int n_sb = f.sb_cols * f.sb_rows;
-    if (t >= n_sb * 3)
-        return;
-    const int sb = t / 3, pl = t % 3;
-    const int ch = pl > 0;
-    const Vp9CudaSbIndex si = f.sb_index[sb];
-    const Vp9CudaIntraTx *rec = f.itx + f.itx_lane_base[si.lane] + si.itx_start;
-    const int sbx4 = ((sb % f.sb_cols) * 16) >> ch, sby4 = ((sb / f.sb_cols) * 16) >> ch;
-    const int S4 = 16 >> ch;                       /* superblock size in 4-pixel cells */
-    int8_t cell[16][16];
-    for (int y = 0; y < S4; y++)
-        for (int x = 0; x < S4; x++)
-            cell[y][x] = -1;
-    uint16_t cnt[ISCHED_MAX_LVL];
-    for (int i = 0; i < ISCHED_MAX_LVL; i++) cnt[i] = 0;
-    /* segment of this plane = after the records of the lower planes of this superblock */
-    uint32_t seg = f.itx_lane_base[si.lane] + si.itx_start;
-    for (int k = 0; k < si.itx_count; k++)
-        if (rec[k].plane < pl)
-            seg++;
-    /* pass 1: levels */
-    uint8_t lv_local[256];
-    int nl = 0, j = 0;
-    for (int k = 0; k < si.itx_count; k++) {
-        const Vp9CudaIntraTx r = rec[k];
-        if (r.plane != pl)
-            continue;
-        const int n = 1 << r.tx;
-        const int cx = r.x4 - sbx4, cy = r.y4 - sby4;
-        int lv = 0;
-        if (cx > 0) {
-            for (int y = max(cy - 1, 0); y < min(cy + n, S4); y++)
-                lv = max(lv, cell[y][cx - 1] + 1);
-        }
-        if (cy > 0) {
-            int xe = cx + n;
-            if (r.tx == 0 && (r.flags & VP9CUDA_ITX_HAVE_RIGHT))
-                xe = cx + 2;
-            for (int x = cx; x < min(xe, S4); x++)
-                lv = max(lv, cell[cy - 1][x] + 1);
-        }
-        for (int y = cy; y < min(cy + n, S4); y++)
-            for (int x = cx; x < min(cx + n, S4); x++)
-                cell[y][x] = (int8_t)lv;
-        cnt[lv]++;
-        nl = max(nl, lv + 1);
-        lv_local[j++] = (uint8_t)lv;
-    }
-    /* pass 2: counting sort */
-    uint16_t start[ISCHED_MAX_LVL];
-    uint16_t acc = 0;
-    uint16_t *lvl_end = f.isched_lvl_end + (size_t)t * ISCHED_MAX_LVL;
-    for (int i = 0; i < ISCHED_MAX_LVL; i++) {
-        start[i] = acc;
-        acc += cnt[i];
-        lvl_end[i] = acc;
-    }
-    j = 0;
-    for (int k = 0; k < si.itx_count; k++) {
-        if (rec[k].plane != pl)
-            continue;
-        int lv = lv_local[j++];
-        f.isched_order[seg + start[lv]++] = (uint16_t)k;
-    }
-    f.isched_seg[t] = seg;
-    f.isched_nlvl[t] = (uint8_t)nl;
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n)
+        atomicAdd(&hist[itx[i].level], 1u);
 }
 
-/* superblock tile in shared memory, with one row above and one column to the left */
-template <class P, int S> struct IntraTile {
-    P px[(S + 1) * (S + 1)];
-    __device__ __forceinline__ P &at(int x, int y) { return px[(y + 1) * (S + 1) + x + 1]; }   /* x,y >= -1 */
-};
-
-template <class P, int S> struct TilePx {
-    IntraTile<P, S> *t; int ox, oy;          /* plane coords of tile (0,0) */
-    __device__ __forceinline__ int operator()(int x, int y) const { return t->at(x - ox, y - oy); }
-};
-template <class P, int S> struct TileBlk {
-    IntraTile<P, S> *t; int bx, by;          /* tile coords of the block origin */
-    __device__ __forceinline__ int get(int x, int y) const { return t->at(bx + x, by + y); }
-    __device__ __forceinline__ void put(int x, int y, int v) { t->at(bx + x, by + y) = (P)v; }
-};
-
-#define INTRA_WARPS 8
-
-template <class P, bool HBD, int S>
-__device__ void intra_superblock(const FrameDesc &f, int pl, int sb, IntraTile<P, S> *tile,
-                                 typename ItxTypes<HBD>::C *tmp_w, int *edge_w)
+/* in-place exclusive scan of hist[0..ILVL_MAX) by one CTA of 1024 threads */
+__global__ void __launch_bounds__(1024) k_ilvl_scan(uint32_t *hist)
 {
-    typedef typename ItxTypes<HBD>::C C;
-    const int ch = pl > 0;
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int t = sb * 3 + pl;
-    const int nl = f.isched_nlvl[t];
-    const uint32_t seg = f.isched_seg[t];
-    const uint16_t *lvl_end = f.isched_lvl_end + (size_t)t * ISCHED_MAX_LVL;
-    const Vp9CudaSbIndex si = f.sb_index[sb];
-    const Vp9CudaIntraTx *rec = f.itx + f.itx_lane_base[si.lane] + si.itx_start;
-    const int ox = ((sb % f.sb_cols) * 64) >> ch, oy = ((sb / f.sb_cols) * 64) >> ch;
-    const int plane_w = (f.cols * 8) >> ch, plane_h = (f.rows * 8) >> ch;
-    const int stride = f.cur.stride[pl];
-    P *plane = (P *)f.cur.pl[pl];
-
-    /* load the tile + its top row and left column (L2 reads: neighbours come from other SMs) */
-    for (int i = threadIdx.x; i < (S + 1) * (S + 1); i += blockDim.x) {
-        int x = i % (S + 1) - 1, y = i / (S + 1) - 1;
-        int gx = ox + x, gy = oy + y;
-        P v = 0;
-        if (gx >= 0 && gy >= 0)
-            v = ld_cg(plane + (size_t)gy * stride + gx);
-        tile->at(x, y) = v;
+    __shared__ uint32_t part[1024];
+    constexpr int PER = ILVL_MAX / 1024;
+    uint32_t loc[PER], s = 0;
+    for (int k = 0; k < PER; k++) {
+        loc[k] = hist[threadIdx.x * PER + k];
+        s += loc[k];
     }
+    part[threadIdx.x] = s;
     __syncthreads();
-
-    int *top = edge_w + warp * 100, *left = top + 66;
-    C *tmp = tmp_w + warp * (32 * 33);
-    int begin = 0;
-    for (int L = 0; L < nl; L++) {
-        const int end = lvl_end[L];
-        for (int k = begin + warp; k < end; k += INTRA_WARPS) {
-            const Vp9CudaIntraTx r = rec[f.isched_order[seg + k]];
-            const int N = 4 << r.tx;
-            const int bx = r.x4 * 4, by = r.y4 * 4;
-            const bool have_top = by > 0, have_left = r.flags & VP9CUDA_ITX_HAVE_LEFT;
-            const int mode = intra_mode_conv(r.mode, have_left, have_top);
-            TilePx<P, S> px = { tile, ox, oy };
-            /* edges: built redundantly by lane 0 into shared memory (small, keeps semantics 1:1) */
-            if (lane == 0)
-                intra_edges(px, bx, by, N, mode, have_top, have_left, r.flags & VP9CUDA_ITX_HAVE_RIGHT,
-                            plane_w - bx, plane_h - by, f.bpp, top, left);
-            __syncwarp();
-            int dc = intra_dc(mode, N, top, left, f.bpp);
-            TileBlk<P, S> blk = { tile, bx - ox, by - oy };
-            for (int i = lane; i < N * N; i += 32)
-                blk.put(i % N, i / N, intra_pixel(mode, N, i % N, i / N, top, left, dc, f.bpp));
-            __syncwarp();
-            if (r.eob) {
-                const C *coef = (const C *)f.coef + r.coef_off;
-                switch (r.tx) {
-                case 0: if (lane < 4)  itx_block<HBD, 4>(coef, tmp, lane, r.txtp, r.eob, f.bpp, blk, 0xfu); break;
-                case 1: if (lane < 8)  itx_block<HBD, 8>(coef, tmp, lane, r.txtp, r.eob, f.bpp, blk, 0xffu); break;
-                case 2: if (lane < 16) itx_block<HBD, 16>(coef, tmp, lane, r.txtp, r.eob, f.bpp, blk, 0xffffu); break;
-                default: itx_block<HBD, 32>(coef, tmp, lane, r.txtp, r.eob, f.bpp, blk, 0xffffffffu); break;
-                }
-            }
-            __syncwarp();
-        }
-        begin = end;
+    for (int o = 1; o < 1024; o <<= 1) {
+        uint32_t v = threadIdx.x >= o ? part[threadIdx.x - o] : 0;
+        __syncthreads();
+        part[threadIdx.x] += v;
         __syncthreads();
     }
-    /* write the superblock back (interior only) */
-    for (int i = threadIdx.x; i < S * S; i += blockDim.x) {
-        int x = i % S, y = i / S;
-        plane[(size_t)(oy + y) * stride + ox + x] = tile->at(x, y);
+    uint32_t base = part[threadIdx.x] - s;
+    for (int k = 0; k < PER; k++) {
+        hist[threadIdx.x * PER + k] = base;
+        base += loc[k];
     }
 }
+
+__global__ void k_ilvl_scatter(const Vp9CudaIntraTx *__restrict__ itx, uint32_t n, uint32_t *cursor,
+                               uint32_t *order)
+{
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n)
+        order[atomicAdd(&cursor[itx[i].level], 1u)] = i;
+}
+
+/* current picture read through L2 (neighbours are written by other SMs during this kernel) */
+template <class P> struct L2PlanePx {
+    const P *p; int stride;
+    __device__ __forceinline__ int operator()(int x, int y) const { return ld_cg(p + (size_t)y * stride + x); }
+};
+/* a block being built in shared memory */
+template <class P> struct SmemBlk {
+    P *p; int stride;
+    __device__ __forceinline__ int get(int x, int y) const { return p[y * stride + x]; }
+    __device__ __forceinline__ void put(int x, int y, int v) { p[y * stride + x] = (P)v; }
+};
+
+#define INTRA_WARPS 4
 
 template <class P, bool HBD>
 __global__ void __launch_bounds__(INTRA_WARPS * 32) k_intra(const __grid_constant__ FrameDesc f)
 {
     typedef typename ItxTypes<HBD>::C C;
-    __shared__ IntraTile<P, 64> tile_mem;
-    __shared__ C tmp_w[INTRA_WARPS * 32 * 33];
-    __shared__ int edge_w[INTRA_WARPS * 100];
-    const int pl = blockIdx.x % 3, row = blockIdx.x / 3;
-    int *prog = f.progress + pl * f.sb_rows;           /* stage 0 */
-    for (int c = 0; c < f.sb_cols; c++) {
-        const int sb = row * f.sb_cols + c;
-        if (f.isched_nlvl[sb * 3 + pl]) {
-            if (row > 0 && threadIdx.x == 0) {
-                volatile int *above = prog + row - 1;
-                while (*above < c + 1)
-                    __nanosleep(100);
-                __threadfence();
+    __shared__ int edge_s[INTRA_WARPS][100];
+    __shared__ P pred_s[INTRA_WARPS][32 * 32];
+    __shared__ C tmp_s[INTRA_WARPS][32 * 33];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    int *top = edge_s[warp], *left = top + 66;
+    P *pred = pred_s[warp];
+    C *tmp = tmp_s[warp];
+
+    for (;;) {
+        uint32_t i = 0;
+        if (lane == 0)
+            i = atomicAdd(f.icounter, 1u);
+        i = __shfl_sync(0xffffffffu, i, 0);
+        if (i >= f.n_itx)
+            break;
+        const Vp9CudaIntraTx r = f.itx[f.iorder[i]];
+        const int pl = r.plane, ch = pl > 0;
+        const int n = 1 << r.tx, N = 4 << r.tx;
+        const int cx = r.x4, cy = r.y4;
+        const bool have_left = r.flags & VP9CUDA_ITX_HAVE_LEFT, have_right = r.flags & VP9CUDA_ITX_HAVE_RIGHT;
+        const bool have_top = cy > 0;
+        const int W = f.done_w[pl], H = f.done_h[pl];
+        uint32_t *done = f.done[pl];
+
+        /* ---- wait for the cells this block may read (same set the host used for `level`) ---- */
+        {
+            int px = -1, py = -1;
+            if (lane <= n) {                       /* left column, lane 0 = top-left */
+                if (have_left && (lane > 0 || have_top) && cy - 1 + lane < H) { px = cx - 1; py = cy - 1 + lane; }
+            } else if (lane >= 16 && have_top) {   /* top row (+ top-right for 4x4) */
+                int k = lane - 16, xe = (r.tx == 0 && have_right) ? 2 : n;
+                if (k < xe && cx + k < W) { px = cx + k; py = cy - 1; }
             }
-            __syncthreads();
-            if (pl == 0)
-                intra_superblock<P, HBD, 64>(f, pl, sb, &tile_mem, tmp_w, edge_w);
-            else
-                intra_superblock<P, HBD, 32>(f, pl, sb, (IntraTile<P, 32> *)&tile_mem, tmp_w, edge_w);
+            if (px >= 0 && f.n_blk) {
+                /* only intra blocks of this frame are ever marked done: skip inter cells */
+                int ci = ch ? py * f.cols + px : (py >> 1) * f.cols + (px >> 1);
+                if (f.cellmap[ci] >= 0)
+                    px = -1;
+            }
+            if (px >= 0) {
+                const volatile uint32_t *flag = done + (size_t)py * W + px;
+                unsigned ns = 32;
+                while (*flag != f.gen) {
+                    __nanosleep(ns);
+                    if (ns < 256) ns <<= 1;
+                }
+            }
+            __syncwarp();
             __threadfence();
-            __syncthreads();
         }
-        /* a superblock without intra blocks is final already (inter kernels ran before), so
-         * the row below never has to wait for anything through it */
-        if (threadIdx.x == 0)
-            atomicExch(prog + row, c + 1);
+
+        /* ---- edges, prediction, residual, all in shared memory ---- */
+        const int bx = cx * 4, by = cy * 4;
+        const int mode = intra_mode_conv(r.mode, have_left, have_top);
+        const int needs = intra_mode_needs(mode);
+        const int stride = f.cur.stride[pl];
+        P *plane = (P *)f.cur.pl[pl];
+        L2PlanePx<P> px = { plane, stride };
+        const int avail_w = ((f.cols * 8) >> ch) - bx, avail_h = ((f.rows * 8) >> ch) - by;
+        for (int e = lane; e < 3 * N + 1; e += 32) {
+            if (e <= 2 * N) {
+                if (needs & 2)
+                    top[e] = intra_edge_top(px, e, bx, by, N, needs, have_top, have_left, have_right, avail_w, f.bpp);
+            } else if (needs & 1) {
+                left[e - 2 * N - 1] = intra_edge_left(px, e - 2 * N - 1, bx, by, have_left, avail_h, f.bpp);
+            }
+        }
+        __syncwarp();
+        const int dc = intra_dc(mode, N, top, left, f.bpp);
+        for (int k = lane; k < N * N; k += 32)
+            pred[k] = (P)intra_pixel(mode, N, k & (N - 1), k >> (2 + r.tx), top, left, dc, f.bpp);
+        __syncwarp();
+        if (r.eob) {
+            SmemBlk<P> blk = { pred, N };
+            const C *coef = (const C *)f.coef + r.coef_off;
+            switch (r.tx) {
+            case 0: if (lane < 4)  itx_block<HBD, 4>(coef, tmp, lane, r.txtp, r.eob, f.bpp, blk, 0xfu); break;
+            case 1: if (lane < 8)  itx_block<HBD, 8>(coef, tmp, lane, r.txtp, r.eob, f.bpp, blk, 0xffu); break;
+            case 2: if (lane < 16) itx_block<HBD, 16>(coef, tmp, lane, r.txtp, r.eob, f.bpp, blk, 0xffffu); break;
+            default: itx_block<HBD, 32>(coef, tmp, lane, r.txtp, r.eob, f.bpp, blk, 0xffffffffu); break;
+            }
+            __syncwarp();
+        }
+        for (int k = lane; k < N * N; k += 32)
+            plane[(size_t)(by + (k >> (2 + r.tx))) * stride + bx + (k & (N - 1))] = pred[k];
+        __threadfence();
+        __syncwarp();
+        /* ---- publish ---- */
+        for (int k = lane; k < n * n; k += 32) {
+            int x = cx + (k & (n - 1)), y = cy + (k >> r.tx);
+            if (x < W && y < H)
+                *(volatile uint32_t *)(done + (size_t)y * W + x) = f.gen;
+        }
     }
 }
 

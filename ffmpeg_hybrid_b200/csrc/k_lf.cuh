@@ -27,29 +27,52 @@ namespace vp9 {
 
 #define LF_THREADS 128
 
-template <class P, int S>
-__device__ void lf_superblock(const FrameDesc &f, int pl, int sr, int sc, P *win /* (S+8)*(S+8) */, LfOps *ops)
+/* pre-pass, fully parallel: one thread per (superblock, plane, direction) turns the VP9Filter
+ * masks into the edge-op table the wavefront kernel consumes */
+__global__ void k_lf_ops(const __grid_constant__ FrameDesc f)
 {
-    constexpr int W = S + 8;
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    const int n_sb = f.sb_cols * f.sb_rows;
+    if (t >= n_sb * 6)
+        return;
+    const int sb = t / 6, pl = (t % 6) >> 1, dir = t & 1;
+    const LfSb &m = *(const LfSb *)&f.lf[sb];
+    LfOps &o = f.lfops[sb * 3 + pl];
+    if (dir == 0)
+        lf_decode_cols(m, pl > 0, sb % f.sb_cols == 0, o);
+    else
+        lf_decode_rows(m, pl > 0, sb / f.sb_cols == 0, o);
+}
+
+#define LF_CLK(k) do { if (f.phase_clk && threadIdx.x == 0) { long long c_ = clock64(); \
+    atomicAdd(&f.phase_clk[k], (unsigned long long)(c_ - clk_)); clk_ = c_; } } while (0)
+
+template <class P, int S>
+__device__ void lf_superblock(const FrameDesc &f, int pl, int sr, int sc, P *win /* (S+8)*(S+10) */, LfOps *ops,
+                              long long &clk_)
+{
+    constexpr int W = S + 10;               /* odd word stride: conflict-free line-per-thread access */
     const int ch = pl > 0;
     const int x0 = sc * S, y0 = sr * S;
     const int stride = f.cur.stride[pl];
     P *plane = (P *)f.cur.pl[pl];
-    const LfSb &m = *(const LfSb *)&f.lf[sr * f.sb_cols + sc];
-
-    for (int i = threadIdx.x; i < W * W; i += blockDim.x) {
-        int x = i % W - 8, y = i / W - 8;
+    (void)ch;
+    for (int i = threadIdx.x; i < (S + 8) * (S + 8); i += blockDim.x) {
+        int x = i % (S + 8) - 8, y = i / (S + 8) - 8;
         int gx = x0 + x, gy = y0 + y;
         P v = 0;
         if (gx >= 0 && gy >= 0 && !(x < 0 && y < 0))
             v = ld_cg(plane + (size_t)gy * stride + gx);
-        win[i] = v;
+        win[(y + 8) * W + x + 8] = v;
     }
-    if (threadIdx.x == 0)
-        lf_decode_cols(m, ch, sc == 0, *ops);
-    if (threadIdx.x == 32)
-        lf_decode_rows(m, ch, sr == 0, *ops);
+    {
+        const uint32_t *src = (const uint32_t *)&f.lfops[(sr * f.sb_cols + sc) * 3 + pl];
+        uint32_t *dst = (uint32_t *)ops;
+        for (int i = threadIdx.x; i < (int)(sizeof(LfOps) / 4); i += blockDim.x)
+            dst[i] = src[i];
+    }
     __syncthreads();
+    LF_CLK(1);
 
     /* column pass: thread = pixel row */
     if (threadIdx.x < S) {
@@ -78,6 +101,7 @@ __device__ void lf_superblock(const FrameDesc &f, int pl, int sr, int sc, P *win
         }
     }
     __syncthreads();
+    LF_CLK(2);
     /* row pass: thread = pixel column */
     if (threadIdx.x < S) {
         const int ln = threadIdx.x;
@@ -105,21 +129,23 @@ __device__ void lf_superblock(const FrameDesc &f, int pl, int sr, int sc, P *win
         }
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < W * W; i += blockDim.x) {
-        int x = i % W - 8, y = i / W - 8;
+    LF_CLK(3);
+    for (int i = threadIdx.x; i < (S + 8) * (S + 8); i += blockDim.x) {
+        int x = i % (S + 8) - 8, y = i / (S + 8) - 8;
         int gx = x0 + x, gy = y0 + y;
         if (gx >= 0 && gy >= 0 && !(x < 0 && y < 0))
-            plane[(size_t)gy * stride + gx] = win[i];
+            plane[(size_t)gy * stride + gx] = win[(y + 8) * W + x + 8];
     }
 }
 
 template <class P>
 __global__ void __launch_bounds__(LF_THREADS) k_lf(const __grid_constant__ FrameDesc f)
 {
-    __shared__ P win[72 * 72];
+    __shared__ P win[72 * 74];
     __shared__ LfOps ops;
     const int pl = blockIdx.x % 3, row = blockIdx.x / 3;
-    int *prog = f.progress + (3 + pl) * f.sb_rows;           /* stage 1 */
+    int *prog = f.progress + pl * f.sb_rows;
+    long long clk_ = clock64();
     for (int c = 0; c < f.sb_cols; c++) {
         if (row > 0 && threadIdx.x == 0) {
             const int need = min(c + 2, f.sb_cols);
@@ -129,14 +155,16 @@ __global__ void __launch_bounds__(LF_THREADS) k_lf(const __grid_constant__ Frame
             __threadfence();
         }
         __syncthreads();
+        LF_CLK(0);
         if (pl == 0)
-            lf_superblock<P, 64>(f, pl, row, c, win, &ops);
+            lf_superblock<P, 64>(f, pl, row, c, win, &ops, clk_);
         else
-            lf_superblock<P, 32>(f, pl, row, c, win, &ops);
+            lf_superblock<P, 32>(f, pl, row, c, win, &ops, clk_);
         __threadfence();
         __syncthreads();
         if (threadIdx.x == 0)
             atomicExch(prog + row, c + 1);
+        LF_CLK(4);
     }
 }
 

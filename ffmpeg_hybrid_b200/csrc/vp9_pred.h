@@ -217,39 +217,46 @@ VP9_HD int intra_mode_needs(int mode)
  *   have_right: not the last tx column of its coding block (vp9recon.c:47)
  *   avail_w/h : pixels from (bx,by) to the 8-aligned frame edge (n_px_have, :103,192)
  * Values that the chosen mode does not read are still filled deterministically. */
+/* top[i] of the edge arrays: i = 0 is the top-left sample, i = 1 + k the k-th sample above */
+template <class PX>
+VP9_HD int intra_edge_top(const PX &Px, int i, int bx, int by, int N, int needs, bool have_top,
+                          bool have_left, bool have_right, int avail_w, int bpp)
+{
+    const int base = 128 << (bpp - 8);
+    if (i == 0)
+        return (have_left && have_top) ? Px(bx - 1, by - 1) : base + (have_top ? 1 : -1);
+    int k = i - 1;
+    if (!have_top)
+        return base - 1;
+    if (k >= N) {
+        /* beyond the block: real top-right only for 4x4 blocks that may read it, else replicate */
+        if (!(N == 4 && (needs & 8) && have_right && 8 <= avail_w))
+            k = N - 1;
+    }
+    return Px(bx + (k < avail_w ? k : avail_w - 1), by - 1);
+}
+
+/* left[y]: the sample left of row y */
+template <class PX>
+VP9_HD int intra_edge_left(const PX &Px, int y, int bx, int by, bool have_left, int avail_h, int bpp)
+{
+    if (!have_left)
+        return (128 << (bpp - 8)) + 1;
+    return Px(bx - 1, by + (y < avail_h ? y : avail_h - 1));
+}
+
 template <class PX>
 VP9_HD void intra_edges(const PX &Px, int bx, int by, int N, int mode /* converted */,
                         bool have_top, bool have_left, bool have_right, int avail_w, int avail_h,
                         int bpp, int *top /* [1 + 2N] */, int *left /* [N] */)
 {
-    const int base = 128 << (bpp - 8);
     int needs = intra_mode_needs(mode);
-    if (needs & 2) {
-        if (have_top) {
-            for (int i = 0; i < N; i++)
-                top[1 + i] = Px(bx + (i < avail_w ? i : avail_w - 1), by - 1);
-        } else {
-            for (int i = 0; i < N; i++)
-                top[1 + i] = base - 1;
-        }
-        if (N == 4 && (needs & 8) && have_top && have_right && 8 <= avail_w) {
-            for (int i = 4; i < 8; i++)
-                top[1 + i] = Px(bx + i, by - 1);
-        } else {
-            for (int i = N; i < 2 * N; i++)
-                top[1 + i] = top[N];
-        }
-        top[0] = (have_left && have_top) ? Px(bx - 1, by - 1) : base + (have_top ? 1 : -1);
-    }
-    if (needs & 1) {
-        if (have_left) {
-            for (int y = 0; y < N; y++)
-                left[y] = Px(bx - 1, by + (y < avail_h ? y : avail_h - 1));
-        } else {
-            for (int y = 0; y < N; y++)
-                left[y] = base + 1;
-        }
-    }
+    if (needs & 2)
+        for (int i = 0; i <= 2 * N; i++)
+            top[i] = intra_edge_top(Px, i, bx, by, N, needs, have_top, have_left, have_right, avail_w, bpp);
+    if (needs & 1)
+        for (int y = 0; y < N; y++)
+            left[y] = intra_edge_left(Px, y, bx, by, have_left, avail_h, bpp);
 }
 
 VP9_HD int avg2(int a, int b) { return (a + b + 1) >> 1; }

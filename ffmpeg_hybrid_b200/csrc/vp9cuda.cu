@@ -19,6 +19,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <algorithm>
 #include <mutex>
 #include <vector>
 
@@ -90,17 +91,16 @@ struct HBuf {
 /* device-resident records + scratch of one frame */
 struct DevRecords {
     DBuf blk, tx[4], itx, coef, sb_index, lf;
-    DBuf cellmap, isched_order, isched_lvl_end, isched_seg, isched_nlvl, progress;
+    DBuf cellmap, ilvl_hist, iorder, icounter, lfops, progress;
     Vp9CudaFrameHeader hdr;
     uint32_t n_blk = 0, n_tx[4] = { 0, 0, 0, 0 }, n_itx = 0;
-    uint32_t itx_lane_base[VP9CUDA_MAX_LANES];
     bool used = false;
     void release()
     {
         blk.release(); itx.release(); coef.release(); sb_index.release(); lf.release();
         for (auto &t : tx) t.release();
-        cellmap.release(); isched_order.release(); isched_lvl_end.release(); isched_seg.release();
-        isched_nlvl.release(); progress.release();
+        cellmap.release(); ilvl_hist.release(); iorder.release(); icounter.release(); lfops.release();
+        progress.release();
     }
 };
 
@@ -123,7 +123,7 @@ struct KStat {
     double ms = 0;
     uint64_t launches = 0, bytes = 0;
 };
-enum { KS_CELLMAP, KS_INTER, KS_ITX, KS_ISCHED, KS_INTRA, KS_LF, KS_H2D, KS_D2H, KS_N };
+enum { KS_CELLMAP, KS_INTER, KS_ITX, KS_ISCHED, KS_INTRA, KS_LFOPS, KS_LF, KS_H2D, KS_D2H, KS_N };
 
 } /* namespace */
 
@@ -147,6 +147,10 @@ struct Vp9CudaCtx {
     size_t tused = 0;
     cudaEvent_t marks[16] = { nullptr };
     DBuf sum_buf;
+    DBuf done[3];                          /* intra "cell is final" maps, tagged with gen */
+    uint32_t gen = 0;
+    DBuf phase_clk;                        /* optional profiling counters (set_option "phase_clk") */
+    bool phase_on = false;
 };
 
 static Surface *surface_get(Vp9CudaCtx *c, int w, int h, int bpp)
@@ -272,11 +276,11 @@ static int upload_records(Vp9CudaCtx *c, DevRecords &d, const Vp9CudaFrameHeader
     r |= d.sb_index.reserve(n_sb * sizeof(Vp9CudaSbIndex));
     r |= d.lf.reserve(n_sb * sizeof(Vp9CudaLoopFilterSb));
     r |= d.cellmap.reserve((size_t)cols * rows * 4);
-    r |= d.isched_order.reserve(n_itx * 2);
-    r |= d.isched_lvl_end.reserve((size_t)n_sb * 3 * ISCHED_MAX_LVL * 2);
-    r |= d.isched_seg.reserve((size_t)n_sb * 3 * 4);
-    r |= d.isched_nlvl.reserve((size_t)n_sb * 3);
-    r |= d.progress.reserve((size_t)6 * sb_rows * 4);
+    r |= d.ilvl_hist.reserve((size_t)ILVL_MAX * 4);
+    r |= d.iorder.reserve(n_itx * 4);
+    r |= d.icounter.reserve(64);
+    r |= d.lfops.reserve((size_t)n_sb * 3 * sizeof(LfOps));
+    r |= d.progress.reserve((size_t)3 * sb_rows * 4);
     if (r)
         return -ENOMEM;
     kstat_begin(c);
@@ -284,7 +288,6 @@ static int upload_records(Vp9CudaCtx *c, DevRecords &d, const Vp9CudaFrameHeader
     for (int l = 0; l < nl; l++) {
         const Vp9CudaLaneCounts &n = recs->counts[l];
         const Vp9CudaLaneRing &g = recs->lanes[l];
-        d.itx_lane_base[l] = (uint32_t)o_itx;
         if (n.blk)
             CK(cudaMemcpyAsync((char *)d.blk.p + o_blk * sizeof(Vp9CudaInterBlock), g.blk,
                                n.blk * sizeof(Vp9CudaInterBlock), cudaMemcpyHostToDevice, c->stream));
@@ -303,9 +306,11 @@ static int upload_records(Vp9CudaCtx *c, DevRecords &d, const Vp9CudaFrameHeader
         o_blk += n.blk; o_itx += n.itx;
         for (int t = 0; t < 4; t++) o_tx[t] += n.tx[t];
     }
-    CK(cudaMemcpyAsync(d.sb_index.p, recs->sb_index, n_sb * sizeof(Vp9CudaSbIndex), cudaMemcpyHostToDevice, c->stream));
-    CK(cudaMemcpyAsync(d.lf.p, recs->lf, n_sb * sizeof(Vp9CudaLoopFilterSb), cudaMemcpyHostToDevice, c->stream));
-    bytes += n_sb * (sizeof(Vp9CudaSbIndex) + sizeof(Vp9CudaLoopFilterSb));
+    /* sb_index is not needed on the device any more (intra records are addressed globally) */
+    if (hdr->lf_level) {
+        CK(cudaMemcpyAsync(d.lf.p, recs->lf, n_sb * sizeof(Vp9CudaLoopFilterSb), cudaMemcpyHostToDevice, c->stream));
+        bytes += n_sb * sizeof(Vp9CudaLoopFilterSb);
+    }
     kstat_end(c, KS_H2D, 0, bytes);
     d.hdr = *hdr;
     d.n_blk = (uint32_t)n_blk; d.n_itx = (uint32_t)n_itx;
@@ -344,17 +349,23 @@ static int launch_frame(Vp9CudaCtx *c, const FrameDesc &f, const DevRecords &d)
         kstat_end(c, KS_ITX, itx_launches, itx_bytes);
     if (f.n_itx) {
         kstat_begin(c);
-        const int n = f.sb_cols * f.sb_rows * 3;
-        k_intra_sched<<<(n + 63) / 64, 64, 0, s>>>(f);
-        kstat_end(c, KS_ISCHED, 1, (uint64_t)f.n_itx * sizeof(Vp9CudaIntraTx));
+        CK(cudaMemsetAsync(f.ilvl_hist, 0, (size_t)ILVL_MAX * 4, s));
+        CK(cudaMemsetAsync(f.icounter, 0, 64, s));
+        k_ilvl_hist<<<(f.n_itx + 255) / 256, 256, 0, s>>>(f.itx, f.n_itx, f.ilvl_hist);
+        k_ilvl_scan<<<1, 1024, 0, s>>>(f.ilvl_hist);
+        k_ilvl_scatter<<<(f.n_itx + 255) / 256, 256, 0, s>>>(f.itx, f.n_itx, f.ilvl_hist, f.iorder);
+        kstat_end(c, KS_ISCHED, 3, (uint64_t)f.n_itx * (sizeof(Vp9CudaIntraTx) + 8));
         kstat_begin(c);
-        CK(cudaMemsetAsync(f.progress, 0, (size_t)3 * f.sb_rows * 4, s));
-        k_intra<P, HBD><<<3 * f.sb_rows, INTRA_WARPS * 32, 0, s>>>(f);
+        const int ctas = (int)std::min<uint64_t>((f.n_itx + INTRA_WARPS - 1) / INTRA_WARPS, 148 * 4);
+        k_intra<P, HBD><<<ctas, INTRA_WARPS * 32, 0, s>>>(f);
         kstat_end(c, KS_INTRA, 1, P_bytes);
     }
     if (f.lf_level) {
         kstat_begin(c);
-        CK(cudaMemsetAsync(f.progress + 3 * f.sb_rows, 0, (size_t)3 * f.sb_rows * 4, s));
+        k_lf_ops<<<(f.sb_cols * f.sb_rows * 6 + 127) / 128, 128, 0, s>>>(f);
+        kstat_end(c, KS_LFOPS, 1, (uint64_t)f.sb_cols * f.sb_rows * (sizeof(Vp9CudaLoopFilterSb) + 3 * sizeof(LfOps)));
+        kstat_begin(c);
+        CK(cudaMemsetAsync(f.progress, 0, (size_t)3 * f.sb_rows * 4, s));
         k_lf<P><<<3 * f.sb_rows, LF_THREADS, 0, s>>>(f);
         kstat_end(c, KS_LF, 1, 2 * P_bytes);
     }
@@ -421,13 +432,24 @@ static int reconstruct(Vp9CudaCtx *c, DevRecords &d, uint8_t *const out_planes[3
     f.coef = d.coef.p;
     f.sb_index = (const Vp9CudaSbIndex *)d.sb_index.p;
     f.lf = (const Vp9CudaLoopFilterSb *)d.lf.p;
-    memcpy(f.itx_lane_base, d.itx_lane_base, sizeof(f.itx_lane_base));
     f.cellmap = (int32_t *)d.cellmap.p;
-    f.isched_order = (uint16_t *)d.isched_order.p;
-    f.isched_lvl_end = (uint16_t *)d.isched_lvl_end.p;
-    f.isched_seg = (uint32_t *)d.isched_seg.p;
-    f.isched_nlvl = (uint8_t *)d.isched_nlvl.p;
+    f.ilvl_hist = (uint32_t *)d.ilvl_hist.p;
+    f.iorder = (uint32_t *)d.iorder.p;
+    f.icounter = (uint32_t *)d.icounter.p;
+    f.lfops = (LfOps *)d.lfops.p;
     f.progress = (int *)d.progress.p;
+    f.gen = ++c->gen;
+    for (int p = 0; p < 3; p++) {
+        f.done_w[p] = (f.cols * 2) >> !!p;
+        f.done_h[p] = (f.rows * 2) >> !!p;
+        size_t n = (size_t)f.done_w[p] * f.done_h[p] * 4;
+        if (n > c->done[p].cap) {
+            if (c->done[p].reserve(n)) { surface_unref(cur); return -ENOMEM; }
+            CK(cudaMemsetAsync(c->done[p].p, 0, c->done[p].cap, c->stream));
+        }
+        f.done[p] = (uint32_t *)c->done[p].p;
+    }
+    f.phase_clk = c->phase_on ? (unsigned long long *)c->phase_clk.p : nullptr;
     memcpy(f.lim_lut, h.lim_lut, 64);
     memcpy(f.mblim_lut, h.mblim_lut, 64);
 
@@ -456,8 +478,9 @@ static int reconstruct(Vp9CudaCtx *c, DevRecords &d, uint8_t *const out_planes[3
 /* ------------------------------------------------------------------------------------------
  * C ABI
  * ---------------------------------------------------------------------------------------- */
-static const char *const ks_names[KS_N] = { "cellmap", "inter_pred", "itxfm_add", "intra_sched",
-                                            "intra_wavefront", "loop_filter", "h2d_records", "d2h_frame" };
+static const char *const ks_names[KS_N] = { "cellmap", "inter_pred", "itxfm_add", "intra_sort",
+                                            "intra_wavefront", "lf_ops", "loop_filter", "h2d_records",
+                                            "d2h_frame" };
 
 extern "C" const char *vp9cuda_version(void)
 {
@@ -542,6 +565,8 @@ extern "C" void vp9cuda_destroy(Vp9CudaCtx *c)
     for (auto &e : c->marks) cudaEventDestroy(e);
     for (auto &e : c->tpool) cudaEventDestroy(e);
     c->sum_buf.release();
+    c->phase_clk.release();
+    for (auto &d : c->done) d.release();
     cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -793,6 +818,15 @@ extern "C" int vp9cuda_set_option(Vp9CudaCtx *c, const char *key, int value)
         CK(cudaEventRecord(c->marks[value], c->stream));
         return 0;
     }
+    if (!strcmp(key, "phase_clk")) {       /* profiling: accumulate per-phase clocks inside k_lf */
+        cudaSetDevice(c->device);
+        if (c->phase_clk.reserve(64 * 8))
+            return -ENOMEM;
+        CK(cudaStreamSynchronize(c->stream));
+        CK(cudaMemset(c->phase_clk.p, 0, 64 * 8));
+        c->phase_on = value != 0;
+        return 0;
+    }
     if (!strcmp(key, "sync")) {
         cudaSetDevice(c->device);
         CK(cudaStreamSynchronize(c->stream));
@@ -817,6 +851,16 @@ extern "C" int vp9cuda_elapsed_ms(Vp9CudaCtx *c, int mark_a, int mark_b, double 
     CK(cudaEventElapsedTime(&f, c->marks[mark_a], c->marks[mark_b]));
     *ms = f;
     return 0;
+}
+
+extern "C" int vp9cuda_phase_clocks(Vp9CudaCtx *c, uint64_t *out, int n)
+{
+    if (!c || !out || n < 1 || n > 64 || !c->phase_clk.p)
+        return -EINVAL;
+    cudaSetDevice(c->device);
+    CK(cudaStreamSynchronize(c->stream));
+    CK(cudaMemcpy(out, c->phase_clk.p, (size_t)n * 8, cudaMemcpyDeviceToHost));
+    return n;
 }
 
 /* ---- checksum of a frame in HBM ----------------------------------------------------------------- */

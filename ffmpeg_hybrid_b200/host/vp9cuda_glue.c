@@ -51,6 +51,12 @@ struct VP9CudaGlue {
     int in_frame;
     int overflow;
     unsigned sb_cols;
+    /* intra dependency levels: per plane one (tag << 16 | level) word per 4x4 cell; a word whose
+     * tag is not the current frame's means "no intra block of this frame here" */
+    uint32_t *lvl[3];
+    int lvl_w[3], lvl_h[3];
+    size_t lvl_cap[3];
+    uint32_t lvl_tag;
 };
 
 /* ------------------------------------------------------------------------------------------
@@ -262,6 +268,8 @@ void ff_vp9cuda_uninit(AVCodecContext *avctx)
     g->api.destroy(g->ctx);
     if (g->dl)
         dlclose(g->dl);
+    for (int p = 0; p < 3; p++)
+        av_freep(&g->lvl[p]);
     av_free(g);
     s->cuda = NULL;
 }
@@ -326,6 +334,24 @@ int ff_vp9cuda_begin_frame(AVCodecContext *avctx)
             return AVERROR_EXTERNAL;
         memset(&g->cnt[i], 0, sizeof(g->cnt[i]));
     }
+    for (int p = 0; p < 3; p++) {
+        int w = (s->cols * 2) >> !!p, hh = (s->rows * 2) >> !!p;
+        size_t n = (size_t)w * hh;
+        if (n > g->lvl_cap[p]) {
+            av_freep(&g->lvl[p]);
+            g->lvl[p] = av_calloc(n, sizeof(uint32_t));
+            if (!g->lvl[p])
+                return AVERROR(ENOMEM);
+            g->lvl_cap[p] = n;
+        }
+        g->lvl_w[p] = w;
+        g->lvl_h[p] = hh;
+    }
+    if (++g->lvl_tag > 0xffff) {               /* tags wrapped: forget everything */
+        for (int p = 0; p < 3; p++)
+            memset(g->lvl[p], 0, g->lvl_cap[p] * sizeof(uint32_t));
+        g->lvl_tag = 1;
+    }
     g->in_frame = 1;
     g->overflow = 0;
     return 0;
@@ -348,6 +374,40 @@ static av_always_inline uint32_t take_coefs(VP9CudaGlue *g, int lane, int16_t *s
     memset(src, 0, bytes);
     c->coef = off + n_coefs;
     return r->coef_base + off;
+}
+
+static av_always_inline int lvl_get(const VP9CudaGlue *g, int p, int x, int y)
+{
+    uint32_t v = g->lvl[p][(size_t)y * g->lvl_w[p] + x];
+    return (v >> 16) == g->lvl_tag ? (int)(v & 0xffff) : -1;
+}
+
+/* Dependency depth of one intra transform block (n x n cells at cell x,y of plane p) and
+ * registration of its cells.  The neighbour set is the superset of what check_intra_mode()
+ * may read (vp9recon.c:37-221): left column incl. top-left when have_left, top row when
+ * have_top, one more cell to the right for 4x4 blocks with have_right.  All of them precede
+ * the block in coding order and lie in the same tile column, so tile threads never race. */
+static av_always_inline int intra_level(VP9CudaGlue *g, int p, int x, int y, int n, int have_left,
+                                        int have_top, int topright)
+{
+    const int w = g->lvl_w[p], h = g->lvl_h[p];
+    int lv = 0, i, j, xe, ye;
+    if (have_left) {
+        ye = FFMIN(y + n, h);
+        for (j = have_top ? y - 1 : y; j < ye; j++)
+            lv = FFMAX(lv, lvl_get(g, p, x - 1, j) + 1);
+    }
+    if (have_top) {
+        xe = FFMIN(x + (topright ? 2 : n), w);
+        for (i = x; i < xe; i++)
+            lv = FFMAX(lv, lvl_get(g, p, i, y - 1) + 1);
+    }
+    xe = FFMIN(x + n, w);
+    ye = FFMIN(y + n, h);
+    for (j = y; j < ye; j++)
+        for (i = x; i < xe; i++)
+            g->lvl[p][(size_t)j * w + i] = g->lvl_tag << 16 | lv;
+    return lv;
 }
 
 void ff_vp9cuda_emit_block(VP9TileData *td)
@@ -394,7 +454,9 @@ void ff_vp9cuda_emit_block(VP9TileData *td)
                 o->txtp = ff_vp9_intra_txfm_type[mode] | lossless;
                 o->flags = ((have_left_blk || x > 0) ? VP9CUDA_ITX_HAVE_LEFT : 0) |
                            (x < w4 - 1 ? VP9CUDA_ITX_HAVE_RIGHT : 0);
-                o->pad = 0;
+                memset(o->pad, 0, sizeof(o->pad));
+                o->level = intra_level(g, 0, o->x4, o->y4, step1d, o->flags & VP9CUDA_ITX_HAVE_LEFT,
+                                       o->y4 > 0, b->tx == TX_4X4 && (o->flags & VP9CUDA_ITX_HAVE_RIGHT));
                 o->coef_off = eob ? take_coefs(g, lane, td->block + 16 * n * bytesperpixel,
                                                16 << (2 * b->tx), bytesperpixel) : 0;
             }
@@ -415,7 +477,9 @@ void ff_vp9cuda_emit_block(VP9TileData *td)
                     o->txtp = DCT_DCT | lossless;
                     o->flags = ((have_left_blk || x > 0) ? VP9CUDA_ITX_HAVE_LEFT : 0) |
                                (x < w4 - 1 ? VP9CUDA_ITX_HAVE_RIGHT : 0);
-                    o->pad = 0;
+                    memset(o->pad, 0, sizeof(o->pad));
+                    o->level = intra_level(g, 1 + p, o->x4, o->y4, uvstep1d, o->flags & VP9CUDA_ITX_HAVE_LEFT,
+                                           o->y4 > 0, b->uvtx == TX_4X4 && (o->flags & VP9CUDA_ITX_HAVE_RIGHT));
                     o->coef_off = eob ? take_coefs(g, lane, td->uvblock[p] + 16 * n * bytesperpixel,
                                                    16 << (2 * b->uvtx), bytesperpixel) : 0;
                 }

@@ -22,7 +22,7 @@ HDR_DTYPE = np.dtype([
     ("lane_sbs", "<u2", (MAX_LANES,)), ("lim_lut", "u1", (64,)), ("mblim_lut", "u1", (64,)),
 ], align=True)
 COUNTS_DTYPE = np.dtype([("blk", "<u4"), ("tx", "<u4", (4,)), ("itx", "<u4"), ("coef", "<u4")])
-BLK_SIZE, TX_SIZE, ITX_SIZE, SBI_SIZE, LF_SIZE = 48, 12, 16, 8, 192
+BLK_SIZE, TX_SIZE, ITX_SIZE, SBI_SIZE, LF_SIZE = 48, 12, 20, 8, 192
 
 
 @dataclass

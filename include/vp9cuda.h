@@ -30,7 +30,7 @@ extern "C" {
 #pragma GCC visibility push(default)   /* the library is built with -fvisibility=hidden */
 #endif
 
-#define VP9CUDA_ABI_VERSION 1
+#define VP9CUDA_ABI_VERSION 2
 #define VP9CUDA_MAX_LANES   64   /* max tile columns, vp9.c:800-810 */
 
 typedef struct Vp9CudaCtx Vp9CudaCtx;
@@ -66,14 +66,19 @@ typedef struct Vp9CudaTx {
 typedef struct Vp9CudaIntraTx {
     uint16_t x4, y4;
     uint16_t eob;            /* 0 = prediction only */
+    uint16_t level;          /* depth of this block's dependency chain in the frame: 0 when no
+                                neighbour it may read (left column incl. top-left, top row, and
+                                top-right for 4x4) is an intra block of this frame, else 1 + the
+                                largest level among those neighbours.  Blocks of equal level are
+                                independent; the GPU dispatches in level order. */
     uint8_t  plane;          /* 0 Y, 1 U, 2 V */
     uint8_t  tx;             /* enum TxfmMode 0..3 */
     uint8_t  mode;           /* signalled IntraPredMode 0..9 (edge remap happens on the GPU) */
     uint8_t  txtp;           /* enum TxfmType | 0x80 when lossless */
     uint8_t  flags;          /* VP9CUDA_ITX_* */
-    uint8_t  pad;
+    uint8_t  pad[3];
     uint32_t coef_off;
-} Vp9CudaIntraTx;            /* 16 bytes */
+} Vp9CudaIntraTx;            /* 20 bytes */
 #define VP9CUDA_ITX_HAVE_LEFT  1   /* col > tile_col_start || x > 0  (vp9recon.c:46) */
 #define VP9CUDA_ITX_HAVE_RIGHT 2   /* x < w - 1 inside the coding block (vp9recon.c:47) */
 
@@ -214,6 +219,9 @@ int  vp9cuda_kernel_stats(Vp9CudaCtx *ctx, const char **names, double *ms, uint6
 /* keys: "timing" 0/1 (per-stage CUDA events on the ctx stream, no host syncs),
  * "reset_stats", "mark" = record timing mark 0..15 on the ctx stream, "sync" = drain the stream */
 int  vp9cuda_set_option(Vp9CudaCtx *ctx, const char *key, int value);
+/* profiling aid: after set_option("phase_clk", 1), SM clock cycles accumulated per phase of the
+ * loop-filter wavefront CTAs (0 wait, 1 load, 2 column pass, 3 row pass, 4 store+publish) */
+int  vp9cuda_phase_clocks(Vp9CudaCtx *ctx, uint64_t *out, int n);
 /* device time between two marks (waits for mark_b) */
 int  vp9cuda_elapsed_ms(Vp9CudaCtx *ctx, int mark_a, int mark_b, double *ms);
 const char *vp9cuda_version(void);

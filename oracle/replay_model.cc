@@ -24,6 +24,7 @@
 #include <cstring>
 #include <cstdint>
 #include <vector>
+#include <algorithm>
 #include <memory>
 
 #include "vp9cuda.h"
@@ -266,7 +267,15 @@ static void decode_frame(Model &m, const Vp9CudaFrameHeader &h, const std::vecto
             for (const auto &r : l.tx[t])
                 itx_add(&c.p[r.plane][(size_t)r.y4 * 4 * c.stride[r.plane] + r.x4 * 4], c.stride[r.plane],
                         coef_ptr(lanes, r.coef_off, cb), t, r.txtp, r.eob, h.bpp);
-    /* phase 3: intra blocks, superblocks in raster order, coding order inside */
+    /* phase 3: intra blocks, superblocks in raster order, coding order inside.  Along the way
+     * the records' dependency levels are re-derived and checked (exactly 1 + max over the intra
+     * neighbours the block may read), which is what the GPU's level-ordered dispatch relies on. */
+    std::vector<int> lvmap[3];
+    int lvw[3], lvh[3];
+    for (int p = 0; p < 3; p++) {
+        lvw[p] = (cols * 2) >> !!p; lvh[p] = (rows * 2) >> !!p;
+        lvmap[p].assign((size_t)lvw[p] * lvh[p], -1);
+    }
     for (int s = 0; s < sb_rows * sb_cols; s++) {
         const Lane &l = lanes[sbi[s].lane];
         for (unsigned k = 0; k < sbi[s].itx_count; k++) {
@@ -274,6 +283,24 @@ static void decode_frame(Model &m, const Vp9CudaFrameHeader &h, const std::vecto
             int pl = r.plane, ch = pl > 0;
             int bx = r.x4 * 4, by = r.y4 * 4;
             int avail_w = ((cols * 8) >> ch) - bx, avail_h = ((rows * 8) >> ch) - by;
+            {
+                const int n = 1 << r.tx, x = r.x4, y = r.y4, w = lvw[pl], hh = lvh[pl];
+                const bool hl = r.flags & VP9CUDA_ITX_HAVE_LEFT, ht = y > 0;
+                int lv = 0;
+                if (hl)
+                    for (int j = ht ? y - 1 : y; j < std::min(y + n, hh); j++)
+                        lv = std::max(lv, lvmap[pl][(size_t)j * w + x - 1] + 1);
+                if (ht)
+                    for (int i = x; i < std::min(x + ((r.tx == 0 && (r.flags & VP9CUDA_ITX_HAVE_RIGHT)) ? 2 : n), w); i++)
+                        lv = std::max(lv, lvmap[pl][(size_t)(y - 1) * w + i] + 1);
+                if (lv != r.level) {
+                    fprintf(stderr, "level mismatch plane %d cell %d,%d: record %d, derived %d\n", pl, x, y, r.level, lv);
+                    exit(4);
+                }
+                for (int j = y; j < std::min(y + n, hh); j++)
+                    for (int i = x; i < std::min(x + n, w); i++)
+                        lvmap[pl][(size_t)j * w + i] = lv;
+            }
             intra_block(c.p[pl].data(), c.stride[pl], bx, by, r.tx, r.mode, by > 0,
                         r.flags & VP9CUDA_ITX_HAVE_LEFT, r.flags & VP9CUDA_ITX_HAVE_RIGHT,
                         avail_w, avail_h, h.bpp);

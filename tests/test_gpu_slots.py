@@ -54,8 +54,8 @@ def test_slot_intra_pred(bpp):
     want = pix.copy()
     for i, (tx, m) in enumerate(combos):
         ref.ref_intra_pred(bpp, tx, m, ptr(want[i]), C.c_ssize_t(64 * bps), ptr(left[i]), ptr(top[i], bps))
-    rc = lib.vp9cuda_slot_intra_pred(0, bpp, n, ptr(u8([c[0] for c in combos])), ptr(u8([c[1] for c in combos])),
-                                     ptr(pix), ptr(left), ptr(top))
+    txs, modes = u8([c[0] for c in combos]), u8([c[1] for c in combos])   # keep alive across the call
+    rc = lib.vp9cuda_slot_intra_pred(0, bpp, n, ptr(txs), ptr(modes), ptr(pix), ptr(left), ptr(top))
     assert rc == 0
     for i, (tx, m) in enumerate(combos):
         N = 4 << tx
@@ -85,8 +85,8 @@ def test_slot_mc(bpp):
             ref.ref_smc(bpp, hs, filt, avg, ptr(want[i]), C.c_ssize_t(64 * bps), ptr(refp[i], off), C.c_ssize_t(160 * bps), h, mx, my, dx, dy)
         else:
             ref.ref_mc(bpp, hs, filt, avg, ptr(want[i]), C.c_ssize_t(64 * bps), ptr(refp[i], off), C.c_ssize_t(160 * bps), h, mx, my)
-    col = lambda k: ptr(u8([c[k] for c in cases]))  # noqa: E731
-    rc = lib.vp9cuda_slot_mc(0, bpp, n, col(1), col(2), col(3), col(4), col(5), col(6), col(7), col(8), ptr(pix), ptr(refp))
+    cols = [u8([c[k] for c in cases]) for k in range(9)]                  # keep alive across the call
+    rc = lib.vp9cuda_slot_mc(0, bpp, n, *[ptr(cols[k]) for k in range(1, 9)], ptr(pix), ptr(refp))
     assert rc == 0
     bad = [cases[i] for i in range(n) if not np.array_equal(pix[i], want[i])]
     assert not bad, f"mc differs for {bad[:6]}"
@@ -116,9 +116,10 @@ def test_slot_loop_filter(bpp):
             ref.ref_loop_filter_16(bpp, d, ptr(want[i], off), C.c_ssize_t(64 * bps), E, I, H)
         else:
             ref.ref_loop_filter_8(bpp, wd_i, d, ptr(want[i], off), C.c_ssize_t(64 * bps), E, I, H)
-    i32 = lambda k: ptr(np.ascontiguousarray(np.asarray([c[k] for c in cases], np.int32)))  # noqa: E731
-    rc = lib.vp9cuda_slot_loop_filter(0, bpp, n, ptr(u8([c[1] for c in cases])), ptr(u8([c[2] for c in cases])),
-                                      ptr(u8([c[3] for c in cases])), i32(4), i32(5), i32(6), ptr(pix))
+    a8 = [u8([c[k] for c in cases]) for k in (1, 2, 3)]                    # keep alive across the call
+    a32 = [np.ascontiguousarray(np.asarray([c[k] for c in cases], np.int32)) for k in (4, 5, 6)]
+    rc = lib.vp9cuda_slot_loop_filter(0, bpp, n, ptr(a8[0]), ptr(a8[1]), ptr(a8[2]), ptr(a32[0]), ptr(a32[1]),
+                                      ptr(a32[2]), ptr(pix))
     assert rc == 0
     bad = [cases[i] for i in range(n) if not np.array_equal(pix[i], want[i])]
     assert not bad, f"loop filter differs for {bad[:6]}"
