@@ -231,7 +231,7 @@ def main():
         pc = ctx.phase_clocks(5)
         ctx.option("phase_clk", 0)
         tot = max(sum(pc), 1)
-        print("loop-filter CTA phase share (wait, load, cols, rows, store):",
+        print("loop-filter compute-warp phase share (wait body, Cr, wait top, R, Ce+signal):",
               [round(x / tot, 3) for x in pc], "total Mcycles", tot / 1e6, file=sys.stderr)
 
     # ---- leg 2: end to end through the C ABI with host buffers ---------------------------------

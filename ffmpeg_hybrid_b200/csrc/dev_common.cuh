@@ -46,7 +46,7 @@ struct FrameDesc {
     uint32_t *done[3];             /* per plane, per 4x4 cell: == gen when its intra block is final */
     int done_w[3], done_h[3];
     uint32_t gen;                  /* unique per reconstructed frame */
-    LfOps *lfops;                  /* [sb][plane] decoded loop-filter edge operations */
+    LfSched *lfsched;              /* [sb][plane] loop-filter edge ops sorted by dependency step */
     int *progress;                 /* [3 planes][sb_rows] loop-filter wavefront counters */
     unsigned long long *phase_clk; /* optional: per-phase clock accumulation (profiling), or NULL */
     uint8_t lim_lut[64], mblim_lut[64];

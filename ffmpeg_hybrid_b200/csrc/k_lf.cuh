@@ -1,19 +1,31 @@
 /*
- * k_lf.cuh -- K4: the VP9 loop filter as a superblock wavefront, in the reference's exact
- * edge order.
+ * k_lf.cuh -- K4: the VP9 loop filter as a superblock-row wavefront, in the reference's exact
+ * edge order, with the edges of one superblock scheduled by their true data dependencies.
  *
  * The reference filters superblock by superblock in raster order and, inside one, plane by
- * plane: every column edge, then every row edge (vp9lpf.c:222-229).  A filter reaches up to 8
- * pixels into the left and upper neighbours, so superblock (r, c) must run after (r, c-1)
- * [same CTA] and after (r-1, c+1) [whose column pass touches our upper strip]: a (left,
- * top-right) wavefront.  Planes never interact, so each plane is its own wavefront.
+ * plane: every column edge C(c), then every row edge R(c) (vp9lpf.c:222-229).  Footprints:
+ * C(c) = columns [x0-8, x0+S) x rows [y0, y0+S); R(c) = columns [x0, x0+S) x rows [y0-8, y0+S).
+ * Only the superblock's left edge reaches into the left neighbour, so C(c) = Ce(c) (edge
+ * position 0) followed by Cr(c) (the rest), and Ce(c+1) commutes with everything of superblock
+ * c+1's upper neighbours.  One CTA owns one (superblock row, plane) and runs the turns
  *
- *   k_lf : one CTA per (superblock row, plane), walking the row left to right behind the row
- *          above (progress counters in global memory).  Per superblock: stage the (S+8)x(S+8)
- *          pixel window in shared memory, decode the VP9Filter masks into an edge-op table
- *          (vp9_lf.h, a 1:1 walk of filter_plane_cols/rows, vp9lpf.c:31-181), run the column
- *          pass with one thread per pixel row (edges left to right), the row pass with one
- *          thread per pixel column (edges top to bottom), and write the window back.
+ *        U(c) = Cr(c) -> R(c) -> Ce(c+1)                       c = 0 .. sb_cols-1
+ *
+ * after which columns [x0, x0+S) are final for rows [y0-8, y0+S-8) and "handed down" for the
+ * last 8 rows.  U(c) of row r needs the hand-down of row r-1's U(c): a lag of ONE superblock
+ * between rows (the plain raster dependency needs two), so the frame's critical path is
+ * sb_cols + sb_rows turns.
+ *
+ * Inside a turn the ops are not run edge by edge: k_lf_sched (pre-pass, fully parallel) decodes
+ * the VP9Filter masks (vp9_lf.h, 1:1 walk of filter_plane_cols/rows, vp9lpf.c:31-181) and sorts
+ * each pass's ops by dependency step (LfSched); all (op, line) pairs of one step run
+ * concurrently on 256 threads, one barrier per step.
+ *
+ * Pixels live in a shared-memory ring of 4 superblock columns x (S+8) rows.  Three helper warps
+ * keep the turn free of global-memory latency: a body loader (cp.async of pre-filter pixels and
+ * the schedule, up to 3 superblocks ahead), a top loader (polls the row above's progress
+ * counter, fetches the 8 handed-down rows), and a storer (writes a finished column block back,
+ * hand-down rows first, then fence + progress counter for the row below).
  *
  * Replaces ff_vp9_loopfilter_sb (vp9lpf.c:183-230) + loop_filter_8/16/mix2 slots
  * (vp9dsp_template.c:1780-1967).  Algorithmic bytes: 2*P (read + write of the picture).
@@ -25,11 +37,13 @@
 
 namespace vp9 {
 
-#define LF_THREADS 128
+#define LF_CW 8                       /* compute warps */
+#define LF_CT (LF_CW * 32)
+#define LF_THREADS (LF_CT + 3 * 32)   /* + body loader, top loader, storer */
 
 /* pre-pass, fully parallel: one thread per (superblock, plane, direction) turns the VP9Filter
- * masks into the edge-op table the wavefront kernel consumes */
-__global__ void k_lf_ops(const __grid_constant__ FrameDesc f)
+ * masks into the step-sorted op lists the wavefront kernel consumes */
+__global__ void k_lf_sched(const __grid_constant__ FrameDesc f)
 {
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     const int n_sb = f.sb_cols * f.sb_rows;
@@ -37,135 +51,261 @@ __global__ void k_lf_ops(const __grid_constant__ FrameDesc f)
         return;
     const int sb = t / 6, pl = (t % 6) >> 1, dir = t & 1;
     const LfSb &m = *(const LfSb *)&f.lf[sb];
-    LfOps &o = f.lfops[sb * 3 + pl];
-    if (dir == 0)
+    LfOps o;
+    LfSched &out = f.lfsched[sb * 3 + pl];
+    if (dir == 0) {
         lf_decode_cols(m, pl > 0, sb % f.sb_cols == 0, o);
-    else
+        lf_schedule_dir(o, 0, out.col, out.cstart);
+    } else {
         lf_decode_rows(m, pl > 0, sb / f.sb_cols == 0, o);
+        lf_schedule_dir(o, 1, out.row, out.rstart);
+    }
 }
 
-#define LF_CLK(k) do { if (f.phase_clk && threadIdx.x == 0) { long long c_ = clock64(); \
+__device__ __forceinline__ void lf_cp16(void *smem, const void *gmem)
+{
+    unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(sa), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void lf_cp_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+template <int N> __device__ __forceinline__ void lf_cp_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
+__device__ __forceinline__ void lf_bar_compute() { asm volatile("bar.sync 1, %0;\n" ::"n"(LF_CT) : "memory"); }
+
+/* signals between the warps of one CTA (shared memory, monotonically increasing counts) */
+struct LfSig {
+    volatile int body;     /* body blocks L(0..body-1) and their schedules are in the ring */
+    volatile int top;      /* top strips T(0..top-1) are in the ring */
+    volatile int done;     /* turns U(0..done-1) are complete in the ring */
+    volatile int stored;   /* column blocks 0..stored-1 have been written back (ring slot reusable) */
+};
+
+template <class P> struct LfPix;
+template <> struct LfPix<uint16_t> {
+    typedef uint2 V;      /* 4 pixels */
+    static __device__ __forceinline__ void unpack(V v, int *px) { px[0] = v.x & 0xffff; px[1] = v.x >> 16; px[2] = v.y & 0xffff; px[3] = v.y >> 16; }
+    static __device__ __forceinline__ V pack(const int *px) { V v; v.x = px[0] | px[1] << 16; v.y = px[2] | px[3] << 16; return v; }
+};
+template <> struct LfPix<uint8_t> {
+    typedef uint32_t V;
+    static __device__ __forceinline__ void unpack(V v, int *px) { px[0] = v & 0xff; px[1] = v >> 8 & 0xff; px[2] = v >> 16 & 0xff; px[3] = v >> 24; }
+    static __device__ __forceinline__ V pack(const int *px) { return px[0] | px[1] << 8 | px[2] << 16 | px[3] << 24; }
+};
+
+#define LF_CLK(k) do { if (f.phase_clk && ctid == 0) { long long c_ = clock64(); \
     atomicAdd(&f.phase_clk[k], (unsigned long long)(c_ - clk_)); clk_ = c_; } } while (0)
 
 template <class P, int S>
-__device__ void lf_superblock(const FrameDesc &f, int pl, int sr, int sc, P *win /* (S+8)*(S+10) */, LfOps *ops,
-                              long long &clk_)
+__device__ void lf_row(const FrameDesc &f, int pl, int row, unsigned char *ring, LfSched *sched, LfSig *sig,
+                       const uint8_t *lut /* lim[64], mblim[64] */)
 {
-    constexpr int W = S + 10;               /* odd word stride: conflict-free line-per-thread access */
-    const int ch = pl > 0;
-    const int x0 = sc * S, y0 = sr * S;
+    typedef typename LfPix<P>::V V;
+    constexpr int RW = 4 * S;                           /* ring width in pixels */
+    constexpr int RSB = RW * (int)sizeof(P) + 16;       /* ring row stride in bytes (16-B aligned, 4 words mod 32) */
+    constexpr int CPR = S * (int)sizeof(P) / 16;        /* 16-byte chunks per block row */
+    constexpr int SLOT = S * (int)sizeof(P);            /* bytes per ring slot row */
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int ncol = f.sb_cols;
+    const bool has_top = row > 0;
     const int stride = f.cur.stride[pl];
     P *plane = (P *)f.cur.pl[pl];
-    (void)ch;
-    for (int i = threadIdx.x; i < (S + 8) * (S + 8); i += blockDim.x) {
-        int x = i % (S + 8) - 8, y = i / (S + 8) - 8;
-        int gx = x0 + x, gy = y0 + y;
-        P v = 0;
-        if (gx >= 0 && gy >= 0 && !(x < 0 && y < 0))
-            v = ld_cg(plane + (size_t)gy * stride + gx);
-        win[(y + 8) * W + x + 8] = v;
-    }
-    {
-        const uint32_t *src = (const uint32_t *)&f.lfops[(sr * f.sb_cols + sc) * 3 + pl];
-        uint32_t *dst = (uint32_t *)ops;
-        for (int i = threadIdx.x; i < (int)(sizeof(LfOps) / 4); i += blockDim.x)
-            dst[i] = src[i];
-    }
-    __syncthreads();
-    LF_CLK(1);
+    const int y0 = row * S;
+    int *prog = f.progress + pl * f.sb_rows;
 
-    /* column pass: thread = pixel row */
-    if (threadIdx.x < S) {
-        const int ln = threadIdx.x;
-        P *row = win + (ln + 8) * W + 8;
-#pragma unroll 1
-        for (int p = 0; p < S / 4; p++) {
-            LfOp op = ops->col[ln >> 3][p];
-            if (!op.wd)
-                continue;
-            int px[16];
-            P *e = row + 4 * p;
-            if (op.wd == 16) {
-#pragma unroll
-                for (int i = 0; i < 16; i++) px[i] = e[i - 8];
-            } else {
-#pragma unroll
-                for (int i = 4; i < 12; i++) px[i] = e[i - 8];
+    if (warp < LF_CW) {
+        /* ------------------------------- compute warps ------------------------------- */
+        const int ctid = threadIdx.x;
+        long long clk_ = clock64();
+        for (int c = 0; c < ncol; c++) {
+            if (ctid == 0) {
+                const int need = min(c + 2, ncol);
+                while (sig->body < need) { }
+                __threadfence_block();
             }
-            unsigned w = lf_line(px, op.wd, f.mblim_lut[op.L], f.lim_lut[op.L], op.L >> 4, f.bpp);
-            if (w) {
+            lf_bar_compute();
+            LF_CLK(0);
+            const LfSched &sc = sched[c & 3];
+            /* one dependency step of column ops of superblock sbi */
+            auto col_step = [&](const uint16_t *ent, int a, int b, int sbi) {
+                for (int t = ctid; t < (b - a) * 8; t += LF_CT) {
+                    const unsigned e = ent[a + (t >> 3)];
+                    const int g = e & 7, p = e >> 3 & 15, wd = 2 << (e >> 7 & 3), L = e >> 9;
+                    unsigned char *rp = ring + (8 + 8 * g + (t & 7)) * RSB;
+                    const int xb = sbi * S + 4 * p;
+                    int px[16];
+                    if (wd == 16) {
+                        LfPix<P>::unpack(*(const V *)(rp + ((xb - 8) & (RW - 1)) * sizeof(P)), px);
+                        LfPix<P>::unpack(*(const V *)(rp + ((xb + 4) & (RW - 1)) * sizeof(P)), px + 12);
+                    }
+                    LfPix<P>::unpack(*(const V *)(rp + ((xb - 4) & (RW - 1)) * sizeof(P)), px + 4);
+                    LfPix<P>::unpack(*(const V *)(rp + (xb & (RW - 1)) * sizeof(P)), px + 8);
+                    const unsigned w = lf_line(px, wd, lut[64 + L], lut[L], L >> 4, f.bpp);
+                    if (w & 0x000f) *(V *)(rp + ((xb - 8) & (RW - 1)) * sizeof(P)) = LfPix<P>::pack(px);
+                    if (w & 0x00f0) *(V *)(rp + ((xb - 4) & (RW - 1)) * sizeof(P)) = LfPix<P>::pack(px + 4);
+                    if (w & 0x0f00) *(V *)(rp + (xb & (RW - 1)) * sizeof(P)) = LfPix<P>::pack(px + 8);
+                    if (w & 0xf000) *(V *)(rp + ((xb + 4) & (RW - 1)) * sizeof(P)) = LfPix<P>::pack(px + 12);
+                }
+            };
+            /* Cr(c) */
+#pragma unroll 1
+            for (int s = 1; s < LF_NSTEP; s++) {
+                const int a = sc.cstart[s], b = sc.cstart[s + 1];
+                if (a == b)
+                    continue;
+                col_step(sc.col, a, b, c);
+                lf_bar_compute();
+            }
+            LF_CLK(1);
+            if (has_top) {
+                if (ctid == 0) {
+                    while (sig->top < c + 1) { }
+                    __threadfence_block();
+                }
+                lf_bar_compute();
+            }
+            LF_CLK(2);
+            /* R(c) */
+#pragma unroll 1
+            for (int s = 0; s < LF_NSTEP; s++) {
+                const int a = sc.rstart[s], b = sc.rstart[s + 1];
+                if (a == b)
+                    continue;
+                for (int t = ctid; t < (b - a) * 8; t += LF_CT) {
+                    const unsigned e = sc.row[a + (t >> 3)];
+                    const int cg = e & 7, ei = e >> 3 & 15, wd = 2 << (e >> 7 & 3), L = e >> 9;
+                    const int col = (c * S + 8 * cg + (t & 7)) & (RW - 1);
+                    unsigned char *cp = ring + 4 * ei * RSB + col * sizeof(P);
+                    int px[16];
+                    if (wd == 16) {
 #pragma unroll
-                for (int i = 1; i < 15; i++)
-                    if (w >> i & 1) e[i - 8] = (P)px[i];
+                        for (int i = 0; i < 16; i++) px[i] = *(const P *)(cp + i * RSB);
+                    } else {
+#pragma unroll
+                        for (int i = 4; i < 12; i++) px[i] = *(const P *)(cp + i * RSB);
+                    }
+                    const unsigned w = lf_line(px, wd, lut[64 + L], lut[L], L >> 4, f.bpp);
+                    if (w) {
+#pragma unroll
+                        for (int i = 1; i < 15; i++)
+                            if (w >> i & 1) *(P *)(cp + i * RSB) = (P)px[i];
+                    }
+                }
+                lf_bar_compute();
+            }
+            LF_CLK(3);
+            /* Ce(c+1) */
+            if (c + 1 < ncol) {
+                const LfSched &sn = sched[(c + 1) & 3];
+                const int a = sn.cstart[0], b = sn.cstart[1];
+                if (a != b) {
+                    col_step(sn.col, a, b, c + 1);
+                    lf_bar_compute();
+                }
+            }
+            if (ctid == 0) {
+                __threadfence_block();
+                sig->done = c + 1;
+            }
+            LF_CLK(4);
+        }
+    } else if (warp == LF_CW) {
+        /* ------------------------------- body loader ------------------------------- */
+        for (int j = 0; j < ncol; j++) {
+            if (j >= 4 && sig->stored < j - 3) {
+                lf_cp_wait<0>();
+                __syncwarp();
+                if (lane == 0) { __threadfence_block(); sig->body = j; }
+                while (sig->stored < j - 3) __nanosleep(20);
+            }
+            const unsigned char *src = (const unsigned char *)(plane + (size_t)y0 * stride + j * S);
+            unsigned char *dst = ring + 8 * RSB + (j & 3) * SLOT;
+#pragma unroll 4
+            for (int i = lane; i < S * CPR; i += 32) {
+                const int r = i / CPR, k = i % CPR;
+                lf_cp16(dst + r * RSB + 16 * k, src + (size_t)r * stride * sizeof(P) + 16 * k);
+            }
+            const unsigned char *ss = (const unsigned char *)&f.lfsched[(row * ncol + j) * 3 + pl];
+            unsigned char *sd = (unsigned char *)&sched[j & 3];
+            for (int i = lane; i < (int)sizeof(LfSched) / 16; i += 32)
+                lf_cp16(sd + 16 * i, ss + 16 * i);
+            lf_cp_commit();
+            lf_cp_wait<1>();
+            __syncwarp();
+            if (lane == 0) { __threadfence_block(); sig->body = j; }
+        }
+        lf_cp_wait<0>();
+        __syncwarp();
+        if (lane == 0) { __threadfence_block(); sig->body = ncol; }
+    } else if (warp == LF_CW + 1) {
+        /* ------------------------------- top loader ------------------------------- */
+        if (has_top) {
+            const volatile int *above = prog + row - 1;
+            for (int c = 0; c < ncol; c++) {
+                while (c >= 4 && sig->stored < c - 3) __nanosleep(20);
+                if (lane == 0) {
+                    while (*above < c + 1) __nanosleep(20);
+                    __threadfence();
+                }
+                __syncwarp();
+                const unsigned char *src = (const unsigned char *)(plane + (size_t)(y0 - 8) * stride + c * S);
+                unsigned char *dst = ring + (c & 3) * SLOT;
+                for (int i = lane; i < 8 * CPR; i += 32) {
+                    const int r = i / CPR, k = i % CPR;
+                    lf_cp16(dst + r * RSB + 16 * k, src + (size_t)r * stride * sizeof(P) + 16 * k);
+                }
+                lf_cp_commit();
+                lf_cp_wait<0>();
+                __syncwarp();
+                if (lane == 0) { __threadfence_block(); sig->top = c + 1; }
             }
         }
-    }
-    __syncthreads();
-    LF_CLK(2);
-    /* row pass: thread = pixel column */
-    if (threadIdx.x < S) {
-        const int ln = threadIdx.x;
-        P *colp = win + 8 * W + 8 + ln;
-#pragma unroll 1
-        for (int p = 0; p < S / 4; p++) {
-            LfOp op = ops->row[p][ln >> 3];
-            if (!op.wd)
-                continue;
-            int px[16];
-            P *e = colp + 4 * p * W;
-            if (op.wd == 16) {
-#pragma unroll
-                for (int i = 0; i < 16; i++) px[i] = e[(i - 8) * W];
-            } else {
-#pragma unroll
-                for (int i = 4; i < 12; i++) px[i] = e[(i - 8) * W];
+    } else {
+        /* ------------------------------- storer ------------------------------- */
+        for (int c = 0; c < ncol; c++) {
+            while (sig->done < c + 1) __nanosleep(20);
+            __threadfence_block();
+            unsigned char *dst = (unsigned char *)(plane + (size_t)(y0 - 8) * stride + c * S);
+            const unsigned char *src = ring + (c & 3) * SLOT;
+            auto store_rows = [&](int r0, int r1) {
+#pragma unroll 4
+                for (int i = lane + r0 * CPR; i < r1 * CPR; i += 32) {
+                    const int r = i / CPR, k = i % CPR;
+                    *(uint4 *)(dst + (ptrdiff_t)r * stride * (int)sizeof(P) + 16 * k) = *(const uint4 *)(src + r * RSB + 16 * k);
+                }
+            };
+            store_rows(S, S + 8);           /* the rows handed down to the next superblock row */
+            __syncwarp();
+            if (lane == 0) {
+                __threadfence();
+                *(volatile int *)(prog + row) = c + 1;
             }
-            unsigned w = lf_line(px, op.wd, f.mblim_lut[op.L], f.lim_lut[op.L], op.L >> 4, f.bpp);
-            if (w) {
-#pragma unroll
-                for (int i = 1; i < 15; i++)
-                    if (w >> i & 1) e[(i - 8) * W] = (P)px[i];
-            }
+            store_rows(has_top ? 0 : 8, S);
+            __syncwarp();
+            if (lane == 0)
+                sig->stored = c + 1;
         }
-    }
-    __syncthreads();
-    LF_CLK(3);
-    for (int i = threadIdx.x; i < (S + 8) * (S + 8); i += blockDim.x) {
-        int x = i % (S + 8) - 8, y = i / (S + 8) - 8;
-        int gx = x0 + x, gy = y0 + y;
-        if (gx >= 0 && gy >= 0 && !(x < 0 && y < 0))
-            plane[(size_t)gy * stride + gx] = win[(y + 8) * W + x + 8];
     }
 }
 
 template <class P>
 __global__ void __launch_bounds__(LF_THREADS) k_lf(const __grid_constant__ FrameDesc f)
 {
-    __shared__ P win[72 * 74];
-    __shared__ LfOps ops;
+    __shared__ __align__(16) unsigned char ring[72 * (256 * sizeof(P) + 16)];
+    __shared__ __align__(16) LfSched sched[4];
+    __shared__ LfSig sig;
+    __shared__ uint8_t lut[128];
     const int pl = blockIdx.x % 3, row = blockIdx.x / 3;
-    int *prog = f.progress + pl * f.sb_rows;
-    long long clk_ = clock64();
-    for (int c = 0; c < f.sb_cols; c++) {
-        if (row > 0 && threadIdx.x == 0) {
-            const int need = min(c + 2, f.sb_cols);
-            volatile int *above = prog + row - 1;
-            while (*above < need)
-                __nanosleep(100);
-            __threadfence();
-        }
-        __syncthreads();
-        LF_CLK(0);
-        if (pl == 0)
-            lf_superblock<P, 64>(f, pl, row, c, win, &ops, clk_);
-        else
-            lf_superblock<P, 32>(f, pl, row, c, win, &ops, clk_);
-        __threadfence();
-        __syncthreads();
-        if (threadIdx.x == 0)
-            atomicExch(prog + row, c + 1);
-        LF_CLK(4);
+    if (threadIdx.x == 0) {
+        sig.body = 0; sig.top = 0; sig.done = 0; sig.stored = 0;
     }
+    if (threadIdx.x < 64) {
+        lut[threadIdx.x] = f.lim_lut[threadIdx.x];
+        lut[64 + threadIdx.x] = f.mblim_lut[threadIdx.x];
+    }
+    __syncthreads();
+    if (pl == 0)
+        lf_row<P, 64>(f, pl, row, ring, sched, &sig, lut);
+    else
+        lf_row<P, 32>(f, pl, row, ring, sched, &sig, lut);
 }
 
 } /* namespace vp9 */

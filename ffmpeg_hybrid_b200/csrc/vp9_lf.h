@@ -226,5 +226,71 @@ VP9_HD void lf_decode_rows(const LfSb &f, bool chroma, bool first_row, LfOps &op
     }
 }
 
+/*
+ * Dependency schedule of one superblock plane's edge ops.
+ *
+ * The reference applies the ops of one 8-line group strictly in increasing edge position
+ * (vp9lpf.c:59-106 / :131-180).  Two ops of the same group commute exactly when the pixel
+ * ranges they READ are disjoint (a filter never writes outside what it reads): read range of an
+ * op at position X is [X-8, X+8) for wd 16 and [X-4, X+4) otherwise.  `step` of an op is the
+ * length of the longest chain of non-commuting earlier ops in its group, so all ops of equal
+ * step (any group) may run concurrently and steps run in increasing order.  Typical content
+ * (uniform 8x8 / 16x16 / 32x32 transform areas) needs 1-3 steps per pass instead of 16.
+ *
+ * Column ops at position 0 (the superblock's left edge, reaching 8 pixels into the left
+ * neighbour) always get step 0 and every other column op a step >= 1, so the wavefront kernel
+ * can run "step 0 of superblock c+1" as the tail of superblock c's turn.
+ *
+ * Entry: bits 0-2 group (col: 8-row group, row: 8-column group), 3-6 edge index (position / 4),
+ * 7-8 width code (1,2,3 = 4,8,16), 9-14 level.  Entries are sorted by step;
+ * cstart/rstart[s] is the first entry of step s, [LF_NSTEP] the total.
+ */
+#define LF_NSTEP 17
+struct LfSched {
+    uint16_t col[128], row[128];
+    uint8_t cstart[LF_NSTEP + 1], rstart[LF_NSTEP + 1];
+    uint8_t pad[28];
+};
+
+VP9_HD uint16_t lf_ent(int grp, int e, const LfOp &o)
+{
+    return (uint16_t)(grp | e << 3 | (o.wd == 16 ? 3 : o.wd == 8 ? 2 : 1) << 7 | (o.L & 63) << 9);
+}
+
+/* dir 0: column ops (o.col[g][p]); dir 1: row ops (o.row[e][c]) */
+VP9_HD void lf_schedule_dir(const LfOps &o, int dir, uint16_t *ent, uint8_t *start)
+{
+    uint8_t step[8][16];
+    uint8_t cnt[LF_NSTEP + 1];
+    for (int s = 0; s <= LF_NSTEP; s++) cnt[s] = 0;
+    for (int g = 0; g < 8; g++)
+        for (int p = 0; p < 16; p++) {
+            const LfOp &op = dir ? o.row[p][g] : o.col[g][p];
+            step[g][p] = 0xff;
+            if (!op.wd)
+                continue;
+            const int lo = 4 * p - (op.wd == 16 ? 8 : 4);
+            int s = (dir == 0 && p > 0) ? 1 : 0;
+            for (int q = p > 3 ? p - 3 : 0; q < p; q++) {
+                const LfOp &pr = dir ? o.row[q][g] : o.col[g][q];
+                if (pr.wd && 4 * q + (pr.wd == 16 ? 8 : 4) > lo && step[g][q] + 1 > s)
+                    s = step[g][q] + 1;
+            }
+            step[g][p] = (uint8_t)s;
+            cnt[s]++;
+        }
+    int acc = 0;
+    for (int s = 0; s <= LF_NSTEP; s++) {
+        int n = cnt[s];
+        start[s] = (uint8_t)acc;
+        cnt[s] = (uint8_t)acc;
+        acc += n;
+    }
+    for (int g = 0; g < 8; g++)
+        for (int p = 0; p < 16; p++)
+            if (step[g][p] != 0xff)
+                ent[cnt[step[g][p]]++] = lf_ent(g, p, dir ? o.row[p][g] : o.col[g][p]);
+}
+
 } /* namespace vp9 */
 #endif /* VP9_LF_H */

@@ -279,7 +279,7 @@ static int upload_records(Vp9CudaCtx *c, DevRecords &d, const Vp9CudaFrameHeader
     r |= d.ilvl_hist.reserve((size_t)ILVL_MAX * 4);
     r |= d.iorder.reserve(n_itx * 4);
     r |= d.icounter.reserve(64);
-    r |= d.lfops.reserve((size_t)n_sb * 3 * sizeof(LfOps));
+    r |= d.lfops.reserve((size_t)n_sb * 3 * sizeof(LfSched));
     r |= d.progress.reserve((size_t)3 * sb_rows * 4);
     if (r)
         return -ENOMEM;
@@ -362,8 +362,8 @@ static int launch_frame(Vp9CudaCtx *c, const FrameDesc &f, const DevRecords &d)
     }
     if (f.lf_level) {
         kstat_begin(c);
-        k_lf_ops<<<(f.sb_cols * f.sb_rows * 6 + 127) / 128, 128, 0, s>>>(f);
-        kstat_end(c, KS_LFOPS, 1, (uint64_t)f.sb_cols * f.sb_rows * (sizeof(Vp9CudaLoopFilterSb) + 3 * sizeof(LfOps)));
+        k_lf_sched<<<(f.sb_cols * f.sb_rows * 6 + 63) / 64, 64, 0, s>>>(f);
+        kstat_end(c, KS_LFOPS, 1, (uint64_t)f.sb_cols * f.sb_rows * (sizeof(Vp9CudaLoopFilterSb) + 3 * sizeof(LfSched)));
         kstat_begin(c);
         CK(cudaMemsetAsync(f.progress, 0, (size_t)3 * f.sb_rows * 4, s));
         k_lf<P><<<3 * f.sb_rows, LF_THREADS, 0, s>>>(f);
@@ -436,7 +436,7 @@ static int reconstruct(Vp9CudaCtx *c, DevRecords &d, uint8_t *const out_planes[3
     f.ilvl_hist = (uint32_t *)d.ilvl_hist.p;
     f.iorder = (uint32_t *)d.iorder.p;
     f.icounter = (uint32_t *)d.icounter.p;
-    f.lfops = (LfOps *)d.lfops.p;
+    f.lfsched = (LfSched *)d.lfops.p;
     f.progress = (int *)d.progress.p;
     f.gen = ++c->gen;
     for (int p = 0; p < 3; p++) {

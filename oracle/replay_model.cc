@@ -489,4 +489,73 @@ void model_lf_decode(const uint8_t *vp9filter /* 192 bytes */, int chroma, int f
         for (int c = 0; c < 8; c++) { row_wd[e * 8 + c] = ops.row[e][c].wd; row_L[e * 8 + c] = ops.row[e][c].L; }
 }
 
+/* Test hook for the dependency schedule (vp9_lf.h: lf_schedule_dir): filters one superblock plane
+ * of seeded pixels (a) in the reference's sequential edge order and (b) step by step in schedule
+ * order, within a step in REVERSE list order; returns the number of differing pixels, or -1 if the
+ * schedule is malformed (entry count, step-0 rule for column position 0). */
+int model_lf_sched_check(const uint8_t *vp9filter, int chroma, int first_col, int first_row, unsigned seed,
+                         int bpp, int *n_steps_out)
+{
+    LfSb sb = *(const LfSb *)vp9filter;
+    for (int i = 0; i < 64; i++) sb.level[i] &= 63;
+    LfOps ops;
+    lf_decode_cols(sb, chroma, first_col, ops);
+    lf_decode_rows(sb, chroma, first_row, ops);
+    LfSched sc;
+    lf_schedule_dir(ops, 0, sc.col, sc.cstart);
+    lf_schedule_dir(ops, 1, sc.row, sc.rstart);
+    uint8_t lim[64], mblim[64];
+    for (int L = 0; L < 64; L++) {          /* sharpness 0 luts, vp9.c:673-686 */
+        int l = L < 1 ? 1 : L;
+        lim[L] = l; mblim[L] = 2 * (L + 2) + l;
+    }
+    const int W = 96, S = chroma ? 32 : 64;
+    std::vector<uint16_t> a(W * W), b;
+    unsigned st = seed * 2654435761u + 12345u;
+    int v = 1 << (bpp - 1);
+    for (int i = 0; i < W * W; i++) {
+        st = st * 1664525u + 1013904223u;
+        int r = st >> 24;
+        v += (r & 0x80) ? ((r & 0x7f) % 3) - 1 : ((r & 0x7f) % 41) - 20;   /* flat runs + jumps */
+        if (v < 0) v = 0;
+        if (v > (1 << bpp) - 1) v = (1 << bpp) - 1;
+        a[i] = (uint16_t)v;
+    }
+    b = a;
+    lf_apply(a.data(), W, 16, 16, chroma, ops, false, lim, mblim, bpp);
+    lf_apply(a.data(), W, 16, 16, chroma, ops, true, lim, mblim, bpp);
+    int n_ops[2] = { 0, 0 };
+    for (int g = 0; g < 8; g++)
+        for (int p = 0; p < 16; p++) { n_ops[0] += ops.col[g][p].wd != 0; n_ops[1] += ops.row[p][g].wd != 0; }
+    if (sc.cstart[LF_NSTEP] != n_ops[0] || sc.rstart[LF_NSTEP] != n_ops[1])
+        return -1;
+    int steps = 0;
+    for (int dir = 0; dir < 2; dir++) {
+        const uint16_t *ent = dir ? sc.row : sc.col;
+        const uint8_t *start = dir ? sc.rstart : sc.cstart;
+        for (int s = 0; s < LF_NSTEP; s++) {
+            if (start[s + 1] > start[s]) steps++;
+            for (int k = start[s + 1] - 1; k >= start[s]; k--) {
+                int e = ent[k], g = e & 7, p = e >> 3 & 15, wd = 2 << (e >> 7 & 3), L = e >> 9;
+                const LfOp &ref = dir ? ops.row[p][g] : ops.col[g][p];
+                if (ref.wd != wd || ref.L != L) return -1;
+                if (!dir && ((p == 0) != (s == 0))) return -1;
+                for (int ln = 0; ln < 8; ln++) {
+                    int ex = dir ? 16 + 8 * g + ln : 16 + 4 * p, ey = dir ? 16 + 4 * p : 16 + 8 * g + ln;
+                    int sx = dir ? 0 : 1, sy = dir ? 1 : 0, px[16];
+                    for (int i = 0; i < 16; i++) px[i] = b[(ey + (i - 8) * sy) * W + ex + (i - 8) * sx];
+                    unsigned m = lf_line(px, wd, mblim[L], lim[L], L >> 4, bpp);
+                    for (int i = 0; i < 16; i++)
+                        if (m >> i & 1) b[(ey + (i - 8) * sy) * W + ex + (i - 8) * sx] = px[i];
+                }
+            }
+        }
+    }
+    (void)S;
+    if (n_steps_out) *n_steps_out = steps;
+    int diff = 0;
+    for (int i = 0; i < W * W; i++) diff += a[i] != b[i];
+    return diff;
+}
+
 } /* extern "C" */

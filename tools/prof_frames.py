@@ -40,7 +40,7 @@ def main():
         print(f"{i:4d} {frames[i].w:5d} {frames[i].h:4d} {len(itx):6d} {nlv:6d} " + " ".join(f"{st[k]['ms']:10.3f}" for k in names))
     pc = ctx.phase_clocks(5)
     tot = max(sum(pc), 1)
-    print("loop-filter CTA phase share (wait, load, cols, rows, store):", [round(x / tot, 3) for x in pc])
+    print("loop-filter compute-warp phase share (wait body, Cr, wait top, R, Ce+signal):", [round(x / tot, 3) for x in pc])
     ctx.close()
 
 
