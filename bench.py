@@ -228,11 +228,10 @@ def main():
     if os.environ.get("VP9CUDA_PHASE"):
         ctx.option("phase_clk", 1)
         ctx.wait(step_resident())
-        pc = ctx.phase_clocks(5)
+        pc = ctx.phase_clocks(10)
         ctx.option("phase_clk", 0)
-        tot = max(sum(pc), 1)
-        print("loop-filter compute-warp phase share (wait body, Cr, wait top, R, Ce+signal):",
-              [round(x / tot, 3) for x in pc], "total Mcycles", tot / 1e6, file=sys.stderr)
+        print("loop-filter compute-warp cycles (wait body, Cr, wait top, R, Ce+signal) luma:", pc[:5],
+              "chroma:", pc[5:], file=sys.stderr)
 
     # ---- leg 2: end to end through the C ABI with host buffers ---------------------------------
     def step_e2e():

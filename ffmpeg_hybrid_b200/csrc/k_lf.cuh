@@ -41,24 +41,105 @@ namespace vp9 {
 #define LF_CT (LF_CW * 32)
 #define LF_THREADS (LF_CT + 3 * 32)   /* + body loader, top loader, storer */
 
-/* pre-pass, fully parallel: one thread per (superblock, plane, direction) turns the VP9Filter
- * masks into the step-sorted op lists the wavefront kernel consumes */
-__global__ void k_lf_sched(const __grid_constant__ FrameDesc f)
+/* pre-pass, fully parallel: one CTA per superblock, one warp per (plane, direction).  Four lanes
+ * decode the VP9Filter masks (two 8-line groups each), eight lanes compute the dependency steps
+ * of their group (same rule as lf_schedule_dir, vp9_lf.h), then the warp sorts the ops by
+ * (step, width) with a shared-memory histogram.  Equal-width ops sit together inside a step so
+ * the warps of the wavefront kernel diverge less. */
+#define LF_SCHED_THREADS 192
+__global__ void __launch_bounds__(LF_SCHED_THREADS) k_lf_sched(const __grid_constant__ FrameDesc f)
 {
-    const int t = blockIdx.x * blockDim.x + threadIdx.x;
-    const int n_sb = f.sb_cols * f.sb_rows;
-    if (t >= n_sb * 6)
-        return;
-    const int sb = t / 6, pl = (t % 6) >> 1, dir = t & 1;
-    const LfSb &m = *(const LfSb *)&f.lf[sb];
-    LfOps o;
+    __shared__ LfSb m;
+    __shared__ uint16_t ent[6][128];
+    __shared__ uint8_t key[6][128];
+    __shared__ int hist[6][72];
+    const int sb = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int pl = warp >> 1, dir = warp & 1;
+    if (threadIdx.x < 48)
+        ((uint32_t *)&m)[threadIdx.x] = ((const uint32_t *)&f.lf[sb])[threadIdx.x];
+    for (int i = threadIdx.x; i < 6 * 72; i += LF_SCHED_THREADS)
+        (&hist[0][0])[i] = 0;
+    __syncthreads();
+    if (lane < 4) {
+        LfOp o1[16], o2[16];
+        if (dir == 0)
+            lf_decode_cols_it(m, pl > 0, sb % f.sb_cols == 0, lane, o1, o2);
+        else
+            lf_decode_rows_j(m, pl > 0, sb / f.sb_cols == 0, lane, o1, o2);
+#pragma unroll
+        for (int p = 0; p < 16; p++) {
+            ent[warp][(2 * lane) * 16 + p] = o1[p].wd ? lf_ent(2 * lane, p, o1[p]) : 0;
+            ent[warp][(2 * lane + 1) * 16 + p] = o2[p].wd ? lf_ent(2 * lane + 1, p, o2[p]) : 0;
+        }
+    }
+    __syncwarp();
+    if (lane < 8) {
+        int st[16];
+#pragma unroll
+        for (int p = 0; p < 16; p++) {
+            const unsigned e = ent[warp][lane * 16 + p];
+            st[p] = -1;
+            int k = 0xff;
+            if (e) {
+                const int wc = e >> 7 & 3, lo = 4 * p - (wc == 3 ? 8 : 4);
+                int s = (dir == 0 && p > 0) ? 1 : 0;
+#pragma unroll
+                for (int q = (p > 3 ? p - 3 : 0); q < p; q++) {
+                    const unsigned eq = ent[warp][lane * 16 + q];
+                    if (eq && 4 * q + ((eq >> 7 & 3) == 3 ? 8 : 4) > lo && st[q] + 1 > s)
+                        s = st[q] + 1;
+                }
+                st[p] = s;
+                k = s * 4 + wc;
+            }
+            key[warp][lane * 16 + p] = (uint8_t)k;
+        }
+    }
+    __syncwarp();
+    int pos[4], kk[4];
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        kk[i] = key[warp][4 * lane + i];
+        pos[i] = kk[i] != 0xff ? atomicAdd(&hist[warp][kk[i]], 1) : 0;
+    }
+    __syncwarp();
+    {
+        /* exclusive scan of hist[warp][0..71], 3 keys per lane (lanes 0..23) */
+        int c0 = 0, c1 = 0, c2 = 0;
+        if (lane < 24) { c0 = hist[warp][3 * lane]; c1 = hist[warp][3 * lane + 1]; c2 = hist[warp][3 * lane + 2]; }
+        int tot = c0 + c1 + c2, inc = tot;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            int v = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += v;
+        }
+        __syncwarp();
+        if (lane < 24) {
+            int base = inc - tot;
+            hist[warp][3 * lane] = base;
+            hist[warp][3 * lane + 1] = base + c0;
+            hist[warp][3 * lane + 2] = base + c0 + c1;
+        }
+    }
+    __syncwarp();
     LfSched &out = f.lfsched[sb * 3 + pl];
-    if (dir == 0) {
-        lf_decode_cols(m, pl > 0, sb % f.sb_cols == 0, o);
-        lf_schedule_dir(o, 0, out.col, out.cstart);
-    } else {
-        lf_decode_rows(m, pl > 0, sb / f.sb_cols == 0, o);
-        lf_schedule_dir(o, 1, out.row, out.rstart);
+    uint16_t *oe = dir ? out.row : out.col;
+    uint8_t *os = dir ? out.rstart : out.cstart;
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+        if (kk[i] != 0xff)
+            oe[hist[warp][kk[i]] + pos[i]] = ent[warp][4 * lane + i];
+    if (lane <= LF_NSTEP)
+        os[lane] = (uint8_t)hist[warp][4 * lane];
+    /* steps are contiguous (an op of step s has a predecessor of step s-1): store the range */
+    int top = -1;
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+        if (kk[i] != 0xff && (kk[i] >> 2) > top) top = kk[i] >> 2;
+    top = __reduce_max_sync(0xffffffffu, top);
+    if (lane == 0) {
+        if (dir) out.rmax = (uint8_t)(top + 1);
+        else     out.cmax = (uint8_t)(top < 0 ? 0 : top);
     }
 }
 
@@ -92,7 +173,7 @@ template <> struct LfPix<uint8_t> {
 };
 
 #define LF_CLK(k) do { if (f.phase_clk && ctid == 0) { long long c_ = clock64(); \
-    atomicAdd(&f.phase_clk[k], (unsigned long long)(c_ - clk_)); clk_ = c_; } } while (0)
+    atomicAdd(&f.phase_clk[(k) + (S == 64 ? 0 : 5)], (unsigned long long)(c_ - clk_)); clk_ = c_; } } while (0)
 
 template <class P, int S>
 __device__ void lf_row(const FrameDesc &f, int pl, int row, unsigned char *ring, LfSched *sched, LfSig *sig,
@@ -147,10 +228,9 @@ __device__ void lf_row(const FrameDesc &f, int pl, int row, unsigned char *ring,
             };
             /* Cr(c) */
 #pragma unroll 1
-            for (int s = 1; s < LF_NSTEP; s++) {
+            const int cmax = sc.cmax, rmax = sc.rmax;
+            for (int s = 1; s <= cmax; s++) {
                 const int a = sc.cstart[s], b = sc.cstart[s + 1];
-                if (a == b)
-                    continue;
                 col_step(sc.col, a, b, c);
                 lf_bar_compute();
             }
@@ -165,10 +245,8 @@ __device__ void lf_row(const FrameDesc &f, int pl, int row, unsigned char *ring,
             LF_CLK(2);
             /* R(c) */
 #pragma unroll 1
-            for (int s = 0; s < LF_NSTEP; s++) {
+            for (int s = 0; s < rmax; s++) {
                 const int a = sc.rstart[s], b = sc.rstart[s + 1];
-                if (a == b)
-                    continue;
                 for (int t = ctid; t < (b - a) * 8; t += LF_CT) {
                     const unsigned e = sc.row[a + (t >> 3)];
                     const int cg = e & 7, ei = e >> 3 & 15, wd = 2 << (e >> 7 & 3), L = e >> 9;

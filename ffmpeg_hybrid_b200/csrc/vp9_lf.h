@@ -22,7 +22,10 @@ namespace vp9 {
 
 /* px[0..15] = p7..p0, q0..q7 across the edge (only px[4..11] are read for wd < 16).
  * Returns a bit mask of modified entries (bit i = px[i] written).
- * E, I, H are the 8-bit-domain thresholds (mblim_lut[L], lim_lut[L], L >> 4). */
+ * E, I, H are the 8-bit-domain thresholds (mblim_lut[L], lim_lut[L], L >> 4).
+ * Same decisions and outputs as loop_filter() (vp9dsp_template.c:1780-1888); the 15- and 7-tap
+ * smoothers are evaluated as running window sums (each output's window is the previous one
+ * shifted by a pixel, ends replicated), which is the same integer sum the reference spells out. */
 VP9_HD unsigned lf_line(int *px, int wd, int E, int I, int H, int bpp)
 {
     const int sh = bpp - 8, F = 1 << sh;
@@ -30,72 +33,75 @@ VP9_HD unsigned lf_line(int *px, int wd, int E, int I, int H, int bpp)
     const int p3 = px[4], p2 = px[5], p1 = px[6], p0 = px[7];
     const int q0 = px[8], q1 = px[9], q2 = px[10], q3 = px[11];
 #define VP9_ABS(v) ((v) < 0 ? -(v) : (v))
-    bool fm = VP9_ABS(p3 - p2) <= I && VP9_ABS(p2 - p1) <= I && VP9_ABS(p1 - p0) <= I &&
-              VP9_ABS(q1 - q0) <= I && VP9_ABS(q2 - q1) <= I && VP9_ABS(q3 - q2) <= I &&
-              VP9_ABS(p0 - q0) * 2 + (VP9_ABS(p1 - q1) >> 1) <= E;
-    if (!fm)
+#define VP9_MAX(a, b) ((a) > (b) ? (a) : (b))
+    const int a_p1p0 = VP9_ABS(p1 - p0), a_q1q0 = VP9_ABS(q1 - q0);
+    int m = VP9_MAX(VP9_ABS(p3 - p2), VP9_ABS(p2 - p1));
+    int m2 = VP9_MAX(VP9_ABS(q2 - q1), VP9_ABS(q3 - q2));
+    m = VP9_MAX(m, a_p1p0); m2 = VP9_MAX(m2, a_q1q0);
+    m = VP9_MAX(m, m2);
+    if (m > I || VP9_ABS(p0 - q0) * 2 + (VP9_ABS(p1 - q1) >> 1) > E)
         return 0;
-    bool flat8out = false, flat8in = false;
-    if (wd >= 16) {
-        flat8out = VP9_ABS(px[0] - p0) <= F && VP9_ABS(px[1] - p0) <= F &&
-                   VP9_ABS(px[2] - p0) <= F && VP9_ABS(px[3] - p0) <= F &&
-                   VP9_ABS(px[12] - q0) <= F && VP9_ABS(px[13] - q0) <= F &&
-                   VP9_ABS(px[14] - q0) <= F && VP9_ABS(px[15] - q0) <= F;
-    }
-    if (wd >= 8)
-        flat8in = VP9_ABS(p3 - p0) <= F && VP9_ABS(p2 - p0) <= F && VP9_ABS(p1 - p0) <= F &&
-                  VP9_ABS(q1 - q0) <= F && VP9_ABS(q2 - q0) <= F && VP9_ABS(q3 - q0) <= F;
-    if (wd >= 16 && flat8out && flat8in) {
-        /* 15-tap: out[i] (i = 1..14) = (sum of the 15 inputs centred on i with the ends
-         * replicated, centre counted twice + 8) >> 4 */
-        int v[16];
-#pragma unroll
-        for (int i = 0; i < 16; i++) v[i] = px[i];
-#pragma unroll
-        for (int i = 1; i <= 14; i++) {
-            int s = v[i] + 8;
-#pragma unroll
-            for (int k = -7; k <= 7; k++) {
-                int j = i + k;
-                j = j < 0 ? 0 : (j > 15 ? 15 : j);
-                s += v[j];
+    if (wd >= 8) {
+        int fi = VP9_MAX(VP9_ABS(p3 - p0), VP9_ABS(p2 - p0));
+        int fi2 = VP9_MAX(VP9_ABS(q2 - q0), VP9_ABS(q3 - q0));
+        fi = VP9_MAX(fi, a_p1p0); fi2 = VP9_MAX(fi2, a_q1q0);
+        if (VP9_MAX(fi, fi2) <= F) {
+            if (wd >= 16) {
+                int fo = VP9_MAX(VP9_ABS(px[0] - p0), VP9_ABS(px[1] - p0));
+                int fo2 = VP9_MAX(VP9_ABS(px[2] - p0), VP9_ABS(px[3] - p0));
+                int fo3 = VP9_MAX(VP9_ABS(px[12] - q0), VP9_ABS(px[13] - q0));
+                int fo4 = VP9_MAX(VP9_ABS(px[14] - q0), VP9_ABS(px[15] - q0));
+                fo = VP9_MAX(fo, fo2); fo3 = VP9_MAX(fo3, fo4);
+                if (VP9_MAX(fo, fo3) <= F) {
+                    /* 15-tap: out[i] = (sum_{k=-7..7} v[clamp(i+k, 0, 15)] + v[i] + 8) >> 4, i = 1..14 */
+                    const int v0 = px[0], v1 = px[1], v2 = px[2], v3 = px[3], v12 = px[12], v13 = px[13],
+                              v14 = px[14], v15 = px[15];
+                    int s = 7 * v0 + 2 * v1 + v2 + v3 + p3 + p2 + p1 + p0 + q0 + 8;
+                    px[1] = s >> 4;  s += v2 - v1 + q1 - v0;
+                    px[2] = s >> 4;  s += v3 - v2 + q2 - v0;
+                    px[3] = s >> 4;  s += p3 - v3 + q3 - v0;
+                    px[4] = s >> 4;  s += p2 - p3 + v12 - v0;
+                    px[5] = s >> 4;  s += p1 - p2 + v13 - v0;
+                    px[6] = s >> 4;  s += p0 - p1 + v14 - v0;
+                    px[7] = s >> 4;  s += q0 - p0 + v15 - v0;
+                    px[8] = s >> 4;  s += q1 - q0 + v15 - v1;
+                    px[9] = s >> 4;  s += q2 - q1 + v15 - v2;
+                    px[10] = s >> 4; s += q3 - q2 + v15 - v3;
+                    px[11] = s >> 4; s += v12 - q3 + v15 - p3;
+                    px[12] = s >> 4; s += v13 - v12 + v15 - p2;
+                    px[13] = s >> 4; s += v14 - v13 + v15 - p1;
+                    px[14] = s >> 4;
+                    return 0x7FFE;
+                }
             }
-            px[i] = s >> 4;
+            /* 7-tap: out[i] = (sum_{k=-3..3} w[clamp(i+k, 0, 7)] + w[i] + 4) >> 3 over w = p3..q3 */
+            int s = 3 * p3 + 2 * p2 + p1 + p0 + q0 + 4;
+            px[5] = s >> 3;  s += p1 - p2 + q1 - p3;
+            px[6] = s >> 3;  s += p0 - p1 + q2 - p3;
+            px[7] = s >> 3;  s += q0 - p0 + q3 - p3;
+            px[8] = s >> 3;  s += q1 - q0 + q3 - p2;
+            px[9] = s >> 3;  s += q2 - q1 + q3 - p1;
+            px[10] = s >> 3;
+            return 0x07E0;
         }
-        return 0x7FFE;
-    }
-    if (wd >= 8 && flat8in) {
-        px[5]  = (p3 + p3 + p3 + 2 * p2 + p1 + p0 + q0 + 4) >> 3;
-        px[6]  = (p3 + p3 + p2 + 2 * p1 + p0 + q0 + q1 + 4) >> 3;
-        px[7]  = (p3 + p2 + p1 + 2 * p0 + q0 + q1 + q2 + 4) >> 3;
-        px[8]  = (p2 + p1 + p0 + 2 * q0 + q1 + q2 + q3 + 4) >> 3;
-        px[9]  = (p1 + p0 + q0 + 2 * q1 + q2 + q3 + q3 + 4) >> 3;
-        px[10] = (p0 + q0 + q1 + 2 * q2 + q3 + q3 + q3 + 4) >> 3;
-        return 0x07E0;
     }
     {
         const int lim_hi = (1 << (bpp - 1)) - 1, lim_lo = -(1 << (bpp - 1));
-        bool hev = VP9_ABS(p1 - p0) > H || VP9_ABS(q1 - q0) > H;
-        if (hev) {
-            int f = iclamp(p1 - q1, lim_lo, lim_hi);
-            f = iclamp(3 * (q0 - p0) + f, lim_lo, lim_hi);
-            int f1 = (f + 4 < lim_hi ? f + 4 : lim_hi) >> 3;
-            int f2 = (f + 3 < lim_hi ? f + 3 : lim_hi) >> 3;
-            px[7] = clip_pixel(p0 + f2, bpp);
-            px[8] = clip_pixel(q0 - f1, bpp);
+        const bool hev = a_p1p0 > H || a_q1q0 > H;
+        int f = hev ? iclamp(p1 - q1, lim_lo, lim_hi) : 0;
+        f = iclamp(3 * (q0 - p0) + f, lim_lo, lim_hi);
+        const int f1 = (f + 4 < lim_hi ? f + 4 : lim_hi) >> 3;
+        const int f2 = (f + 3 < lim_hi ? f + 3 : lim_hi) >> 3;
+        px[7] = clip_pixel(p0 + f2, bpp);
+        px[8] = clip_pixel(q0 - f1, bpp);
+        if (hev)
             return 0x0180;
-        } else {
-            int f = iclamp(3 * (q0 - p0), lim_lo, lim_hi);
-            int f1 = (f + 4 < lim_hi ? f + 4 : lim_hi) >> 3;
-            int f2 = (f + 3 < lim_hi ? f + 3 : lim_hi) >> 3;
-            px[7] = clip_pixel(p0 + f2, bpp);
-            px[8] = clip_pixel(q0 - f1, bpp);
-            f = (f1 + 1) >> 1;
-            px[6] = clip_pixel(p1 + f, bpp);
-            px[9] = clip_pixel(q1 - f, bpp);
-            return 0x03C0;
-        }
+        f = (f1 + 1) >> 1;
+        px[6] = clip_pixel(p1 + f, bpp);
+        px[9] = clip_pixel(q1 - f, bpp);
+        return 0x03C0;
     }
+#undef VP9_MAX
 #undef VP9_ABS
 }
 
@@ -123,105 +129,122 @@ struct LfOps {
 
 VP9_HD void lf_set(LfOp &o, int wd, int L) { o.wd = (uint8_t)wd; o.L = (uint8_t)L; }
 
-/* filter_plane_cols, vp9lpf.c:31-107.  first_col: superblock is at the frame's left edge. */
-VP9_HD void lf_decode_cols(const LfSb &f, bool chroma, bool first_col, LfOps &ops)
+/* One iteration `it` of filter_plane_cols' outer loop (vp9lpf.c:31-107): the column ops of the two
+ * 8-line groups 2*it (o1) and 2*it+1 (o2), indexed by edge position / 4.
+ * first_col: superblock is at the frame's left edge. */
+VP9_HD void lf_decode_cols_it(const LfSb &f, bool chroma, bool first_col, int it, LfOp *o1, LfOp *o2)
 {
     const int ss = chroma ? 1 : 0;
     const uint8_t (*mask)[4] = f.mask[ss][0];
-    for (int g = 0; g < 8; g++)
-        for (int p = 0; p < 16; p++)
-            lf_set(ops.col[g][p], 0, 0);
-    int it = 0;
-    for (int y = 0; y < 8; y += 2 << ss, it++) {
-        const uint8_t *h1 = mask[y], *h2 = mask[y + 1 + ss];
-        const uint8_t *lvl = f.level + it * (16 << ss);
-        unsigned hm1 = h1[0] | h1[1] | h1[2], hm13 = h1[3];
-        unsigned hm2 = h2[1] | h2[2], hm23 = h2[3];
-        unsigned hm = hm1 | hm2 | hm13 | hm23;
-        int g1 = 2 * it, g2 = 2 * it + 1;   /* 8-line groups of the two halves */
-        int loff = 0;
-        for (int b = 0; b < 8 && (hm & ~((1u << b) - 1)); b++) {
-            unsigned x = 1u << b;
-            const uint8_t *l = lvl + loff;
-            int pm = chroma ? b : 2 * b;     /* position index of the main edge */
-            if (!first_col || b > 0) {
-                if (hm1 & x) {
-                    int L = l[0];
-                    if (h1[0] & x) {
-                        lf_set(ops.col[g1][pm], 16, L);
-                        if (h2[0] & x)
-                            lf_set(ops.col[g2][pm], 16, L);
-                    } else if (hm2 & x) {
-                        lf_set(ops.col[g1][pm], (h1[1] & x) ? 8 : 4, L);
-                        lf_set(ops.col[g2][pm], (h2[1] & x) ? 8 : 4, l[8 << ss]);
-                    } else {
-                        lf_set(ops.col[g1][pm], (h1[1] & x) ? 8 : 4, L);
-                    }
+    for (int p = 0; p < 16; p++) {
+        lf_set(o1[p], 0, 0);
+        lf_set(o2[p], 0, 0);
+    }
+    const int y = it * (2 << ss);
+    if (y >= 8)
+        return;
+    const uint8_t *h1 = mask[y], *h2 = mask[y + 1 + ss];
+    const uint8_t *lvl = f.level + it * (16 << ss);
+    unsigned hm1 = h1[0] | h1[1] | h1[2], hm13 = h1[3];
+    unsigned hm2 = h2[1] | h2[2], hm23 = h2[3];
+    unsigned hm = hm1 | hm2 | hm13 | hm23;
+    int loff = 0;
+    for (int b = 0; b < 8 && (hm & ~((1u << b) - 1)); b++) {
+        unsigned x = 1u << b;
+        const uint8_t *l = lvl + loff;
+        int pm = chroma ? b : 2 * b;     /* position index of the main edge */
+        if (!first_col || b > 0) {
+            if (hm1 & x) {
+                int L = l[0];
+                if (h1[0] & x) {
+                    lf_set(o1[pm], 16, L);
+                    if (h2[0] & x)
+                        lf_set(o2[pm], 16, L);
                 } else if (hm2 & x) {
-                    lf_set(ops.col[g2][pm], (h2[1] & x) ? 8 : 4, l[8 << ss]);
+                    lf_set(o1[pm], (h1[1] & x) ? 8 : 4, L);
+                    lf_set(o2[pm], (h2[1] & x) ? 8 : 4, l[8 << ss]);
+                } else {
+                    lf_set(o1[pm], (h1[1] & x) ? 8 : 4, L);
                 }
+            } else if (hm2 & x) {
+                lf_set(o2[pm], (h2[1] & x) ? 8 : 4, l[8 << ss]);
             }
-            if (chroma) {
-                if (x & 0xAA)
-                    loff += 2;
-            } else {
-                if (hm13 & x)
-                    lf_set(ops.col[g1][pm + 1], 4, l[0]);
-                if (hm23 & x)
-                    lf_set(ops.col[g2][pm + 1], 4, l[8]);
-                loff++;
-            }
+        }
+        if (chroma) {
+            if (x & 0xAA)
+                loff += 2;
+        } else {
+            if (hm13 & x)
+                lf_set(o1[pm + 1], 4, l[0]);
+            if (hm23 & x)
+                lf_set(o2[pm + 1], 4, l[8]);
+            loff++;
         }
     }
 }
 
-/* filter_plane_rows, vp9lpf.c:109-181.  first_row: superblock is at the frame's top edge. */
-VP9_HD void lf_decode_rows(const LfSb &f, bool chroma, bool first_row, LfOps &ops)
+VP9_HD void lf_decode_cols(const LfSb &f, bool chroma, bool first_col, LfOps &ops)
+{
+    for (int it = 0; it < 4; it++)
+        lf_decode_cols_it(f, chroma, first_col, it, ops.col[2 * it], ops.col[2 * it + 1]);
+}
+
+/* Iteration `j` of filter_plane_rows' inner loop for every y (vp9lpf.c:109-181): the row ops of
+ * the two 8-column groups 2*j (o1) and 2*j+1 (o2), indexed by edge position / 4.
+ * first_row: superblock is at the frame's top edge. */
+VP9_HD void lf_decode_rows_j(const LfSb &f, bool chroma, bool first_row, int j, LfOp *o1, LfOp *o2)
 {
     const int ss = chroma ? 1 : 0;
     const uint8_t (*mask)[4] = f.mask[ss][1];
-    for (int e = 0; e < 16; e++)
-        for (int c = 0; c < 8; c++)
-            lf_set(ops.row[e][c], 0, 0);
-    const uint8_t *lvl = f.level;
+    for (int e = 0; e < 16; e++) {
+        lf_set(o1[e], 0, 0);
+        lf_set(o2[e], 0, 0);
+    }
+    const int b = j * (2 << ss);
+    if (b >= 8)
+        return;
+    const unsigned x = 1u << b, x2 = x << (1 + ss);
     for (int y = 0; y < 8; y++) {
         const uint8_t *vmask = mask[y];
         unsigned vm = vmask[0] | vmask[1] | vmask[2], vm3 = vmask[3];
+        if (!(vm & ~(x - 1)))
+            continue;                         /* the reference's x loop has ended before this pair */
         int em = chroma ? y : 2 * y;          /* edge index of the main edge (units of 4 rows) */
-        int j = 0;
-        for (int b = 0; b < 8 && (vm & ~((1u << b) - 1)); b += 2 << ss, j++) {
-            unsigned x = 1u << b, x2 = x << (1 + ss);
-            const uint8_t *l = lvl + j * (2 << ss);
-            int c1 = 2 * j, c2 = 2 * j + 1;   /* 8-column groups of the two halves */
-            if (!first_row || y) {
-                if (vm & x) {
-                    int L = l[0];
-                    if (vmask[0] & x) {
-                        lf_set(ops.row[em][c1], 16, L);
-                        if (vmask[0] & x2)
-                            lf_set(ops.row[em][c2], 16, L);
-                    } else if (vm & x2) {
-                        lf_set(ops.row[em][c1], (vmask[1] & x) ? 8 : 4, L);
-                        lf_set(ops.row[em][c2], (vmask[1] & x2) ? 8 : 4, l[1 + ss]);
-                    } else {
-                        lf_set(ops.row[em][c1], (vmask[1] & x) ? 8 : 4, L);
-                    }
+        const uint8_t *l = f.level + (chroma ? (y >> 1) * 16 : y * 8) + j * (2 << ss);
+        if (!first_row || y) {
+            if (vm & x) {
+                int L = l[0];
+                if (vmask[0] & x) {
+                    lf_set(o1[em], 16, L);
+                    if (vmask[0] & x2)
+                        lf_set(o2[em], 16, L);
                 } else if (vm & x2) {
-                    lf_set(ops.row[em][c2], (vmask[1] & x2) ? 8 : 4, l[1 + ss]);
+                    lf_set(o1[em], (vmask[1] & x) ? 8 : 4, L);
+                    lf_set(o2[em], (vmask[1] & x2) ? 8 : 4, l[1 + ss]);
+                } else {
+                    lf_set(o1[em], (vmask[1] & x) ? 8 : 4, L);
                 }
-            }
-            if (!chroma) {
-                if (vm3 & x)
-                    lf_set(ops.row[em + 1][c1], 4, l[0]);
-                if (vm3 & x2)
-                    lf_set(ops.row[em + 1][c2], 4, l[1]);
+            } else if (vm & x2) {
+                lf_set(o2[em], (vmask[1] & x2) ? 8 : 4, l[1 + ss]);
             }
         }
-        if (chroma) {
-            if (y & 1)
-                lvl += 16;
-        } else {
-            lvl += 8;
+        if (!chroma) {
+            if (vm3 & x)
+                lf_set(o1[em + 1], 4, l[0]);
+            if (vm3 & x2)
+                lf_set(o2[em + 1], 4, l[1]);
+        }
+    }
+}
+
+VP9_HD void lf_decode_rows(const LfSb &f, bool chroma, bool first_row, LfOps &ops)
+{
+    for (int j = 0; j < 4; j++) {
+        LfOp o1[16], o2[16];
+        lf_decode_rows_j(f, chroma, first_row, j, o1, o2);
+        for (int e = 0; e < 16; e++) {
+            ops.row[e][2 * j] = o1[e];
+            ops.row[e][2 * j + 1] = o2[e];
         }
     }
 }
@@ -249,7 +272,8 @@ VP9_HD void lf_decode_rows(const LfSb &f, bool chroma, bool first_row, LfOps &op
 struct LfSched {
     uint16_t col[128], row[128];
     uint8_t cstart[LF_NSTEP + 1], rstart[LF_NSTEP + 1];
-    uint8_t pad[28];
+    uint8_t cmax, rmax;          /* highest non-empty column step; number of row steps (device pre-pass) */
+    uint8_t pad[26];
 };
 
 VP9_HD uint16_t lf_ent(int grp, int e, const LfOp &o)

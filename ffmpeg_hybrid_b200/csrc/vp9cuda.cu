@@ -362,7 +362,7 @@ static int launch_frame(Vp9CudaCtx *c, const FrameDesc &f, const DevRecords &d)
     }
     if (f.lf_level) {
         kstat_begin(c);
-        k_lf_sched<<<(f.sb_cols * f.sb_rows * 6 + 63) / 64, 64, 0, s>>>(f);
+        k_lf_sched<<<f.sb_cols * f.sb_rows, LF_SCHED_THREADS, 0, s>>>(f);
         kstat_end(c, KS_LFOPS, 1, (uint64_t)f.sb_cols * f.sb_rows * (sizeof(Vp9CudaLoopFilterSb) + 3 * sizeof(LfSched)));
         kstat_begin(c);
         CK(cudaMemsetAsync(f.progress, 0, (size_t)3 * f.sb_rows * 4, s));

@@ -38,9 +38,11 @@ def main():
             names = [k for k in st]
             print("frame  w    h  n_itx  levels " + " ".join(f"{k[:10]:>10s}" for k in names))
         print(f"{i:4d} {frames[i].w:5d} {frames[i].h:4d} {len(itx):6d} {nlv:6d} " + " ".join(f"{st[k]['ms']:10.3f}" for k in names))
-    pc = ctx.phase_clocks(5)
-    tot = max(sum(pc), 1)
-    print("loop-filter compute-warp phase share (wait body, Cr, wait top, R, Ce+signal):", [round(x / tot, 3) for x in pc])
+    pc = ctx.phase_clocks(10)
+    units = sum(((f.w + 63) // 64) * ((f.h + 63) // 64) for f in frames)
+    for name, v, n in (("luma", pc[:5], units), ("chroma", pc[5:], 2 * units)):
+        print(f"loop filter {name}: cycles per superblock turn (wait body, Cr, wait top, R, Ce+signal):",
+              [round(x / n) for x in v], "sum", round(sum(v) / n))
     ctx.close()
 
 
