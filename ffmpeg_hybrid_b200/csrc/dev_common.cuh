@@ -23,6 +23,21 @@ struct SurfDesc {
     int w, h;
 };
 
+/* Intra pre-pass output (k_intra_prep): one per superblock ... */
+struct IntraSb {
+    uint32_t start;                  /* first record of this superblock in irec[] */
+    uint16_t count, pad;             /* intra transform blocks (all planes); 0 = nothing to do */
+    uint32_t coef_lo, coef_n;        /* coefficient range its blocks use (arena units) */
+};
+/* ... and one per intra transform block, sorted by dependency depth inside the superblock */
+struct IntraRec {
+    uint8_t lx, ly;                  /* position inside the superblock plane, 4-pixel units */
+    uint8_t plane, tx, mode, txtp, flags, pad;
+    uint16_t eob;
+    uint16_t run;                    /* first block of a dependency step: blocks in the step, else 0 */
+    uint32_t coef_rel;               /* coefficient offset relative to IntraSb.coef_lo */
+};
+
 /* Everything a kernel needs to know about the frame being reconstructed. */
 struct FrameDesc {
     SurfDesc cur;
@@ -40,12 +55,10 @@ struct FrameDesc {
     const Vp9CudaLoopFilterSb *lf;
     /* scratch */
     int32_t *cellmap;              /* cols*rows: index into blk, -1 = not inter */
-    uint32_t *ilvl_hist;           /* [65536] records per intra dependency level -> start offsets */
-    uint32_t *iorder;              /* n_itx record indices sorted by level */
-    uint32_t *icounter;            /* [0] work-claim counter of the intra kernel */
-    uint32_t *done[3];             /* per plane, per 4x4 cell: == gen when its intra block is final */
-    int done_w[3], done_h[3];
-    uint32_t gen;                  /* unique per reconstructed frame */
+    uint32_t lane_itx_base[VP9CUDA_MAX_LANES]; /* first itx record of each lane in the concatenated list */
+    IntraSb *isb;                  /* [sb] intra work of each superblock */
+    IntraRec *irec;                /* n_itx records regrouped per superblock, sorted by depth */
+    int *iprogress;                /* [sb_rows] intra wavefront counters */
     LfSched *lfsched;              /* [sb][plane] loop-filter edge ops sorted by dependency step */
     int *progress;                 /* [3 planes][sb_rows] loop-filter wavefront counters */
     unsigned long long *phase_clk; /* optional: per-phase clock accumulation (profiling), or NULL */

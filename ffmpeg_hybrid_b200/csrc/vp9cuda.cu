@@ -91,7 +91,8 @@ struct HBuf {
 /* device-resident records + scratch of one frame */
 struct DevRecords {
     DBuf blk, tx[4], itx, coef, sb_index, lf;
-    DBuf cellmap, ilvl_hist, iorder, icounter, lfops, progress;
+    DBuf cellmap, isb, irec, iprogress, lfops, progress;
+    uint32_t lane_itx_base[VP9CUDA_MAX_LANES] = { 0 };
     Vp9CudaFrameHeader hdr;
     uint32_t n_blk = 0, n_tx[4] = { 0, 0, 0, 0 }, n_itx = 0;
     bool used = false;
@@ -99,7 +100,7 @@ struct DevRecords {
     {
         blk.release(); itx.release(); coef.release(); sb_index.release(); lf.release();
         for (auto &t : tx) t.release();
-        cellmap.release(); ilvl_hist.release(); iorder.release(); icounter.release(); lfops.release();
+        cellmap.release(); isb.release(); irec.release(); iprogress.release(); lfops.release();
         progress.release();
     }
 };
@@ -147,8 +148,6 @@ struct Vp9CudaCtx {
     size_t tused = 0;
     cudaEvent_t marks[16] = { nullptr };
     DBuf sum_buf;
-    DBuf done[3];                          /* intra "cell is final" maps, tagged with gen */
-    uint32_t gen = 0;
     DBuf phase_clk;                        /* optional profiling counters (set_option "phase_clk") */
     bool phase_on = false;
 };
@@ -276,9 +275,9 @@ static int upload_records(Vp9CudaCtx *c, DevRecords &d, const Vp9CudaFrameHeader
     r |= d.sb_index.reserve(n_sb * sizeof(Vp9CudaSbIndex));
     r |= d.lf.reserve(n_sb * sizeof(Vp9CudaLoopFilterSb));
     r |= d.cellmap.reserve((size_t)cols * rows * 4);
-    r |= d.ilvl_hist.reserve((size_t)ILVL_MAX * 4);
-    r |= d.iorder.reserve(n_itx * 4);
-    r |= d.icounter.reserve(64);
+    r |= d.isb.reserve((size_t)n_sb * sizeof(IntraSb));
+    r |= d.irec.reserve(n_itx * sizeof(IntraRec));
+    r |= d.iprogress.reserve((size_t)sb_rows * 4);
     r |= d.lfops.reserve((size_t)n_sb * 3 * sizeof(LfSched));
     r |= d.progress.reserve((size_t)3 * sb_rows * 4);
     if (r)
@@ -301,12 +300,16 @@ static int upload_records(Vp9CudaCtx *c, DevRecords &d, const Vp9CudaFrameHeader
         if (n.coef)
             CK(cudaMemcpyAsync((char *)d.coef.p + (size_t)g.coef_base * cb, g.coef, (size_t)n.coef * cb,
                                cudaMemcpyHostToDevice, c->stream));
+        d.lane_itx_base[l] = (uint32_t)o_itx;
         bytes += n.blk * sizeof(Vp9CudaInterBlock) + n.itx * sizeof(Vp9CudaIntraTx) + (uint64_t)n.coef * cb;
         for (int t = 0; t < 4; t++) bytes += n.tx[t] * sizeof(Vp9CudaTx);
         o_blk += n.blk; o_itx += n.itx;
         for (int t = 0; t < 4; t++) o_tx[t] += n.tx[t];
     }
-    /* sb_index is not needed on the device any more (intra records are addressed globally) */
+    if (n_itx) {
+        CK(cudaMemcpyAsync(d.sb_index.p, recs->sb_index, n_sb * sizeof(Vp9CudaSbIndex), cudaMemcpyHostToDevice, c->stream));
+        bytes += n_sb * sizeof(Vp9CudaSbIndex);
+    }
     if (hdr->lf_level) {
         CK(cudaMemcpyAsync(d.lf.p, recs->lf, n_sb * sizeof(Vp9CudaLoopFilterSb), cudaMemcpyHostToDevice, c->stream));
         bytes += n_sb * sizeof(Vp9CudaLoopFilterSb);
@@ -348,16 +351,14 @@ static int launch_frame(Vp9CudaCtx *c, const FrameDesc &f, const DevRecords &d)
     if (itx_launches)
         kstat_end(c, KS_ITX, itx_launches, itx_bytes);
     if (f.n_itx) {
+        if (f.sb_cols > INTRA_MAX_SB_COLS)
+            return -EINVAL;
         kstat_begin(c);
-        CK(cudaMemsetAsync(f.ilvl_hist, 0, (size_t)ILVL_MAX * 4, s));
-        CK(cudaMemsetAsync(f.icounter, 0, 64, s));
-        k_ilvl_hist<<<(f.n_itx + 255) / 256, 256, 0, s>>>(f.itx, f.n_itx, f.ilvl_hist);
-        k_ilvl_scan<<<1, 1024, 0, s>>>(f.ilvl_hist);
-        k_ilvl_scatter<<<(f.n_itx + 255) / 256, 256, 0, s>>>(f.itx, f.n_itx, f.ilvl_hist, f.iorder);
-        kstat_end(c, KS_ISCHED, 3, (uint64_t)f.n_itx * (sizeof(Vp9CudaIntraTx) + 8));
+        k_intra_prep<<<f.sb_cols * f.sb_rows, 128, 0, s>>>(f);
+        kstat_end(c, KS_ISCHED, 1, (uint64_t)f.n_itx * (sizeof(Vp9CudaIntraTx) + sizeof(IntraRec)));
         kstat_begin(c);
-        const int ctas = (int)std::min<uint64_t>((f.n_itx + INTRA_WARPS - 1) / INTRA_WARPS, 148 * 4);
-        k_intra<P, HBD><<<ctas, INTRA_WARPS * 32, 0, s>>>(f);
+        CK(cudaMemsetAsync(f.iprogress, 0, (size_t)f.sb_rows * 4, s));
+        k_intra<P, HBD><<<f.sb_rows, INTRA_THREADS, IntraSmem<P, HBD>::BYTES, s>>>(f);
         kstat_end(c, KS_INTRA, 1, P_bytes);
     }
     if (f.lf_level) {
@@ -433,22 +434,12 @@ static int reconstruct(Vp9CudaCtx *c, DevRecords &d, uint8_t *const out_planes[3
     f.sb_index = (const Vp9CudaSbIndex *)d.sb_index.p;
     f.lf = (const Vp9CudaLoopFilterSb *)d.lf.p;
     f.cellmap = (int32_t *)d.cellmap.p;
-    f.ilvl_hist = (uint32_t *)d.ilvl_hist.p;
-    f.iorder = (uint32_t *)d.iorder.p;
-    f.icounter = (uint32_t *)d.icounter.p;
+    f.isb = (IntraSb *)d.isb.p;
+    f.irec = (IntraRec *)d.irec.p;
+    f.iprogress = (int *)d.iprogress.p;
+    memcpy(f.lane_itx_base, d.lane_itx_base, sizeof(f.lane_itx_base));
     f.lfsched = (LfSched *)d.lfops.p;
     f.progress = (int *)d.progress.p;
-    f.gen = ++c->gen;
-    for (int p = 0; p < 3; p++) {
-        f.done_w[p] = (f.cols * 2) >> !!p;
-        f.done_h[p] = (f.rows * 2) >> !!p;
-        size_t n = (size_t)f.done_w[p] * f.done_h[p] * 4;
-        if (n > c->done[p].cap) {
-            if (c->done[p].reserve(n)) { surface_unref(cur); return -ENOMEM; }
-            CK(cudaMemsetAsync(c->done[p].p, 0, c->done[p].cap, c->stream));
-        }
-        f.done[p] = (uint32_t *)c->done[p].p;
-    }
     f.phase_clk = c->phase_on ? (unsigned long long *)c->phase_clk.p : nullptr;
     memcpy(f.lim_lut, h.lim_lut, 64);
     memcpy(f.mblim_lut, h.mblim_lut, 64);
@@ -505,6 +496,10 @@ extern "C" int vp9cuda_create(Vp9CudaCtx **out, int device, int max_w, int max_h
     Vp9CudaCtx *c = new Vp9CudaCtx;
     c->device = device;
     CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    CK(cudaFuncSetAttribute(k_intra<uint8_t, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                            IntraSmem<uint8_t, false>::BYTES));
+    CK(cudaFuncSetAttribute(k_intra<uint16_t, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                            IntraSmem<uint16_t, true>::BYTES));
     c->ticket_ev.resize(256);
     for (auto &e : c->ticket_ev)
         CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
@@ -566,7 +561,6 @@ extern "C" void vp9cuda_destroy(Vp9CudaCtx *c)
     for (auto &e : c->tpool) cudaEventDestroy(e);
     c->sum_buf.release();
     c->phase_clk.release();
-    for (auto &d : c->done) d.release();
     cudaStreamDestroy(c->stream);
     delete c;
 }
