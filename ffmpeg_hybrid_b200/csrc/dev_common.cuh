@@ -26,16 +26,19 @@ struct SurfDesc {
 /* Intra pre-pass output (k_intra_prep): one per superblock ... */
 struct IntraSb {
     uint32_t start;                  /* first record of this superblock in irec[] */
-    uint16_t count, pad;             /* intra transform blocks (all planes); 0 = nothing to do */
-    uint32_t coef_lo, coef_n;        /* coefficient range its blocks use (arena units) */
+    uint16_t count;                  /* intra transform blocks (all planes); 0 = nothing to do */
+    uint16_t ntab;                   /* entries of its work table (itab) */
+    uint16_t has_res;                /* any of them has coefficients */
+    uint16_t pad;
+    uint32_t pad2;
 };
 /* ... and one per intra transform block, sorted by dependency depth inside the superblock */
 struct IntraRec {
     uint8_t lx, ly;                  /* position inside the superblock plane, 4-pixel units */
-    uint8_t plane, tx, mode, txtp, flags, pad;
+    uint8_t plane, tx, mode /* edge-converted */, txtp, flags /* 1 left, 2 right, 4 top */, pad;
     uint16_t eob;
-    uint16_t run;                    /* first block of a dependency step: blocks in the step, else 0 */
-    uint32_t coef_rel;               /* coefficient offset relative to IntraSb.coef_lo */
+    uint16_t run;                    /* unused */
+    uint32_t coef_off;               /* first coefficient in the frame's arena */
 };
 
 /* Everything a kernel needs to know about the frame being reconstructed. */
@@ -59,6 +62,8 @@ struct FrameDesc {
     IntraSb *isb;                  /* [sb] intra work of each superblock */
     IntraRec *irec;                /* n_itx records regrouped per superblock, sorted by depth */
     int *iprogress;                /* [sb_rows] intra wavefront counters */
+    uint16_t *itab;                /* [sb][768] per-step chunk tables (k_intra_prep) */
+    int16_t *ires;                 /* [sb][6144] intra residual tiles (k_intra_res -> k_intra) */
     LfSched *lfsched;              /* [sb][plane] loop-filter edge ops sorted by dependency step */
     int *progress;                 /* [3 planes][sb_rows] loop-filter wavefront counters */
     unsigned long long *phase_clk; /* optional: per-phase clock accumulation (profiling), or NULL */

@@ -10,16 +10,20 @@
  *
  *   k_intra_prep : one CTA per superblock.  Sorts the superblock's records (all three planes)
  *       by the host-computed dependency depth (Vp9CudaIntraTx.level; equal depth = mutually
- *       independent) and writes them as compact 16-byte IntraRec with run lengths, plus the
- *       superblock's coefficient range.
+ *       independent) and writes them as compact 16-byte IntraRec with run lengths.
+ *   k_intra_res : the inverse transforms do not depend on any neighbour, so they leave the
+ *       dependency chain: one warp per coded block writes the rounded residual (int16, clamped
+ *       to [-2^bpp, 2^bpp], which keeps clip(pred + residual) exact) into a per-superblock
+ *       residual tile.  Fully parallel.
  *   k_intra : one CTA per superblock ROW.  The row's pixels slide through a shared-memory ring
  *       of four superblock columns per plane (row 0 of each ring = the pixel row above).  A
- *       body-loader warp streams tiles, records and coefficients in with cp.async one turn
- *       ahead; a top-loader warp polls the row above's progress counter and fetches the border
- *       row; eight compute warps run the turn's dependency steps (one block per warp and step,
- *       edges -> prediction -> inverse transform, all in shared memory, one barrier per step); a
- *       storer warp writes the finished tile back, bottom pixel row first, then fence + progress
- *       counter for the row below.  Superblocks without intra blocks cost one flag update.
+ *       body-loader warp streams tiles, records and residual tiles in with cp.async up to two
+ *       turns ahead; a top-loader warp polls the row above's progress counter and fetches the
+ *       border row; eight compute warps run the turn's dependency steps (edges -> prediction +
+ *       residual, all in shared memory, one barrier per step; 32x32 blocks are split four ways);
+ *       a storer warp writes the finished tile back, bottom pixel row first, then fence +
+ *       progress counter for the row below.  Superblocks without intra blocks cost one flag
+ *       update.
  *
  * Replaces intra_recon + check_intra_mode (vp9recon.c:37-364) and the intra_pred slots
  * (vp9dsp_template.c:33-1153).  Reads the pre-loop-filter picture everywhere, which is what
@@ -34,12 +38,13 @@
 
 namespace vp9 {
 
-#define INTRA_CW 8                          /* compute warps */
+#define INTRA_CW 16                         /* compute warps */
 #define INTRA_CT (INTRA_CW * 32)
 #define INTRA_THREADS (INTRA_CT + 3 * 32)   /* + body loader, top loader, storer */
 #define INTRA_MAX_SB_COLS 256
 #define INTRA_SB_RECS 384                   /* 256 luma + 2 x 64 chroma 4x4 blocks */
-#define INTRA_SB_COEFS 6144                 /* 64*64 + 2 * 32*32 */
+#define INTRA_SB_RES 6144                   /* residual tile: 64*64 + 2 * 32*32 int16 */
+#define INTRA_SB_TAB 768                    /* work table: <= 384 chunk entries + <= 384 step headers */
 
 __device__ __forceinline__ void cp16(void *smem, const void *gmem)
 {
@@ -49,79 +54,202 @@ __device__ __forceinline__ void cp16(void *smem, const void *gmem)
 __device__ __forceinline__ void cp_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
 template <int N> __device__ __forceinline__ void cp_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
 
+/* 32-pixel chunks a block is dealt out in (a 4x4 block is one half-filled chunk) */
+__device__ __forceinline__ int intra_chunks(int tx) { return tx == 0 ? 1 : 2 << (2 * (tx - 1)); }
+
 /* ---------------------------------------------------------------------------------------------- */
+/* Pre-pass, one CTA per superblock.
+ *  1. sort the records by the host's frame-wide depth (a topological order);
+ *  2. walk that order and compute each block's depth INSIDE the superblock, counting only the
+ *     neighbours its (edge-converted) mode really reads -- left column / top-left / top row /
+ *     top-right cell, the read set of check_intra_mode (vp9recon.c:72-221) -- and only cells that
+ *     hold intra blocks of this superblock: everything else is final before the turn starts;
+ *  3. sort by that local depth, emit IntraRec in that order and the work table: per step a header
+ *     (0x8000 | chunk count) followed by one entry per 32-pixel chunk (record | chunk << 9). */
 __global__ void __launch_bounds__(128) k_intra_prep(const __grid_constant__ FrameDesc f)
 {
     __shared__ uint32_t keys[512];
-    __shared__ unsigned lo, hi;
+    __shared__ uint32_t inf[512];
+    __shared__ uint8_t loc[512];
+    __shared__ uint8_t lvl[3 * 256];
+    __shared__ unsigned any_res;
     const int sb = blockIdx.x, tid = threadIdx.x;
     const Vp9CudaSbIndex si = f.sb_index[sb];
     const int n = si.itx_count;
     const uint32_t g0 = n ? f.lane_itx_base[si.lane] + si.itx_start : 0;
-    if (n == 0 || n > 512) {
+    if (n == 0 || n > INTRA_SB_RECS) {
         if (tid == 0) {
-            IntraSb o = { g0, 0, 0, 0, 0 };
+            IntraSb o = { g0, 0, 0, 0, 0, 0 };
             f.isb[sb] = o;
         }
         return;
     }
-    if (tid == 0) { lo = 0xffffffffu; hi = 0; }
+    if (tid == 0) any_res = 0;
     int m = 32;
     while (m < n) m <<= 1;
+    const int sbx = sb % f.sb_cols, sby = sb / f.sb_cols;
+    for (int i = tid; i < 3 * 256; i += 128) lvl[i] = 0xff;
     __syncthreads();
     for (int i = tid; i < m; i += 128) {
         uint32_t key = 0xffffffffu;
         if (i < n) {
             const Vp9CudaIntraTx &r = f.itx[g0 + i];
             key = (uint32_t)r.level << 10 | i;
-            if (r.eob) {
-                atomicMin(&lo, r.coef_off);
-                atomicMax(&hi, r.coef_off + (16u << (2 * r.tx)));
-            }
+            const int ch = r.plane > 0;
+            const int lx = r.x4 - sbx * (16 >> ch), ly = r.y4 - sby * (16 >> ch);
+            const bool have_top = r.y4 > 0, have_left = r.flags & VP9CUDA_ITX_HAVE_LEFT;
+            const int cmode = intra_mode_conv(r.mode, have_left, have_top);
+            inf[i] = lx | ly << 4 | r.plane << 8 | r.tx << 10 | cmode << 12 | (r.flags & 3) << 16 |
+                     (r.eob ? 1 : 0) << 18 | (have_top ? 1 : 0) << 19;
+            if (r.eob)
+                any_res = 1;
         }
         keys[i] = key;
     }
     __syncthreads();
-    for (int k = 2; k <= m; k <<= 1)
-        for (int j = k >> 1; j > 0; j >>= 1) {
-            for (int i = tid; i < m; i += 128) {
-                const int p = i ^ j;
-                if (p > i) {
-                    const uint32_t a = keys[i], b = keys[p];
-                    if ((a > b) == ((i & k) == 0)) { keys[i] = b; keys[p] = a; }
+    auto sort_keys = [&]() {
+        for (int k = 2; k <= m; k <<= 1)
+            for (int j = k >> 1; j > 0; j >>= 1) {
+                for (int i = tid; i < m; i += 128) {
+                    const int p = i ^ j;
+                    if (p > i) {
+                        const uint32_t a = keys[i], b = keys[p];
+                        if ((a > b) == ((i & k) == 0)) { keys[i] = b; keys[p] = a; }
+                    }
                 }
+                __syncthreads();
             }
-            __syncthreads();
+    };
+    sort_keys();
+    /* local depth, one frame-wide depth value (= set of mutually independent blocks) at a time */
+    for (int pos = 0; pos < n;) {
+        const uint32_t L = keys[pos] >> 10;
+        int end = pos + 1;
+        while (end < n && (keys[end] >> 10) == L) end++;
+        int mine[3], nm = 0;
+        for (int k = pos + tid; k < end && nm < 3; k += 128) {
+            const int i = keys[k] & 1023;
+            const uint32_t v = inf[i];
+            const int lx = v & 15, ly = v >> 4 & 15, pl = v >> 8 & 3, tx = v >> 10 & 3, cm = v >> 12 & 15;
+            const bool have_left = v >> 16 & 1, have_right = v >> 17 & 1, have_top = v >> 19 & 1;
+            const int needs = intra_mode_needs(cm), nb = 1 << tx, W = pl ? 8 : 16;
+            int mx = -1;
+            auto dep = [&](int x, int y) {
+                if (x >= 0 && y >= 0 && x < W && y < W) {
+                    const int d = lvl[pl * 256 + y * 16 + x];
+                    if (d != 0xff && d > mx) mx = d;
+                }
+            };
+            if (have_left) {
+                if (needs & 1)
+                    for (int j = 0; j < nb; j++) dep(lx - 1, ly + j);
+                if ((needs & 4) && have_top)
+                    dep(lx - 1, ly - 1);
+            }
+            if (have_top) {
+                if (needs & 2)
+                    for (int j = 0; j < nb; j++) dep(lx + j, ly - 1);
+                if ((needs & 8) && tx == 0 && have_right)
+                    dep(lx + 1, ly - 1);
+            }
+            loc[i] = (uint8_t)(mx + 1);
+            mine[nm++] = i;
         }
-    const int sbx = sb % f.sb_cols, sby = sb / f.sb_cols;
+        __syncthreads();
+        for (int q = 0; q < nm; q++) {
+            const uint32_t v = inf[mine[q]];
+            const int lx = v & 15, ly = v >> 4 & 15, pl = v >> 8 & 3, nb = 1 << (v >> 10 & 3);
+            for (int y = 0; y < nb; y++)
+                for (int x = 0; x < nb; x++)
+                    lvl[pl * 256 + (ly + y) * 16 + lx + x] = loc[mine[q]];
+        }
+        __syncthreads();
+        pos = end;
+    }
     for (int k = tid; k < n; k += 128) {
-        const uint32_t key = keys[k], lvl = key >> 10;
-        int run = 0;
-        if (k == 0 || (keys[k - 1] >> 10) != lvl) {
-            int e = k + 1;
-            while (e < n && (keys[e] >> 10) == lvl) e++;
-            run = e - k;
-        }
-        const Vp9CudaIntraTx r = f.itx[g0 + (key & 1023)];
-        const int ch = r.plane > 0;
+        const int i = keys[k] & 1023;
+        keys[k] = (uint32_t)loc[i] << 10 | i;
+    }
+    __syncthreads();
+    sort_keys();
+    for (int k = tid; k < n; k += 128) {
+        const int i = keys[k] & 1023;
+        const uint32_t v = inf[i];
+        const Vp9CudaIntraTx &r = f.itx[g0 + i];
         IntraRec o;
-        o.lx = (uint8_t)(r.x4 - sbx * (16 >> ch));
-        o.ly = (uint8_t)(r.y4 - sby * (16 >> ch));
-        o.plane = r.plane; o.tx = r.tx; o.mode = r.mode; o.txtp = r.txtp; o.flags = r.flags; o.pad = 0;
+        o.lx = v & 15; o.ly = v >> 4 & 15;
+        o.plane = r.plane; o.tx = r.tx; o.mode = v >> 12 & 15; o.txtp = r.txtp;
+        o.flags = (v >> 16 & 3) | (v >> 19 & 1) << 2;
+        o.pad = 0;
         o.eob = r.eob;
-        o.run = (uint16_t)run;
-        o.coef_rel = r.eob ? r.coef_off - lo : 0;
+        o.run = 0;
+        o.coef_off = r.coef_off;
         f.irec[g0 + k] = o;
     }
     if (tid == 0) {
-        IntraSb o = { g0, (uint16_t)n, 0, hi ? lo : 0, hi ? hi - lo : 0 };
+        uint16_t *tab = f.itab + (size_t)sb * INTRA_SB_TAB;
+        int pos = 0;
+        for (int k = 0; k < n;) {
+            const uint32_t L = keys[k] >> 10;
+            const int hdr = pos++;
+            int cnt = 0;
+            for (; k < n && (keys[k] >> 10) == L; k++) {
+                const int nch = intra_chunks(inf[keys[k] & 1023] >> 10 & 3);
+                for (int q = 0; q < nch; q++)
+                    tab[pos++] = (uint16_t)(k | q << 9);
+                cnt += nch;
+            }
+            tab[hdr] = (uint16_t)(0x8000 | cnt);
+        }
+        IntraSb o = { g0, (uint16_t)n, (uint16_t)pos, (uint16_t)any_res, 0, 0 };
         f.isb[sb] = o;
     }
 }
 
 /* ---------------------------------------------------------------------------------------------- */
+/* residual tile of one superblock: luma 64x64 row-major, then U 32x32, then V 32x32 (int16) */
+__device__ __forceinline__ int res_plane_off(int pl) { return pl == 0 ? 0 : pl == 1 ? 4096 : 5120; }
+
+struct ResBlk {
+    int16_t *p; int stride;
+    __device__ __forceinline__ int get(int, int) const { return 0; }
+    __device__ __forceinline__ void put(int x, int y, int v) { p[y * stride + x] = (int16_t)v; }
+};
+
+#define IRES_WARPS 4
+template <bool HBD>
+__global__ void __launch_bounds__(IRES_WARPS * 32) k_intra_res(const __grid_constant__ FrameDesc f)
+{
+    typedef typename ItxTypes<HBD>::C C;
+    __shared__ C tmp_s[IRES_WARPS][32 * 33];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    C *tmp = tmp_s[warp];
+    /* one warp per (superblock, record); superblock = blockIdx.y keeps the residual tile address cheap */
+    const int sb = blockIdx.x;
+    const IntraSb si = f.isb[sb];
+    if (!si.has_res)
+        return;
+    int16_t *tile = f.ires + (size_t)sb * INTRA_SB_RES;
+    for (int k = warp; k < si.count; k += IRES_WARPS) {
+        const IntraRec r = f.irec[si.start + k];
+        if (!r.eob)
+            continue;
+        const int S = r.plane ? 32 : 64;
+        ResBlk blk = { tile + res_plane_off(r.plane) + r.ly * 4 * S + r.lx * 4, S };
+        const C *coef = (const C *)f.coef + r.coef_off;
+        switch (r.tx) {
+        case 0: if (lane < 4)  itx_block<HBD, 4, ResBlk, true>(coef, tmp, lane, r.txtp, r.eob, f.bpp, blk, 0xfu); break;
+        case 1: if (lane < 8)  itx_block<HBD, 8, ResBlk, true>(coef, tmp, lane, r.txtp, r.eob, f.bpp, blk, 0xffu); break;
+        case 2: if (lane < 16) itx_block<HBD, 16, ResBlk, true>(coef, tmp, lane, r.txtp, r.eob, f.bpp, blk, 0xffffu); break;
+        default: itx_block<HBD, 32, ResBlk, true>(coef, tmp, lane, r.txtp, r.eob, f.bpp, blk, 0xffffffffu); break;
+        }
+        __syncwarp();
+    }
+}
+
+/* ---------------------------------------------------------------------------------------------- */
 struct IntraSig {
-    volatile int body;     /* tiles / records / coefficients of superblocks < body are in shared memory */
+    volatile int body;     /* tiles / records / residuals of superblocks < body are in shared memory */
     volatile int top;      /* border rows of superblocks < top are in shared memory */
     volatile int done;     /* turns < done are complete */
     volatile int stored;   /* superblocks < stored have been written back */
@@ -132,37 +260,45 @@ template <class P> struct TilePx {
     unsigned char *t; int rsb, mask;
     __device__ __forceinline__ int operator()(int x, int y) const { return *(const P *)(t + y * rsb + (x & mask) * (int)sizeof(P)); }
 };
-template <class P> struct SmemBlk {
-    P *p; int stride;
-    __device__ __forceinline__ int get(int x, int y) const { return p[y * stride + x]; }
-    __device__ __forceinline__ void put(int x, int y, int v) { p[y * stride + x] = (P)v; }
+
+/* edge samples evaluated on the fly from the ring (same rules as intra_edges, vp9_pred.h) */
+template <class P> struct TileEdges {
+    TilePx<P> px;
+    int bx, by, N, needs, avail_w, avail_h, bpp;
+    bool have_top, have_left, have_right;
+    __device__ __forceinline__ int top(int i) const
+    {
+        return intra_edge_top(px, i, bx, by, N, needs, have_top, have_left, have_right, avail_w, bpp);
+    }
+    __device__ __forceinline__ int left(int y) const { return intra_edge_left(px, y, bx, by, have_left, avail_h, bpp); }
 };
 
-template <class P, bool HBD> struct IntraSmem {
-    typedef typename ItxTypes<HBD>::C C;
+template <class P> struct IntraSmem {
     static constexpr int RSBY = 4 * 64 * (int)sizeof(P) + 16;      /* luma ring row stride, bytes */
     static constexpr int RSBC = 4 * 32 * (int)sizeof(P) + 16;
     static constexpr int O_Y = 0;
     static constexpr int O_U = O_Y + 65 * RSBY;
     static constexpr int O_V = O_U + 33 * RSBC;
-    static constexpr int O_COEF = O_V + 33 * RSBC;                 /* [2][INTRA_SB_COEFS] C */
-    static constexpr int O_REC = O_COEF + 2 * INTRA_SB_COEFS * (int)sizeof(C);
-    static constexpr int O_TMP = O_REC + 2 * INTRA_SB_RECS * (int)sizeof(IntraRec);
-    static constexpr int O_EDGE = O_TMP + INTRA_CW * 32 * 33 * (int)sizeof(C);
-    static constexpr int O_INFO = O_EDGE + INTRA_CW * 100 * 4;
+    static constexpr int O_RES = O_V + 33 * RSBC;                  /* [4][INTRA_SB_RES] int16 */
+    static constexpr int O_REC = O_RES + 4 * INTRA_SB_RES * 2;     /* [4][INTRA_SB_RECS] IntraRec */
+    static constexpr int O_TAB = O_REC + 4 * INTRA_SB_RECS * (int)sizeof(IntraRec);   /* [4][INTRA_SB_TAB] u16 */
+    static constexpr int O_INFO = O_TAB + 4 * INTRA_SB_TAB * 2;
     static constexpr int BYTES = O_INFO + INTRA_MAX_SB_COLS * (int)sizeof(IntraSb);
 };
 
-template <class P, bool HBD>
+#define ICLK(k) do { if (f.phase_clk) { long long c_ = clock64(); \
+    atomicAdd(&f.phase_clk[k], (unsigned long long)(c_ - clk_)); clk_ = c_; } } while (0)
+
+template <class P>
 __global__ void __launch_bounds__(INTRA_THREADS) k_intra(const __grid_constant__ FrameDesc f)
 {
-    typedef typename ItxTypes<HBD>::C C;
-    typedef IntraSmem<P, HBD> L;
+    typedef IntraSmem<P> L;
     extern __shared__ __align__(16) unsigned char sm[];
     __shared__ IntraSig sig;
     auto tile = [&](int pl) -> unsigned char * { return sm + (pl == 0 ? L::O_Y : pl == 1 ? L::O_U : L::O_V); };
-    C *const coefbuf = (C *)(sm + L::O_COEF);
+    int16_t *const resbuf = (int16_t *)(sm + L::O_RES);
     IntraRec *const recbuf = (IntraRec *)(sm + L::O_REC);
+    uint16_t *const tabbuf = (uint16_t *)(sm + L::O_TAB);
     const IntraSb *const info = (const IntraSb *)(sm + L::O_INFO);
     const int row = blockIdx.x, ncol = f.sb_cols;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -175,8 +311,6 @@ __global__ void __launch_bounds__(INTRA_THREADS) k_intra(const __grid_constant__
 
     if (warp < INTRA_CW) {
         /* ------------------------------- compute warps ------------------------------- */
-        int *top = (int *)(sm + L::O_EDGE) + warp * 100, *left = top + 66;
-        C *tmp = (C *)(sm + L::O_TMP) + warp * 32 * 33;
         for (int c = 0; c < ncol; c++) {
             const int n = info[c].count;
             if (n == 0) {
@@ -184,65 +318,77 @@ __global__ void __launch_bounds__(INTRA_THREADS) k_intra(const __grid_constant__
                     sig.done = c + 1;
                 continue;
             }
+            long long clk_ = 0;
+            if (f.phase_clk && threadIdx.x == 0) clk_ = clock64();
             if (threadIdx.x == 0) {
                 while (sig.body < c + 1) { }
+                ICLK(10);
                 if (has_top)
                     while (sig.top < c + 1) { }
+                ICLK(11);
                 __threadfence_block();
             }
             asm volatile("bar.sync 1, %0;\n" ::"n"(INTRA_CT) : "memory");
-            const IntraRec *rec = recbuf + (c & 1) * INTRA_SB_RECS;
-            const C *coefs = coefbuf + (c & 1) * INTRA_SB_COEFS;
-            for (int a = 0; a < n;) {
-                const int run = rec[a].run;
-                for (int t = a + warp; t < a + run; t += INTRA_CW) {
-                    const IntraRec r = rec[t];
+            int nsteps = 0;
+            const IntraRec *rec = recbuf + (c & 3) * INTRA_SB_RECS;
+            const int16_t *res = resbuf + (c & 3) * INTRA_SB_RES;
+            const uint16_t *tab = tabbuf + (c & 3) * INTRA_SB_TAB;
+            const int ntab = info[c].ntab;
+            for (int pos = 0; pos < ntab;) {
+                const int cnt = tab[pos] & 0x7fff;
+                for (int i = warp; i < cnt; i += INTRA_CW) {
+                    const unsigned ent = tab[pos + 1 + i];
+                    const IntraRec r = rec[ent & 511];
+                    const int q = ent >> 9 & 31;
                     const int pl = r.plane, ch = pl > 0;
                     const int N = 4 << r.tx, S = 64 >> ch;
                     const int rsb = ch ? L::RSBC : L::RSBY;
                     unsigned char *tl = tile(pl);
-                    const int bx = (c & 3) * S + r.lx * 4, by = 1 + r.ly * 4;      /* ring coordinates */
-                    const int abx = c * S + r.lx * 4, aby = row * S + r.ly * 4;    /* plane coordinates */
-                    const bool have_left = r.flags & VP9CUDA_ITX_HAVE_LEFT, have_right = r.flags & VP9CUDA_ITX_HAVE_RIGHT;
-                    const bool have_top = aby > 0;
-                    const int mode = intra_mode_conv(r.mode, have_left, have_top);
-                    const int needs = intra_mode_needs(mode);
-                    const int avail_w = ((f.cols * 8) >> ch) - abx, avail_h = ((f.rows * 8) >> ch) - aby;
-                    TilePx<P> px = { tl, rsb, 4 * S - 1 };
-                    for (int e = lane; e < 3 * N + 1; e += 32) {
-                        if (e <= 2 * N) {
-                            if (needs & 2)
-                                top[e] = intra_edge_top(px, e, bx, by, N, needs, have_top, have_left, have_right, avail_w, f.bpp);
-                        } else if (needs & 1) {
-                            left[e - 2 * N - 1] = intra_edge_left(px, e - 2 * N - 1, bx, by, have_left, avail_h, f.bpp);
+                    TileEdges<P> e;
+                    e.px.t = tl; e.px.rsb = rsb; e.px.mask = 4 * S - 1;
+                    e.bx = (c & 3) * S + r.lx * 4; e.by = 1 + r.ly * 4;            /* ring coordinates */
+                    e.N = N; e.bpp = f.bpp;
+                    e.have_left = r.flags & 1; e.have_right = r.flags & 2; e.have_top = r.flags & 4;
+                    const int mode = r.mode;                                        /* already edge-converted */
+                    e.needs = intra_mode_needs(mode);
+                    e.avail_w = ((f.cols * 8) >> ch) - (c * S + r.lx * 4);
+                    e.avail_h = ((f.rows * 8) >> ch) - (row * S + r.ly * 4);
+                    int dc = 0;
+                    if (mode == DC_PRED || mode == LEFT_DC_PRED || mode == TOP_DC_PRED) {
+                        /* intra_dc's sums (vp9_pred.h), lane-parallel */
+                        int sum = 0;
+                        if (lane < N) {
+                            if (mode != LEFT_DC_PRED) sum += e.top(1 + lane);
+                            if (mode != TOP_DC_PRED) sum += e.left(lane);
                         }
+                        sum = __reduce_add_sync(0xffffffffu, sum);
+                        const int lg = 2 + r.tx;
+                        dc = mode == DC_PRED ? (sum + N) >> (lg + 1) : (sum + (N >> 1)) >> lg;
+                    } else if (mode >= DC_128_PRED) {
+                        dc = (128 << (f.bpp - 8)) + (mode == DC_127_PRED ? -1 : mode == DC_129_PRED ? 1 : 0);
                     }
-                    __syncwarp();
-                    const int dc = intra_dc(mode, N, top, left, f.bpp);
-                    P *blkp = (P *)(tl + by * rsb) + bx;
-                    const int bstride = rsb / (int)sizeof(P);
-                    for (int k = lane; k < N * N; k += 32)
-                        blkp[(k >> (2 + r.tx)) * bstride + (k & (N - 1))] =
-                            (P)intra_pixel(mode, N, k & (N - 1), k >> (2 + r.tx), top, left, dc, f.bpp);
-                    __syncwarp();
-                    if (r.eob) {
-                        SmemBlk<P> blk = { blkp, bstride };
-                        const C *coef = coefs + r.coef_rel;
-                        switch (r.tx) {
-                        case 0: if (lane < 4)  itx_block<HBD, 4>(coef, tmp, lane, r.txtp, r.eob, f.bpp, blk, 0xfu); break;
-                        case 1: if (lane < 8)  itx_block<HBD, 8>(coef, tmp, lane, r.txtp, r.eob, f.bpp, blk, 0xffu); break;
-                        case 2: if (lane < 16) itx_block<HBD, 16>(coef, tmp, lane, r.txtp, r.eob, f.bpp, blk, 0xffffu); break;
-                        default: itx_block<HBD, 32>(coef, tmp, lane, r.txtp, r.eob, f.bpp, blk, 0xffffffffu); break;
-                        }
-                        __syncwarp();
+                    const int p = q * 32 + lane;
+                    if (p < N * N) {
+                        const int x = p & (N - 1), y = p >> (2 + r.tx);
+                        int v = intra_pixel_e(mode, N, x, y, e, dc, f.bpp);
+                        if (r.eob)
+                            v = clip_pixel(v + res[res_plane_off(pl) + (r.ly * 4 + y) * S + r.lx * 4 + x], f.bpp);
+                        *((P *)(tl + (e.by + y) * rsb) + e.bx + x) = (P)v;
                     }
                 }
                 asm volatile("bar.sync 1, %0;\n" ::"n"(INTRA_CT) : "memory");
-                a += run;
+                pos += cnt + 1;
+                nsteps++;
             }
             if (threadIdx.x == 0) {
                 __threadfence_block();
                 sig.done = c + 1;
+                ICLK(12);
+                if (f.phase_clk) {
+                    atomicAdd(&f.phase_clk[13], (unsigned long long)nsteps);
+                    atomicAdd(&f.phase_clk[14], 1ull);
+                    atomicAdd(&f.phase_clk[15], (unsigned long long)n);
+                }
             }
         }
     } else if (warp == INTRA_CW) {
@@ -250,11 +396,12 @@ __global__ void __launch_bounds__(INTRA_THREADS) k_intra(const __grid_constant__
         for (int j = 0; j < ncol; j++) {
             const IntraSb sj = info[j];
             const bool need_tile = sj.count > 0 || (j + 1 < ncol && info[j + 1].count > 0);
-            if (need_tile && (sig.done < j - 1 || sig.stored < j - 3)) {
+            /* ring slot j & 3 last served superblock j-4 (tile: also the left border of turn j-3) */
+            if (need_tile && (sig.done < j - 2 || sig.stored < j - 3)) {
                 cp_wait<0>();
                 __syncwarp();
                 if (lane == 0) { __threadfence_block(); sig.body = j; }
-                while (sig.done < j - 1 || sig.stored < j - 3) __nanosleep(20);
+                while (sig.done < j - 2 || sig.stored < j - 3) __nanosleep(20);
             }
             if (need_tile) {
 #pragma unroll
@@ -272,14 +419,19 @@ __global__ void __launch_bounds__(INTRA_THREADS) k_intra(const __grid_constant__
             }
             if (sj.count > 0) {
                 const unsigned char *rs = (const unsigned char *)(f.irec + sj.start);
-                unsigned char *rd = (unsigned char *)(recbuf + (j & 1) * INTRA_SB_RECS);
+                unsigned char *rd = (unsigned char *)(recbuf + (j & 3) * INTRA_SB_RECS);
                 for (int i = lane; i < sj.count; i += 32)
                     cp16(rd + 16 * i, rs + 16 * i);
-                const unsigned char *cs = (const unsigned char *)((const C *)f.coef + sj.coef_lo);
-                unsigned char *cd = (unsigned char *)(coefbuf + (j & 1) * INTRA_SB_COEFS);
-                const int nch = (int)(sj.coef_n * sizeof(C) / 16);
-                for (int i = lane; i < nch; i += 32)
-                    cp16(cd + 16 * i, cs + 16 * i);
+                const unsigned char *ts = (const unsigned char *)(f.itab + (size_t)(row * ncol + j) * INTRA_SB_TAB);
+                unsigned char *td = (unsigned char *)(tabbuf + (j & 3) * INTRA_SB_TAB);
+                for (int i = lane; i < (sj.ntab * 2 + 15) / 16; i += 32)
+                    cp16(td + 16 * i, ts + 16 * i);
+                if (sj.has_res) {
+                    const unsigned char *cs = (const unsigned char *)(f.ires + (size_t)(row * ncol + j) * INTRA_SB_RES);
+                    unsigned char *cd = (unsigned char *)(resbuf + (j & 3) * INTRA_SB_RES);
+                    for (int i = lane; i < INTRA_SB_RES * 2 / 16; i += 32)
+                        cp16(cd + 16 * i, cs + 16 * i);
+                }
             }
             cp_commit();
             cp_wait<1>();

@@ -27,7 +27,10 @@ template <> struct ItxTypes<true>  { typedef W64 T; typedef int32_t C; };
  * blk: coefficients (global); tmp: N*(N+1) elements of shared memory owned by this block;
  * Pix: accessor with int get(x,y) / void put(x,y,v) relative to the block origin.
  * `sync` synchronises the N threads (warp-level; N <= 32 and the threads sit in one warp). */
-template <bool HBD, int N, class Pix>
+/* RES = true: instead of adding to the picture, put() receives the rounded residual clamped to
+ * [-2^bpp, 2^bpp] -- clip_pixel(pred + r) is the same for every pred in [0, 2^bpp) whether or not
+ * r was clamped to that range, so a later `clip_pixel(pred + residual)` is bit-exact. */
+template <bool HBD, int N, class Pix, bool RES = false>
 __device__ __forceinline__ void itx_block(const typename ItxTypes<HBD>::C *__restrict__ blk,
                                           typename ItxTypes<HBD>::C *tmp, int lane, int txtp, int eob,
                                           int bpp, Pix &pix, unsigned syncmask)
@@ -42,7 +45,7 @@ __device__ __forceinline__ void itx_block(const typename ItxTypes<HBD>::C *__res
         int r = itx_round(itx_dc_only<HBD>(blk[0]), bits);
 #pragma unroll 4
         for (int j = 0; j < N; j++)
-            pix.put(lane, j, clip_pixel(pix.get(lane, j) + r, bpp));
+            pix.put(lane, j, RES ? iclamp(r, -(1 << bpp), 1 << bpp) : clip_pixel(pix.get(lane, j) + r, bpp));
         return;
     }
     if (N == 4 && lossless) {
@@ -58,7 +61,8 @@ __device__ __forceinline__ void itx_block(const typename ItxTypes<HBD>::C *__res
         iwht4(in, 1, out, 1);
 #pragma unroll
         for (int j = 0; j < 4; j++)
-            pix.put(lane, j, clip_pixel(pix.get(lane, j) + (int32_t)(C)out[j].v, bpp));
+            pix.put(lane, j, RES ? iclamp((int32_t)(C)out[j].v, -(1 << bpp), 1 << bpp)
+                                 : clip_pixel(pix.get(lane, j) + (int32_t)(C)out[j].v, bpp));
         return;
     }
     {
@@ -74,7 +78,8 @@ __device__ __forceinline__ void itx_block(const typename ItxTypes<HBD>::C *__res
         itx_1d<T, N>(in, out, (txtp & 2) && N < 32);
 #pragma unroll
         for (int j = 0; j < N; j++)
-            pix.put(lane, j, clip_pixel(pix.get(lane, j) + itx_round((int32_t)(C)out[j].v, bits), bpp));
+            pix.put(lane, j, RES ? iclamp(itx_round((int32_t)(C)out[j].v, bits), -(1 << bpp), 1 << bpp)
+                                 : clip_pixel(pix.get(lane, j) + itx_round((int32_t)(C)out[j].v, bits), bpp));
     }
 }
 

@@ -284,72 +284,90 @@ VP9_HD int intra_dc(int mode, int N, const int *top, const int *left, int bpp)
     return 0;
 }
 
+/* Edge access for the predictors: top(i) = top[i] of intra_edges (i = 0 top-left), left(y).
+ * ArrayEdges reads prepared arrays; kernels may plug in an accessor that evaluates
+ * intra_edge_top/left on the fly. */
+struct ArrayEdges {
+    const int *t, *l;
+    VP9_HDM int top(int i) const { return t[i]; }
+    VP9_HDM int left(int y) const { return l[y]; }
+};
+
 /* S(k): the edge walked from bottom-left up the left column, through the top-left corner and
  * along the top row: S(k) = left[N-1-k] (k < N), S(N) = top-left, S(N+1+i) = above[i]. */
-VP9_HD int edge_S(int k, int N, const int *top, const int *left)
+template <class E>
+VP9_HD int edge_S(int k, int N, const E &e)
 {
-    return k < N ? left[N - 1 - k] : top[k - N];
+    return k < N ? e.left(N - 1 - k) : e.top(k - N);
 }
 
-/* Predicted sample (x, y) of an N x N block for a converted mode.  top/left from intra_edges,
+/* Predicted sample (x, y) of an N x N block for a converted mode.  Edges as in intra_edges,
  * dc from intra_dc.  Closed forms of vp9dsp_template.c:33-1100. */
-VP9_HD int intra_pixel(int mode, int N, int x, int y, const int *top, const int *left, int dc,
-                       int bpp)
+template <class E>
+VP9_HD int intra_pixel_e(int mode, int N, int x, int y, const E &e, int dc, int bpp)
 {
-    const int *A = top + 1;                 /* A[i] = above pixel i, A[-1] = top-left */
+#define A_(i) e.top(1 + (i))                 /* A_(i) = above pixel i, A_(-1) = top-left */
     switch (mode) {
-    case VERT_PRED: return A[x];
-    case HOR_PRED:  return left[y];
-    case TM_VP8_PRED: return clip_pixel(A[x] + left[y] - A[-1], bpp);
+    case VERT_PRED: return A_(x);
+    case HOR_PRED:  return e.left(y);
+    case TM_VP8_PRED: return clip_pixel(A_(x) + e.left(y) - A_(-1), bpp);
     case DIAG_DOWN_LEFT_PRED: {
         int i = x + y;
         if (N == 4 && i == 6)
-            return A[7];
-        return avg3(A[i], A[i + 1], A[i + 2 < 2 * N ? i + 2 : 2 * N - 1]);
+            return A_(7);
+        return avg3(A_(i), A_(i + 1), A_(i + 2 < 2 * N ? i + 2 : 2 * N - 1));
     }
     case DIAG_DOWN_RIGHT_PRED: {
         int c = N + x - y;
-        return avg3(edge_S(c - 1, N, top, left), edge_S(c, N, top, left), edge_S(c + 1, N, top, left));
+        return avg3(edge_S(c - 1, N, e), edge_S(c, N, e), edge_S(c + 1, N, e));
     }
     case VERT_RIGHT_PRED: {
         int j = y >> 1, k = (N >> 1) - 1 - j + x;
         if (x >= j) {
             if (!(y & 1))
-                return avg2(A[x - j - 1], A[x - j]);
+                return avg2(A_(x - j - 1), A_(x - j));
             int c = N + x - j;
-            return avg3(edge_S(c - 1, N, top, left), edge_S(c, N, top, left), edge_S(c + 1, N, top, left));
+            return avg3(edge_S(c - 1, N, e), edge_S(c, N, e), edge_S(c + 1, N, e));
         } else {
             int c = (y & 1) ? 2 * k + 2 : 2 * k + 3;
-            return avg3(edge_S(c - 1, N, top, left), edge_S(c, N, top, left), edge_S(c + 1, N, top, left));
+            return avg3(edge_S(c - 1, N, e), edge_S(c, N, e), edge_S(c + 1, N, e));
         }
     }
     case HOR_DOWN_PRED: {
         int m = 2 * N - 2 - 2 * y + x;
         if (m >= 2 * N) {
             int c = m - N + 1;
-            return avg3(edge_S(c - 1, N, top, left), edge_S(c, N, top, left), edge_S(c + 1, N, top, left));
+            return avg3(edge_S(c - 1, N, e), edge_S(c, N, e), edge_S(c + 1, N, e));
         }
         int i = m >> 1;
         if (!(m & 1))
-            return avg2(edge_S(i, N, top, left), edge_S(i + 1, N, top, left));
-        return avg3(edge_S(i, N, top, left), edge_S(i + 1, N, top, left), edge_S(i + 2, N, top, left));
+            return avg2(edge_S(i, N, e), edge_S(i + 1, N, e));
+        return avg3(edge_S(i, N, e), edge_S(i + 1, N, e), edge_S(i + 2, N, e));
     }
     case VERT_LEFT_PRED: {
         int k = (y >> 1) + x;
         if (!(y & 1))
-            return avg2(A[k], A[k + 1]);
-        return avg3(A[k], A[k + 1], A[k + 2]);
+            return avg2(A_(k), A_(k + 1));
+        return avg3(A_(k), A_(k + 1), A_(k + 2));
     }
     case HOR_UP_PRED: {
         int m = 2 * y + x, i = m >> 1;
-        int l0 = left[i < N ? i : N - 1], l1 = left[i + 1 < N ? i + 1 : N - 1];
+        int l0 = e.left(i < N ? i : N - 1), l1 = e.left(i + 1 < N ? i + 1 : N - 1);
         if (!(m & 1))
             return avg2(l0, l1);
-        return avg3(l0, l1, left[i + 2 < N ? i + 2 : N - 1]);
+        return avg3(l0, l1, e.left(i + 2 < N ? i + 2 : N - 1));
     }
     default:
         return dc;
     }
+#undef A_
+}
+
+VP9_HD int intra_pixel(int mode, int N, int x, int y, const int *top, const int *left, int dc,
+                       int bpp)
+{
+    ArrayEdges e = { top, left };
+    return intra_pixel_e(mode, N, x, y, e, dc, bpp);
 }
 
 } /* namespace vp9 */

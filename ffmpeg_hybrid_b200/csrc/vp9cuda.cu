@@ -91,7 +91,7 @@ struct HBuf {
 /* device-resident records + scratch of one frame */
 struct DevRecords {
     DBuf blk, tx[4], itx, coef, sb_index, lf;
-    DBuf cellmap, isb, irec, iprogress, lfops, progress;
+    DBuf cellmap, isb, irec, ires, itab, iprogress, lfops, progress;
     uint32_t lane_itx_base[VP9CUDA_MAX_LANES] = { 0 };
     Vp9CudaFrameHeader hdr;
     uint32_t n_blk = 0, n_tx[4] = { 0, 0, 0, 0 }, n_itx = 0;
@@ -100,7 +100,7 @@ struct DevRecords {
     {
         blk.release(); itx.release(); coef.release(); sb_index.release(); lf.release();
         for (auto &t : tx) t.release();
-        cellmap.release(); isb.release(); irec.release(); iprogress.release(); lfops.release();
+        cellmap.release(); isb.release(); irec.release(); ires.release(); itab.release(); iprogress.release(); lfops.release();
         progress.release();
     }
 };
@@ -277,6 +277,8 @@ static int upload_records(Vp9CudaCtx *c, DevRecords &d, const Vp9CudaFrameHeader
     r |= d.cellmap.reserve((size_t)cols * rows * 4);
     r |= d.isb.reserve((size_t)n_sb * sizeof(IntraSb));
     r |= d.irec.reserve(n_itx * sizeof(IntraRec));
+    if (n_itx) r |= d.ires.reserve((size_t)n_sb * INTRA_SB_RES * 2);
+    if (n_itx) r |= d.itab.reserve((size_t)n_sb * INTRA_SB_TAB * 2);
     r |= d.iprogress.reserve((size_t)sb_rows * 4);
     r |= d.lfops.reserve((size_t)n_sb * 3 * sizeof(LfSched));
     r |= d.progress.reserve((size_t)3 * sb_rows * 4);
@@ -355,10 +357,11 @@ static int launch_frame(Vp9CudaCtx *c, const FrameDesc &f, const DevRecords &d)
             return -EINVAL;
         kstat_begin(c);
         k_intra_prep<<<f.sb_cols * f.sb_rows, 128, 0, s>>>(f);
-        kstat_end(c, KS_ISCHED, 1, (uint64_t)f.n_itx * (sizeof(Vp9CudaIntraTx) + sizeof(IntraRec)));
+        k_intra_res<HBD><<<f.sb_cols * f.sb_rows, IRES_WARPS * 32, 0, s>>>(f);
+        kstat_end(c, KS_ISCHED, 2, (uint64_t)f.n_itx * (sizeof(Vp9CudaIntraTx) + sizeof(IntraRec)));
         kstat_begin(c);
         CK(cudaMemsetAsync(f.iprogress, 0, (size_t)f.sb_rows * 4, s));
-        k_intra<P, HBD><<<f.sb_rows, INTRA_THREADS, IntraSmem<P, HBD>::BYTES, s>>>(f);
+        k_intra<P><<<f.sb_rows, INTRA_THREADS, IntraSmem<P>::BYTES, s>>>(f);
         kstat_end(c, KS_INTRA, 1, P_bytes);
     }
     if (f.lf_level) {
@@ -437,6 +440,8 @@ static int reconstruct(Vp9CudaCtx *c, DevRecords &d, uint8_t *const out_planes[3
     f.isb = (IntraSb *)d.isb.p;
     f.irec = (IntraRec *)d.irec.p;
     f.iprogress = (int *)d.iprogress.p;
+    f.ires = (int16_t *)d.ires.p;
+    f.itab = (uint16_t *)d.itab.p;
     memcpy(f.lane_itx_base, d.lane_itx_base, sizeof(f.lane_itx_base));
     f.lfsched = (LfSched *)d.lfops.p;
     f.progress = (int *)d.progress.p;
@@ -496,10 +501,8 @@ extern "C" int vp9cuda_create(Vp9CudaCtx **out, int device, int max_w, int max_h
     Vp9CudaCtx *c = new Vp9CudaCtx;
     c->device = device;
     CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
-    CK(cudaFuncSetAttribute(k_intra<uint8_t, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                            IntraSmem<uint8_t, false>::BYTES));
-    CK(cudaFuncSetAttribute(k_intra<uint16_t, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                            IntraSmem<uint16_t, true>::BYTES));
+    CK(cudaFuncSetAttribute(k_intra<uint8_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, IntraSmem<uint8_t>::BYTES));
+    CK(cudaFuncSetAttribute(k_intra<uint16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, IntraSmem<uint16_t>::BYTES));
     c->ticket_ev.resize(256);
     for (auto &e : c->ticket_ev)
         CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
