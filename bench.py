@@ -181,7 +181,7 @@ def main():
     n_shown = sum(1 for f in frames if not f.invisible)
     h2d_per_step = sum(f.h2d_bytes for f in frames)
 
-    ctx = binding.Context(device=local, frames_in_flight=2)
+    ctx = binding.Context(device=local, frames_in_flight=3)
     big = max(frames, key=lambda f: f.w * f.h)
     outs = [binding.OutFrame(lib, big.w, big.h, big.bpp) for _ in range(2)]
     d2h_per_step = sum(outs[0].nbytes for f in frames if not f.invisible and (f.w, f.h) == (big.w, big.h))

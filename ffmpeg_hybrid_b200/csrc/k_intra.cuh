@@ -186,23 +186,66 @@ __global__ void __launch_bounds__(128) k_intra_prep(const __grid_constant__ Fram
         o.coef_off = r.coef_off;
         f.irec[g0 + k] = o;
     }
-    if (tid == 0) {
-        uint16_t *tab = f.itab + (size_t)sb * INTRA_SB_TAB;
-        int pos = 0;
-        for (int k = 0; k < n;) {
-            const uint32_t L = keys[k] >> 10;
-            const int hdr = pos++;
-            int cnt = 0;
-            for (; k < n && (keys[k] >> 10) == L; k++) {
-                const int nch = intra_chunks(inf[keys[k] & 1023] >> 10 & 3);
-                for (int q = 0; q < nch; q++)
-                    tab[pos++] = (uint16_t)(k | q << 9);
-                cnt += nch;
+    /* work table: thread t owns sorted records 4t .. 4t+3; two block-wide exclusive scans give every
+     * record the chunks and the step headers in front of it */
+    {
+        __shared__ int wsum[2][4];
+        __shared__ int scnt[INTRA_SB_RECS];
+        for (int i = tid; i < INTRA_SB_RECS; i += 128) scnt[i] = 0;
+        int nch[4], first[4], tc = 0, ts = 0;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const int k = 4 * tid + j;
+            nch[j] = 0; first[j] = 0;
+            if (k < n) {
+                nch[j] = intra_chunks(inf[keys[k] & 1023] >> 10 & 3);
+                first[j] = k == 0 || (keys[k - 1] >> 10) != (keys[k] >> 10);
             }
-            tab[hdr] = (uint16_t)(0x8000 | cnt);
+            tc += nch[j]; ts += first[j];
         }
-        IntraSb o = { g0, (uint16_t)n, (uint16_t)pos, (uint16_t)any_res, 0, 0 };
-        f.isb[sb] = o;
+        int ic = tc, is = ts;
+        const int lane = tid & 31, w = tid >> 5;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int a = __shfl_up_sync(0xffffffffu, ic, o), b2 = __shfl_up_sync(0xffffffffu, is, o);
+            if (lane >= o) { ic += a; is += b2; }
+        }
+        if (lane == 31) { wsum[0][w] = ic; wsum[1][w] = is; }
+        __syncthreads();
+        int bc = 0, bs = 0, totc = 0, tots = 0;
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            if (q < w) { bc += wsum[0][q]; bs += wsum[1][q]; }
+            totc += wsum[0][q]; tots += wsum[1][q];
+        }
+        int cpos = bc + ic - tc, sidx = bs + is - ts;       /* exclusive prefixes at record 4t */
+        uint16_t *tab = f.itab + (size_t)sb * INTRA_SB_TAB;
+        int hdr_pos[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const int k = 4 * tid + j;
+            hdr_pos[j] = -1;
+            if (k < n) {
+                sidx += first[j];
+                if (first[j]) hdr_pos[j] = cpos + sidx - 1;
+                for (int q = 0; q < nch[j]; q++)
+                    tab[cpos + sidx + q] = (uint16_t)(k | q << 9);
+                atomicAdd(&scnt[sidx - 1], nch[j]);
+                cpos += nch[j];
+            }
+        }
+        __syncthreads();
+        sidx = bs + is - ts;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            sidx += first[j];
+            if (hdr_pos[j] >= 0)
+                tab[hdr_pos[j]] = (uint16_t)(0x8000 | scnt[sidx - 1]);
+        }
+        if (tid == 0) {
+            IntraSb o = { g0, (uint16_t)n, (uint16_t)(totc + tots), (uint16_t)any_res, 0, 0 };
+            f.isb[sb] = o;
+        }
     }
 }
 

@@ -43,6 +43,9 @@ struct Surface {
     int stride[3] = { 0, 0, 0 };       /* pixels */
     int w = 0, h = 0, bpp = 0, aw = 0, ah = 0;
     int refs = 0;                      /* reference slots + "current" holding this surface */
+    cudaEvent_t ready = nullptr;       /* recorded on the compute stream when the picture is final */
+    cudaEvent_t d2h_done = nullptr;    /* recorded on the download stream after the last copy-out */
+    bool has_d2h = false;
 };
 
 /* growable device buffer */
@@ -96,8 +99,14 @@ struct DevRecords {
     Vp9CudaFrameHeader hdr;
     uint32_t n_blk = 0, n_tx[4] = { 0, 0, 0, 0 }, n_itx = 0;
     bool used = false;
+    cudaEvent_t uploaded = nullptr;    /* H2D of the records finished (upload stream) */
+    cudaEvent_t dev_free = nullptr;    /* the kernels reading these records finished (compute stream) */
+    bool wait_upload = false, has_free = false;
     void release()
     {
+        if (uploaded) cudaEventDestroy(uploaded);
+        if (dev_free) cudaEventDestroy(dev_free);
+        uploaded = dev_free = nullptr;
         blk.release(); itx.release(); coef.release(); sb_index.release(); lf.release();
         for (auto &t : tx) t.release();
         cellmap.release(); isb.release(); irec.release(); ires.release(); itab.release(); iprogress.release(); lfops.release();
@@ -130,7 +139,9 @@ enum { KS_CELLMAP, KS_INTER, KS_ITX, KS_ISCHED, KS_INTRA, KS_LFOPS, KS_LF, KS_H2
 
 struct Vp9CudaCtx {
     int device = 0;
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr;         /* compute */
+    cudaStream_t s_up = nullptr;           /* record upload (H2D), overlaps the previous frame's kernels */
+    cudaStream_t s_down = nullptr;         /* picture download (D2H), overlaps the next frame's kernels */
     std::vector<Surface *> pool;           /* every surface ever allocated */
     Surface *ref[8] = { nullptr };
     Surface *last = nullptr;               /* most recently reconstructed frame */
@@ -147,6 +158,7 @@ struct Vp9CudaCtx {
     std::vector<int> tstage;               /* stage id of pair i */
     size_t tused = 0;
     cudaEvent_t marks[16] = { nullptr };
+    cudaEvent_t join_ev[2] = { nullptr, nullptr };
     DBuf sum_buf;
     DBuf phase_clk;                        /* optional profiling counters (set_option "phase_clk") */
     bool phase_on = false;
@@ -157,15 +169,27 @@ static Surface *surface_get(Vp9CudaCtx *c, int w, int h, int bpp)
     for (Surface *s : c->pool)
         if (!s->refs && s->w == w && s->h == h && s->bpp == bpp) {
             s->refs = 1;
+            if (s->has_d2h) {               /* a copy-out of its previous picture may still be in flight */
+                cudaStreamWaitEvent(c->stream, s->d2h_done, 0);
+                s->has_d2h = false;
+            }
             return s;
         }
-    /* drop unused surfaces of other sizes before growing */
-    for (size_t i = 0; i < c->pool.size();) {
+    /* Unused surfaces of other sizes stay cached (streams with resize frames alternate between a
+     * few sizes, and cudaFree / cudaMalloc would drain the pipeline every time); only when more
+     * than POOL_IDLE_MAX sit idle are the idle ones of other sizes released. */
+    enum { POOL_IDLE_MAX = 12 };
+    int idle = 0;
+    for (Surface *s : c->pool) idle += !s->refs;
+    for (size_t i = 0; idle > POOL_IDLE_MAX && i < c->pool.size();) {
         Surface *s = c->pool[i];
         if (!s->refs && (s->w != w || s->h != h || s->bpp != bpp)) {
+            if (s->has_d2h) cudaEventSynchronize(s->d2h_done);
             for (int p = 0; p < 3; p++) cudaFree(s->pl[p]);
+            cudaEventDestroy(s->ready); cudaEventDestroy(s->d2h_done);
             delete s;
             c->pool.erase(c->pool.begin() + i);
+            idle--;
         } else {
             i++;
         }
@@ -185,9 +209,18 @@ static Surface *surface_get(Vp9CudaCtx *c, int w, int h, int bpp)
         }
         cudaMemsetAsync(s->pl[p], 0, n, c->stream);
     }
+    cudaEventCreateWithFlags(&s->ready, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&s->d2h_done, cudaEventDisableTiming);
     s->refs = 1;
     c->pool.push_back(s);
     return s;
+}
+
+static void sync_all(Vp9CudaCtx *c)
+{
+    cudaStreamSynchronize(c->s_up);
+    cudaStreamSynchronize(c->stream);
+    cudaStreamSynchronize(c->s_down);
 }
 
 static void surface_unref(Surface *s)
@@ -207,8 +240,9 @@ static SurfDesc surf_desc(const Surface *s)
     return d;
 }
 
-static void kstat_begin(Vp9CudaCtx *c)
+static void kstat_begin(Vp9CudaCtx *c, cudaStream_t st = nullptr)
 {
+    if (!st) st = c->stream;
     if (!c->timing)
         return;
     if (c->tused * 2 + 2 > c->tpool.size()) {
@@ -219,14 +253,15 @@ static void kstat_begin(Vp9CudaCtx *c)
         c->tpool.push_back(b);
         c->tstage.push_back(0);
     }
-    cudaEventRecord(c->tpool[c->tused * 2], c->stream);
+    cudaEventRecord(c->tpool[c->tused * 2], st);
 }
-static void kstat_end(Vp9CudaCtx *c, int k, uint64_t launches, uint64_t bytes)
+static void kstat_end(Vp9CudaCtx *c, int k, uint64_t launches, uint64_t bytes, cudaStream_t st = nullptr)
 {
+    if (!st) st = c->stream;
     c->ks[k].launches += launches;
     c->ks[k].bytes += bytes;
     if (c->timing) {
-        cudaEventRecord(c->tpool[c->tused * 2 + 1], c->stream);
+        cudaEventRecord(c->tpool[c->tused * 2 + 1], st);
         c->tstage[c->tused] = k;
         c->tused++;
     }
@@ -236,6 +271,8 @@ static void kstat_resolve(Vp9CudaCtx *c)
     if (!c->tused)
         return;
     cudaStreamSynchronize(c->stream);
+    cudaStreamSynchronize(c->s_up);
+    cudaStreamSynchronize(c->s_down);
     for (size_t i = 0; i < c->tused; i++) {
         float ms = 0;
         if (cudaEventElapsedTime(&ms, c->tpool[i * 2], c->tpool[i * 2 + 1]) == cudaSuccess)
@@ -284,24 +321,32 @@ static int upload_records(Vp9CudaCtx *c, DevRecords &d, const Vp9CudaFrameHeader
     r |= d.progress.reserve((size_t)3 * sb_rows * 4);
     if (r)
         return -ENOMEM;
-    kstat_begin(c);
+    if (!d.uploaded) {
+        CK(cudaEventCreateWithFlags(&d.uploaded, cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&d.dev_free, cudaEventDisableTiming));
+    }
+    if (d.has_free) {                       /* the previous user of this landing zone must be done */
+        CK(cudaStreamWaitEvent(c->s_up, d.dev_free, 0));
+        d.has_free = false;
+    }
+    kstat_begin(c, c->s_up);
     uint64_t o_blk = 0, o_tx[4] = { 0, 0, 0, 0 }, o_itx = 0, bytes = 0;
     for (int l = 0; l < nl; l++) {
         const Vp9CudaLaneCounts &n = recs->counts[l];
         const Vp9CudaLaneRing &g = recs->lanes[l];
         if (n.blk)
             CK(cudaMemcpyAsync((char *)d.blk.p + o_blk * sizeof(Vp9CudaInterBlock), g.blk,
-                               n.blk * sizeof(Vp9CudaInterBlock), cudaMemcpyHostToDevice, c->stream));
+                               n.blk * sizeof(Vp9CudaInterBlock), cudaMemcpyHostToDevice, c->s_up));
         for (int t = 0; t < 4; t++)
             if (n.tx[t])
                 CK(cudaMemcpyAsync((char *)d.tx[t].p + o_tx[t] * sizeof(Vp9CudaTx), g.tx[t],
-                                   n.tx[t] * sizeof(Vp9CudaTx), cudaMemcpyHostToDevice, c->stream));
+                                   n.tx[t] * sizeof(Vp9CudaTx), cudaMemcpyHostToDevice, c->s_up));
         if (n.itx)
             CK(cudaMemcpyAsync((char *)d.itx.p + o_itx * sizeof(Vp9CudaIntraTx), g.itx,
-                               n.itx * sizeof(Vp9CudaIntraTx), cudaMemcpyHostToDevice, c->stream));
+                               n.itx * sizeof(Vp9CudaIntraTx), cudaMemcpyHostToDevice, c->s_up));
         if (n.coef)
             CK(cudaMemcpyAsync((char *)d.coef.p + (size_t)g.coef_base * cb, g.coef, (size_t)n.coef * cb,
-                               cudaMemcpyHostToDevice, c->stream));
+                               cudaMemcpyHostToDevice, c->s_up));
         d.lane_itx_base[l] = (uint32_t)o_itx;
         bytes += n.blk * sizeof(Vp9CudaInterBlock) + n.itx * sizeof(Vp9CudaIntraTx) + (uint64_t)n.coef * cb;
         for (int t = 0; t < 4; t++) bytes += n.tx[t] * sizeof(Vp9CudaTx);
@@ -309,14 +354,16 @@ static int upload_records(Vp9CudaCtx *c, DevRecords &d, const Vp9CudaFrameHeader
         for (int t = 0; t < 4; t++) o_tx[t] += n.tx[t];
     }
     if (n_itx) {
-        CK(cudaMemcpyAsync(d.sb_index.p, recs->sb_index, n_sb * sizeof(Vp9CudaSbIndex), cudaMemcpyHostToDevice, c->stream));
+        CK(cudaMemcpyAsync(d.sb_index.p, recs->sb_index, n_sb * sizeof(Vp9CudaSbIndex), cudaMemcpyHostToDevice, c->s_up));
         bytes += n_sb * sizeof(Vp9CudaSbIndex);
     }
     if (hdr->lf_level) {
-        CK(cudaMemcpyAsync(d.lf.p, recs->lf, n_sb * sizeof(Vp9CudaLoopFilterSb), cudaMemcpyHostToDevice, c->stream));
+        CK(cudaMemcpyAsync(d.lf.p, recs->lf, n_sb * sizeof(Vp9CudaLoopFilterSb), cudaMemcpyHostToDevice, c->s_up));
         bytes += n_sb * sizeof(Vp9CudaLoopFilterSb);
     }
-    kstat_end(c, KS_H2D, 0, bytes);
+    kstat_end(c, KS_H2D, 0, bytes, c->s_up);
+    CK(cudaEventRecord(d.uploaded, c->s_up));
+    d.wait_upload = true;
     d.hdr = *hdr;
     d.n_blk = (uint32_t)n_blk; d.n_itx = (uint32_t)n_itx;
     for (int t = 0; t < 4; t++) d.n_tx[t] = (uint32_t)n_tx[t];
@@ -378,27 +425,30 @@ static int launch_frame(Vp9CudaCtx *c, const FrameDesc &f, const DevRecords &d)
     return 0;
 }
 
-static int copy_out(Vp9CudaCtx *c, const Surface *s, uint8_t *const out_planes[3], const ptrdiff_t out_strides[3])
+static int copy_out(Vp9CudaCtx *c, Surface *s, uint8_t *const out_planes[3], const ptrdiff_t out_strides[3])
 {
     const int bytes = s->bpp > 8 ? 2 : 1;
     uint64_t total = 0;
-    kstat_begin(c);
+    CK(cudaStreamWaitEvent(c->s_down, s->ready, 0));
+    kstat_begin(c, c->s_down);
     for (int p = 0; p < 3; p++) {
         int sh = p ? 1 : 0;
         int w = (s->w + sh) >> sh, h = (s->h + sh) >> sh;
         CK(cudaMemcpy2DAsync(out_planes[p], out_strides[p], s->pl[p], (size_t)s->stride[p] * bytes,
-                             (size_t)w * bytes, h, cudaMemcpyDeviceToHost, c->stream));
+                             (size_t)w * bytes, h, cudaMemcpyDeviceToHost, c->s_down));
         total += (uint64_t)w * h * bytes;
     }
-    kstat_end(c, KS_D2H, 0, total);
+    kstat_end(c, KS_D2H, 0, total, c->s_down);
+    CK(cudaEventRecord(s->d2h_done, c->s_down));
+    s->has_d2h = true;
     return 0;
 }
 
-static int make_ticket(Vp9CudaCtx *c, uint64_t *ticket)
+static int make_ticket(Vp9CudaCtx *c, uint64_t *ticket, cudaStream_t st)
 {
     uint64_t t = c->next_ticket++;
     cudaEvent_t ev = c->ticket_ev[t % c->ticket_ev.size()];
-    CK(cudaEventRecord(ev, c->stream));
+    CK(cudaEventRecord(ev, st));
     if (ticket)
         *ticket = t;
     return 0;
@@ -449,7 +499,17 @@ static int reconstruct(Vp9CudaCtx *c, DevRecords &d, uint8_t *const out_planes[3
     memcpy(f.lim_lut, h.lim_lut, 64);
     memcpy(f.mblim_lut, h.mblim_lut, 64);
 
+    if (d.wait_upload) {
+        CK(cudaStreamWaitEvent(c->stream, d.uploaded, 0));
+        d.wait_upload = false;
+    }
     int r = h.bpp > 8 ? launch_frame<uint16_t, true>(c, f, d) : launch_frame<uint8_t, false>(c, f, d);
+    if (r == 0 && d.dev_free) {
+        CK(cudaEventRecord(d.dev_free, c->stream));
+        d.has_free = true;
+    }
+    if (r == 0)
+        CK(cudaEventRecord(cur->ready, c->stream));
     if (r < 0) {
         surface_unref(cur);
         return r;
@@ -467,8 +527,9 @@ static int reconstruct(Vp9CudaCtx *c, DevRecords &d, uint8_t *const out_planes[3
         r = copy_out(c, cur, out_planes, out_strides);
         if (r < 0)
             return r;
+        return make_ticket(c, ticket, c->s_down);
     }
-    return make_ticket(c, ticket);
+    return make_ticket(c, ticket, c->stream);
 }
 
 /* ------------------------------------------------------------------------------------------
@@ -501,6 +562,8 @@ extern "C" int vp9cuda_create(Vp9CudaCtx **out, int device, int max_w, int max_h
     Vp9CudaCtx *c = new Vp9CudaCtx;
     c->device = device;
     CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&c->s_up, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&c->s_down, cudaStreamNonBlocking));
     CK(cudaFuncSetAttribute(k_intra<uint8_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, IntraSmem<uint8_t>::BYTES));
     CK(cudaFuncSetAttribute(k_intra<uint16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, IntraSmem<uint16_t>::BYTES));
     c->ticket_ev.resize(256);
@@ -508,6 +571,8 @@ extern "C" int vp9cuda_create(Vp9CudaCtx **out, int device, int max_w, int max_h
         CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     for (auto &e : c->marks)
         CK(cudaEventCreate(&e));
+    for (auto &e : c->join_ev)
+        CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     if (frames_in_flight < 1) frames_in_flight = 1;
     if (frames_in_flight > 16) frames_in_flight = 16;
     for (int i = 0; i < frames_in_flight; i++) {
@@ -528,7 +593,7 @@ extern "C" int vp9cuda_flush(Vp9CudaCtx *c)
     if (!c)
         return -EINVAL;
     cudaSetDevice(c->device);
-    CK(cudaStreamSynchronize(c->stream));
+    sync_all(c);
     for (int i = 0; i < 8; i++) {
         surface_unref(c->ref[i]);
         c->ref[i] = nullptr;
@@ -545,9 +610,10 @@ extern "C" void vp9cuda_destroy(Vp9CudaCtx *c)
     if (!c)
         return;
     cudaSetDevice(c->device);
-    cudaStreamSynchronize(c->stream);
+    sync_all(c);
     for (Surface *s : c->pool) {
         for (int p = 0; p < 3; p++) cudaFree(s->pl[p]);
+        cudaEventDestroy(s->ready); cudaEventDestroy(s->d2h_done);
         delete s;
     }
     for (RingSet *r : c->rings) {
@@ -561,10 +627,13 @@ extern "C" void vp9cuda_destroy(Vp9CudaCtx *c)
         if (d) { d->release(); delete d; }
     for (auto &e : c->ticket_ev) cudaEventDestroy(e);
     for (auto &e : c->marks) cudaEventDestroy(e);
+    for (auto &e : c->join_ev) cudaEventDestroy(e);
     for (auto &e : c->tpool) cudaEventDestroy(e);
     c->sum_buf.release();
     c->phase_clk.release();
     cudaStreamDestroy(c->stream);
+    cudaStreamDestroy(c->s_up);
+    cudaStreamDestroy(c->s_down);
     delete c;
 }
 
@@ -694,7 +763,7 @@ extern "C" int vp9cuda_finish_frame(Vp9CudaCtx *c, uint32_t frame_id, uint8_t *c
     recs.lf = (const Vp9CudaLoopFilterSb *)r->lf.p;
     int ret = upload_records(c, r->dev, &r->hdr, &recs);
     if (ret == 0)
-        CK(cudaEventRecord(r->consumed, c->stream));
+        CK(cudaEventRecord(r->consumed, c->s_up));
     r->busy = false;
     if (ret < 0)
         return ret;
@@ -708,6 +777,7 @@ extern "C" int vp9cuda_wait(Vp9CudaCtx *c, uint64_t ticket)
     cudaSetDevice(c->device);
     if (c->next_ticket - ticket > c->ticket_ev.size()) {
         CK(cudaStreamSynchronize(c->stream));     /* event slot already recycled: everything older is done */
+        CK(cudaStreamSynchronize(c->s_down));
         return 0;
     }
     CK(cudaEventSynchronize(c->ticket_ev[ticket % c->ticket_ev.size()]));
@@ -723,7 +793,7 @@ extern "C" int vp9cuda_show_existing(Vp9CudaCtx *c, int slot, uint8_t *const out
     cudaSetDevice(c->device);
     std::lock_guard<std::mutex> lk(c->mu);
     int r = copy_out(c, c->ref[slot], out_planes, out_strides);
-    return r < 0 ? r : make_ticket(c, ticket);
+    return r < 0 ? r : make_ticket(c, ticket, c->s_down);
 }
 
 extern "C" int vp9cuda_decode_frame(Vp9CudaCtx *c, const Vp9CudaFrameHeader *hdr, const Vp9CudaFrameRecords *recs,
@@ -755,7 +825,8 @@ extern "C" int vp9cuda_stage_frame(Vp9CudaCtx *c, const Vp9CudaFrameHeader *hdr,
         delete d;
         return ret;
     }
-    CK(cudaStreamSynchronize(c->stream));
+    CK(cudaStreamSynchronize(c->s_up));
+    d->wait_upload = false;
     c->staged.push_back(d);
     *handle = (int)c->staged.size() - 1;
     return 0;
@@ -776,7 +847,7 @@ extern "C" int vp9cuda_free_staged(Vp9CudaCtx *c, int handle)
     if (!c || handle < 0 || handle >= (int)c->staged.size() || !c->staged[handle])
         return -EINVAL;
     cudaSetDevice(c->device);
-    cudaStreamSynchronize(c->stream);
+    sync_all(c);
     c->staged[handle]->release();
     delete c->staged[handle];
     c->staged[handle] = nullptr;
@@ -812,6 +883,11 @@ extern "C" int vp9cuda_set_option(Vp9CudaCtx *c, const char *key, int value)
         if (value < 0 || value > 15)
             return -EINVAL;
         cudaSetDevice(c->device);
+        /* join the upload and download streams so the mark brackets everything submitted so far */
+        CK(cudaEventRecord(c->join_ev[0], c->s_up));
+        CK(cudaEventRecord(c->join_ev[1], c->s_down));
+        CK(cudaStreamWaitEvent(c->stream, c->join_ev[0], 0));
+        CK(cudaStreamWaitEvent(c->stream, c->join_ev[1], 0));
         CK(cudaEventRecord(c->marks[value], c->stream));
         return 0;
     }
@@ -826,7 +902,7 @@ extern "C" int vp9cuda_set_option(Vp9CudaCtx *c, const char *key, int value)
     }
     if (!strcmp(key, "sync")) {
         cudaSetDevice(c->device);
-        CK(cudaStreamSynchronize(c->stream));
+        sync_all(c);
         return 0;
     }
     if (!strcmp(key, "reset_stats")) {
