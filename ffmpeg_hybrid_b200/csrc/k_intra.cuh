@@ -332,20 +332,20 @@ template <class P> struct IntraSmem {
 #define ICLK(k) do { if (f.phase_clk) { long long c_ = clock64(); \
     atomicAdd(&f.phase_clk[k], (unsigned long long)(c_ - clk_)); clk_ = c_; } } while (0)
 
+/* one superblock row of the intra wavefront; runs on all INTRA_THREADS threads of the CTA */
 template <class P>
-__global__ void __launch_bounds__(INTRA_THREADS) k_intra(const __grid_constant__ FrameDesc f)
+__device__ __forceinline__ void intra_row(const FrameDesc &f, const int row, unsigned char *sm, IntraSig &sig)
 {
     typedef IntraSmem<P> L;
-    extern __shared__ __align__(16) unsigned char sm[];
-    __shared__ IntraSig sig;
     auto tile = [&](int pl) -> unsigned char * { return sm + (pl == 0 ? L::O_Y : pl == 1 ? L::O_U : L::O_V); };
     int16_t *const resbuf = (int16_t *)(sm + L::O_RES);
     IntraRec *const recbuf = (IntraRec *)(sm + L::O_REC);
     uint16_t *const tabbuf = (uint16_t *)(sm + L::O_TAB);
     const IntraSb *const info = (const IntraSb *)(sm + L::O_INFO);
-    const int row = blockIdx.x, ncol = f.sb_cols;
+    const int ncol = f.sb_cols;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const bool has_top = row > 0;
+    int *const ifull = f.iprogress + f.sb_rows;      /* [row]: superblocks < ifull are completely written back */
 
     if (threadIdx.x == 0) { sig.body = 0; sig.top = 0; sig.done = 0; sig.stored = 0; }
     for (int i = threadIdx.x; i < ncol * 4; i += INTRA_THREADS)
@@ -544,14 +544,28 @@ __global__ void __launch_bounds__(INTRA_THREADS) k_intra(const __grid_constant__
                     *(volatile int *)(f.iprogress + row) = c + 1;
                 }
                 store_rows(0, 1, 64); store_rows(1, 1, 32); store_rows(2, 1, 32);
+                __syncwarp();
+                if (lane == 0) {
+                    __threadfence();
+                    *(volatile int *)(ifull + row) = c + 1;
+                }
             } else if (lane == 0) {
                 *(volatile int *)(f.iprogress + row) = c + 1;
+                *(volatile int *)(ifull + row) = c + 1;
             }
             __syncwarp();
             if (lane == 0)
                 sig.stored = c + 1;
         }
     }
+}
+
+template <class P>
+__global__ void __launch_bounds__(INTRA_THREADS) k_intra(const __grid_constant__ FrameDesc f)
+{
+    extern __shared__ __align__(16) unsigned char sm[];
+    __shared__ IntraSig sig;
+    intra_row<P>(f, blockIdx.x, sm, sig);
 }
 
 } /* namespace vp9 */

@@ -191,6 +191,11 @@ __device__ void lf_row(const FrameDesc &f, int pl, int row, unsigned char *ring,
     P *plane = (P *)f.cur.pl[pl];
     const int y0 = row * S;
     int *prog = f.progress + pl * f.sb_rows;
+    /* Running beside the intra wavefront (k_wave): superblock (row, j) may be read once the intra
+     * pass has written it back completely, and column block c may be written once the intra row
+     * below has fetched its border row (pre-filter bottom line of this row) for columns c and c+1. */
+    const volatile int *const intra_full = f.lf_follow ? f.iprogress + f.sb_rows + row : nullptr;
+    const volatile int *const intra_below = f.lf_follow && row + 1 < f.sb_rows ? f.iprogress + row + 1 : nullptr;
 
     if (warp < LF_CW) {
         /* ------------------------------- compute warps ------------------------------- */
@@ -294,6 +299,23 @@ __device__ void lf_row(const FrameDesc &f, int pl, int row, unsigned char *ring,
                 if (lane == 0) { __threadfence_block(); sig->body = j; }
                 while (sig->stored < j - 3) __nanosleep(20);
             }
+            if (intra_full) {
+                int ready = 1;
+                if (lane == 0) ready = *intra_full >= j + 1;
+                ready = __shfl_sync(0xffffffffu, ready, 0);
+                if (!ready) {
+                    /* hand over what is already in flight before sleeping on the intra pass */
+                    lf_cp_wait<0>();
+                    __syncwarp();
+                    if (lane == 0) {
+                        __threadfence_block();
+                        sig->body = j;
+                        while (*intra_full < j + 1) __nanosleep(40);
+                    }
+                }
+                if (lane == 0) __threadfence();
+                __syncwarp();
+            }
             const unsigned char *src = (const unsigned char *)(plane + (size_t)y0 * stride + j * S);
             unsigned char *dst = ring + 8 * RSB + (j & 3) * SLOT;
 #pragma unroll 4
@@ -341,6 +363,12 @@ __device__ void lf_row(const FrameDesc &f, int pl, int row, unsigned char *ring,
         for (int c = 0; c < ncol; c++) {
             while (sig->done < c + 1) __nanosleep(20);
             __threadfence_block();
+            if (intra_below) {
+                const int need = min(c + 2, ncol);
+                if (lane == 0)
+                    while (*intra_below < need) __nanosleep(40);
+                __syncwarp();
+            }
             unsigned char *dst = (unsigned char *)(plane + (size_t)(y0 - 8) * stride + c * S);
             const unsigned char *src = ring + (c & 3) * SLOT;
             auto store_rows = [&](int r0, int r1) {
@@ -364,14 +392,23 @@ __device__ void lf_row(const FrameDesc &f, int pl, int row, unsigned char *ring,
     }
 }
 
+/* shared memory of one loop-filter CTA */
+template <class P> struct LfSmem {
+    static constexpr int O_RING = 0;                                      /* 72 ring rows */
+    static constexpr int O_SCHED = 72 * (256 * (int)sizeof(P) + 16);       /* LfSched[4] */
+    static constexpr int O_LUT = O_SCHED + 4 * (int)sizeof(LfSched);       /* lim[64], mblim[64] */
+    static constexpr int BYTES = O_LUT + 128;
+};
+
+/* loop-filter CTA `idx` = (superblock row idx / 3, plane idx % 3); threads >= LF_THREADS idle */
 template <class P>
-__global__ void __launch_bounds__(LF_THREADS) k_lf(const __grid_constant__ FrameDesc f)
+__device__ __forceinline__ void lf_cta(const FrameDesc &f, int idx, unsigned char *sm, LfSig &sig)
 {
-    __shared__ __align__(16) unsigned char ring[72 * (256 * sizeof(P) + 16)];
-    __shared__ __align__(16) LfSched sched[4];
-    __shared__ LfSig sig;
-    __shared__ uint8_t lut[128];
-    const int pl = blockIdx.x % 3, row = blockIdx.x / 3;
+    typedef LfSmem<P> L;
+    unsigned char *ring = sm + L::O_RING;
+    LfSched *sched = (LfSched *)(sm + L::O_SCHED);
+    uint8_t *lut = sm + L::O_LUT;
+    const int pl = idx % 3, row = idx / 3;
     if (threadIdx.x == 0) {
         sig.body = 0; sig.top = 0; sig.done = 0; sig.stored = 0;
     }
@@ -380,10 +417,20 @@ __global__ void __launch_bounds__(LF_THREADS) k_lf(const __grid_constant__ Frame
         lut[64 + threadIdx.x] = f.mblim_lut[threadIdx.x];
     }
     __syncthreads();
+    if (threadIdx.x >= LF_THREADS)
+        return;
     if (pl == 0)
         lf_row<P, 64>(f, pl, row, ring, sched, &sig, lut);
     else
         lf_row<P, 32>(f, pl, row, ring, sched, &sig, lut);
+}
+
+template <class P>
+__global__ void __launch_bounds__(LF_THREADS) k_lf(const __grid_constant__ FrameDesc f)
+{
+    __shared__ __align__(16) unsigned char sm[LfSmem<P>::BYTES];
+    __shared__ LfSig sig;
+    lf_cta<P>(f, blockIdx.x, sm, sig);
 }
 
 } /* namespace vp9 */
