@@ -7,6 +7,7 @@
 
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdio.h>
 
 #include "vp9cuda.h"
 #include "vp9_itx.h"
@@ -61,7 +62,8 @@ struct FrameDesc {
     uint32_t lane_itx_base[VP9CUDA_MAX_LANES]; /* first itx record of each lane in the concatenated list */
     IntraSb *isb;                  /* [sb] intra work of each superblock */
     IntraRec *irec;                /* n_itx records regrouped per superblock, sorted by depth */
-    int *iprogress;                /* [sb_rows] intra wavefront counters */
+    int *iprogress;                /* [2][sb_rows] intra wavefront counters: border row stored, superblock stored */
+    int lf_follow;                 /* the loop filter runs beside the intra wavefront (k_wave) */
     uint16_t *itab;                /* [sb][768] per-step chunk tables (k_intra_prep) */
     int16_t *ires;                 /* [sb][6144] intra residual tiles (k_intra_res -> k_intra) */
     LfSched *lfsched;              /* [sb][plane] loop-filter edge ops sorted by dependency step */
@@ -85,6 +87,32 @@ __device__ __forceinline__ int rounded_div(int a, int b)
 {
     return a >= 0 ? (a + (b >> 1)) / b : (a - (b >> 1)) / b;
 }
+
+/* Spin-wait on `cond`; `ns` > 0 sleeps between polls.  Built with -DVP9CUDA_WATCHDOG a wait that
+ * lasts longer than ~1 s reports where it is stuck into a host-mapped buffer and traps, so a
+ * dependency bug shows up as an error instead of a hung GPU. */
+#ifndef VP9_TIGHT_NS
+#define VP9_TIGHT_NS 0      /* sleep (ns) inside the compute warps' waits for their loader warps */
+#endif
+#ifdef VP9CUDA_WATCHDOG
+__device__ int *g_wd_buf;            /* host-mapped: [0] = count, then {line, id, at, block} per report */
+#define VP9_SPIN(cond, ns, tag, a, b) do { long long t0_ = clock64(); bool rep_ = false; while (cond) { if ((ns) > 0) __nanosleep(ns); \
+    const long long dt_ = clock64() - t0_; \
+    if (dt_ > (1ll << 31) && !rep_) { rep_ = true; const int i_ = atomicAdd(g_wd_buf, 1); \
+        if (i_ < 255) { int *q_ = g_wd_buf + 4 + 4 * i_; q_[0] = __LINE__; q_[1] = (int)(a); q_[2] = (int)(b); q_[3] = (int)blockIdx.x; } \
+        __threadfence_system(); } \
+    if (dt_ > (3ll << 30)) __trap(); } } while (0)
+#elif defined(VP9CUDA_HEARTBEAT)
+/* least-intrusive tracing: every wait notes {line, id, at} in a host-mapped table slot of its
+ * (block, warp) on entry and negates the line on exit; the host dumps the table when a frame
+ * does not finish (vp9cuda_wait). */
+__device__ int *g_wd_buf;
+#define VP9_SPIN(cond, ns, tag, a, b) do { int *q_ = g_wd_buf + ((blockIdx.x & 63) * 32 + (threadIdx.x >> 5)) * 4; \
+    q_[1] = (int)(a); q_[2] = (int)(b); q_[0] = __LINE__; \
+    while (cond) { if ((ns) > 0) __nanosleep(ns); } q_[0] = -__LINE__; } while (0)
+#else
+#define VP9_SPIN(cond, ns, tag, a, b) do { while (cond) { if ((ns) > 0) __nanosleep(ns); } } while (0)
+#endif
 
 template <class P> __device__ __forceinline__ P ld_cg(const P *p);
 template <> __device__ __forceinline__ uint8_t ld_cg<uint8_t>(const uint8_t *p)

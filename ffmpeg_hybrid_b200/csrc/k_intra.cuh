@@ -364,10 +364,10 @@ __device__ __forceinline__ void intra_row(const FrameDesc &f, const int row, uns
             long long clk_ = 0;
             if (f.phase_clk && threadIdx.x == 0) clk_ = clock64();
             if (threadIdx.x == 0) {
-                while (sig.body < c + 1) { }
+                VP9_SPIN(sig.body < c + 1, VP9_TIGHT_NS, "intra compute: body", row, c);
                 ICLK(10);
                 if (has_top)
-                    while (sig.top < c + 1) { }
+                    VP9_SPIN(sig.top < c + 1, VP9_TIGHT_NS, "intra compute: top", row, c);
                 ICLK(11);
                 __threadfence_block();
             }
@@ -440,11 +440,21 @@ __device__ __forceinline__ void intra_row(const FrameDesc &f, const int row, uns
             const IntraSb sj = info[j];
             const bool need_tile = sj.count > 0 || (j + 1 < ncol && info[j + 1].count > 0);
             /* ring slot j & 3 last served superblock j-4 (tile: also the left border of turn j-3) */
-            if (need_tile && (sig.done < j - 2 || sig.stored < j - 3)) {
+            /* lane 0 decides for the warp (see lf_row's body loader) */
+            int wait = 0;
+            if (lane == 0)
+                wait = need_tile && (sig.done < j - 2 || sig.stored < j - 3);
+            wait = __shfl_sync(0xffffffffu, wait, 0);
+            if (wait) {
                 cp_wait<0>();
                 __syncwarp();
-                if (lane == 0) { __threadfence_block(); sig.body = j; }
-                while (sig.done < j - 2 || sig.stored < j - 3) __nanosleep(20);
+                if (lane == 0) {
+                    __threadfence_block();
+                    sig.body = j;
+                    VP9_SPIN(sig.done < j - 2 || sig.stored < j - 3, 20, "intra body loader: ring", row, j);
+                    __threadfence_block();
+                }
+                __syncwarp();
             }
             if (need_tile) {
 #pragma unroll
@@ -494,9 +504,9 @@ __device__ __forceinline__ void intra_row(const FrameDesc &f, const int row, uns
                     if (lane == 0) sig.top = c + 1;
                     continue;
                 }
-                while (sig.done < c - 2 || sig.stored < c - 3) __nanosleep(20);
                 if (lane == 0) {
-                    while (*above < c + 1) __nanosleep(20);
+                    VP9_SPIN(sig.done < c - 2 || sig.stored < c - 3, 20, "intra top loader: ring", row, c);
+                    VP9_SPIN(*above < c + 1, 20, "intra top loader: row above", row, c);
                     __threadfence();
                 }
                 __syncwarp();
@@ -523,8 +533,11 @@ __device__ __forceinline__ void intra_row(const FrameDesc &f, const int row, uns
     } else {
         /* ------------------------------- storer ------------------------------- */
         for (int c = 0; c < ncol; c++) {
-            while (sig.done < c + 1) __nanosleep(20);
-            __threadfence_block();
+            if (lane == 0) {
+                VP9_SPIN(sig.done < c + 1, 20, "intra storer: done", row, c);
+                __threadfence_block();
+            }
+            __syncwarp();
             if (info[c].count > 0) {
                 auto store_rows = [&](int pl, int r0, int r1) {
                     const int S = pl ? 32 : 64, rsb = pl ? L::RSBC : L::RSBY;

@@ -34,6 +34,7 @@
 #define VP9CUDA_K_LF_CUH
 
 #include "dev_common.cuh"
+#include "k_intra.cuh"
 
 namespace vp9 {
 
@@ -194,8 +195,8 @@ __device__ void lf_row(const FrameDesc &f, int pl, int row, unsigned char *ring,
     /* Running beside the intra wavefront (k_wave): superblock (row, j) may be read once the intra
      * pass has written it back completely, and column block c may be written once the intra row
      * below has fetched its border row (pre-filter bottom line of this row) for columns c and c+1. */
-    const volatile int *const intra_full = f.lf_follow ? f.iprogress + f.sb_rows + row : nullptr;
-    const volatile int *const intra_below = f.lf_follow && row + 1 < f.sb_rows ? f.iprogress + row + 1 : nullptr;
+    const volatile int *const intra_full = (f.lf_follow & 1) ? f.iprogress + f.sb_rows + row : nullptr;
+    const volatile int *const intra_below = (f.lf_follow & 2) && row + 1 < f.sb_rows ? f.iprogress + row + 1 : nullptr;
 
     if (warp < LF_CW) {
         /* ------------------------------- compute warps ------------------------------- */
@@ -204,7 +205,7 @@ __device__ void lf_row(const FrameDesc &f, int pl, int row, unsigned char *ring,
         for (int c = 0; c < ncol; c++) {
             if (ctid == 0) {
                 const int need = min(c + 2, ncol);
-                while (sig->body < need) { }
+                VP9_SPIN(sig->body < need, VP9_TIGHT_NS, "lf compute: body", row * 3 + pl, c);
                 __threadfence_block();
             }
             lf_bar_compute();
@@ -242,7 +243,7 @@ __device__ void lf_row(const FrameDesc &f, int pl, int row, unsigned char *ring,
             LF_CLK(1);
             if (has_top) {
                 if (ctid == 0) {
-                    while (sig->top < c + 1) { }
+                    VP9_SPIN(sig->top < c + 1, VP9_TIGHT_NS, "lf compute: top", row * 3 + pl, c);
                     __threadfence_block();
                 }
                 lf_bar_compute();
@@ -293,29 +294,27 @@ __device__ void lf_row(const FrameDesc &f, int pl, int row, unsigned char *ring,
     } else if (warp == LF_CW) {
         /* ------------------------------- body loader ------------------------------- */
         for (int j = 0; j < ncol; j++) {
-            if (j >= 4 && sig->stored < j - 3) {
+            /* Lane 0 alone looks at the flags and the warp follows its verdict: a per-lane read of a
+             * changing flag could send part of the warp into the hand-over branch and leave the
+             * __syncwarp()s below unpaired. */
+            int wait = 0;
+            if (lane == 0)
+                wait = (j >= 4 && sig->stored < j - 3) || (intra_full && *intra_full < j + 1);
+            wait = __shfl_sync(0xffffffffu, wait, 0);
+            if (wait) {
+                /* hand over what is already in flight before sleeping */
                 lf_cp_wait<0>();
                 __syncwarp();
-                if (lane == 0) { __threadfence_block(); sig->body = j; }
-                while (sig->stored < j - 3) __nanosleep(20);
-            }
-            if (intra_full) {
-                int ready = 1;
-                if (lane == 0) ready = *intra_full >= j + 1;
-                ready = __shfl_sync(0xffffffffu, ready, 0);
-                if (!ready) {
-                    /* hand over what is already in flight before sleeping on the intra pass */
-                    lf_cp_wait<0>();
-                    __syncwarp();
-                    if (lane == 0) {
-                        __threadfence_block();
-                        sig->body = j;
-                        while (*intra_full < j + 1) __nanosleep(40);
-                    }
+                if (lane == 0) {
+                    __threadfence_block();
+                    sig->body = j;
+                    VP9_SPIN(j >= 4 && sig->stored < j - 3, 20, "lf body loader: ring", row * 3 + pl, j);
+                    if (intra_full)
+                        VP9_SPIN(*intra_full < j + 1, 40, "lf body loader: intra written back", row * 3 + pl, j);
                 }
-                if (lane == 0) __threadfence();
-                __syncwarp();
             }
+            if (lane == 0) __threadfence();
+            __syncwarp();
             const unsigned char *src = (const unsigned char *)(plane + (size_t)y0 * stride + j * S);
             unsigned char *dst = ring + 8 * RSB + (j & 3) * SLOT;
 #pragma unroll 4
@@ -340,9 +339,9 @@ __device__ void lf_row(const FrameDesc &f, int pl, int row, unsigned char *ring,
         if (has_top) {
             const volatile int *above = prog + row - 1;
             for (int c = 0; c < ncol; c++) {
-                while (c >= 4 && sig->stored < c - 3) __nanosleep(20);
                 if (lane == 0) {
-                    while (*above < c + 1) __nanosleep(20);
+                    VP9_SPIN(c >= 4 && sig->stored < c - 3, 20, "lf top loader: ring", row * 3 + pl, c);
+                    VP9_SPIN(*above < c + 1, 20, "lf top loader: row above", row * 3 + pl, c);
                     __threadfence();
                 }
                 __syncwarp();
@@ -361,14 +360,13 @@ __device__ void lf_row(const FrameDesc &f, int pl, int row, unsigned char *ring,
     } else {
         /* ------------------------------- storer ------------------------------- */
         for (int c = 0; c < ncol; c++) {
-            while (sig->done < c + 1) __nanosleep(20);
-            __threadfence_block();
-            if (intra_below) {
-                const int need = min(c + 2, ncol);
-                if (lane == 0)
-                    while (*intra_below < need) __nanosleep(40);
-                __syncwarp();
+            if (lane == 0) {
+                VP9_SPIN(sig->done < c + 1, 20, "lf storer: done", row * 3 + pl, c);
+                if (intra_below)
+                    VP9_SPIN(*intra_below < min(c + 2, ncol), 40, "lf storer: intra row below", row * 3 + pl, c);
+                __threadfence();
             }
+            __syncwarp();
             unsigned char *dst = (unsigned char *)(plane + (size_t)(y0 - 8) * stride + c * S);
             const unsigned char *src = ring + (c & 3) * SLOT;
             auto store_rows = [&](int r0, int r1) {
@@ -431,6 +429,32 @@ __global__ void __launch_bounds__(LF_THREADS) k_lf(const __grid_constant__ Frame
     __shared__ __align__(16) unsigned char sm[LfSmem<P>::BYTES];
     __shared__ LfSig sig;
     lf_cta<P>(f, blockIdx.x, sm, sig);
+}
+
+/* ---------------------------------------------------------------------------------------------- */
+/* k_wave: the intra wavefront and the loop-filter wavefront of one frame in ONE launch.
+ *
+ * CTAs [0, sb_rows) run intra_row, CTAs [sb_rows, 4*sb_rows) run lf_cta.  The loop filter of
+ * superblock row r follows the intra pass at a distance of about three superblocks: it reads
+ * block (r, j) once the intra pass has written it back (ifull[r] > j) and writes column block c
+ * once the intra row below has taken its pre-filter border row for columns c and c+1
+ * (iprogress[r+1] >= c+2) -- the role intra_pred_data plays in the reference (vp9.c:1404-1416).
+ * Every wait points at a CTA with a lower block index, so in-order CTA dispatch rules out
+ * deadlock even when the grid is larger than the machine (8K frames). */
+template <class P> struct WaveSmem {
+    static constexpr int BYTES = IntraSmem<P>::BYTES > LfSmem<P>::BYTES ? IntraSmem<P>::BYTES : LfSmem<P>::BYTES;
+};
+
+template <class P>
+__global__ void __launch_bounds__(INTRA_THREADS) k_wave(const __grid_constant__ FrameDesc f)
+{
+    extern __shared__ __align__(16) unsigned char sm[];
+    __shared__ IntraSig isig;
+    __shared__ LfSig lsig;
+    if ((int)blockIdx.x < f.sb_rows)
+        intra_row<P>(f, blockIdx.x, sm, isig);
+    else
+        lf_cta<P>(f, blockIdx.x - f.sb_rows, sm, lsig);
 }
 
 } /* namespace vp9 */

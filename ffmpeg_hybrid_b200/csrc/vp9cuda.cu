@@ -18,6 +18,8 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <time.h>
+#include <unistd.h>
 
 #include <algorithm>
 #include <mutex>
@@ -32,9 +34,39 @@
 
 using namespace vp9;
 
+#ifdef VP9CUDA_WATCHDOG
+static int *g_wd_host;
+static void wd_dump(void)
+{
+    if (!g_wd_host || !g_wd_host[0])
+        return;
+    fprintf(stderr, "vp9cuda watchdog: %d stuck waits\n", g_wd_host[0]);
+    for (int i = 0; i < g_wd_host[0] && i < 255; i++) {
+        const int *q = g_wd_host + 4 + 4 * i;
+        fprintf(stderr, "  line %d id %d at %d block %d\n", q[0], q[1], q[2], q[3]);
+    }
+    g_wd_host[0] = 0;
+}
+#elif defined(VP9CUDA_HEARTBEAT)
+static int *g_wd_host;
+static void wd_dump(void)
+{
+    if (!g_wd_host)
+        return;
+    for (int b = 0; b < 64; b++)
+        for (int w = 0; w < 32; w++) {
+            const int *q = g_wd_host + (b * 32 + w) * 4;
+            if (q[0] > 0)
+                fprintf(stderr, "  block %d warp %d waits at line %d id %d at %d\n", b, w, q[0], q[1], q[2]);
+        }
+}
+#else
+static void wd_dump(void) {}
+#endif
+
 #define CK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { \
     fprintf(stderr, "vp9cuda: %s failed at %s:%d: %s\n", #call, __FILE__, __LINE__, cudaGetErrorString(e_)); \
-    return -EIO; } } while (0)
+    wd_dump(); return -EIO; } } while (0)
 
 namespace {
 
@@ -101,12 +133,14 @@ struct DevRecords {
     bool used = false;
     cudaEvent_t uploaded = nullptr;    /* H2D of the records finished (upload stream) */
     cudaEvent_t dev_free = nullptr;    /* the kernels reading these records finished (compute stream) */
+    cudaEvent_t prepped = nullptr;     /* the pixel-independent pre-passes finished (prep stream) */
     bool wait_upload = false, has_free = false;
     void release()
     {
         if (uploaded) cudaEventDestroy(uploaded);
         if (dev_free) cudaEventDestroy(dev_free);
-        uploaded = dev_free = nullptr;
+        if (prepped) cudaEventDestroy(prepped);
+        uploaded = dev_free = prepped = nullptr;
         blk.release(); itx.release(); coef.release(); sb_index.release(); lf.release();
         for (auto &t : tx) t.release();
         cellmap.release(); isb.release(); irec.release(); ires.release(); itab.release(); iprogress.release(); lfops.release();
@@ -133,7 +167,7 @@ struct KStat {
     double ms = 0;
     uint64_t launches = 0, bytes = 0;
 };
-enum { KS_CELLMAP, KS_INTER, KS_ITX, KS_ISCHED, KS_INTRA, KS_LFOPS, KS_LF, KS_H2D, KS_D2H, KS_N };
+enum { KS_CELLMAP, KS_INTER, KS_ITX, KS_ISCHED, KS_INTRA, KS_LFOPS, KS_LF, KS_WAVE, KS_H2D, KS_D2H, KS_N };
 
 } /* namespace */
 
@@ -142,6 +176,10 @@ struct Vp9CudaCtx {
     cudaStream_t stream = nullptr;         /* compute */
     cudaStream_t s_up = nullptr;           /* record upload (H2D), overlaps the previous frame's kernels */
     cudaStream_t s_down = nullptr;         /* picture download (D2H), overlaps the next frame's kernels */
+    cudaStream_t s_prep = nullptr;         /* pixel-independent pre-passes, overlap the previous frame / inter stage */
+    int follow_mask = 3;                   /* debugging: 1 = wait for intra write-back, 2 = wait for the intra row below */
+    bool trace = false;                    /* VP9CUDA_TRACE: one stderr line per submitted / finished frame */
+    bool fuse_wave = true;                 /* set_option "fuse_wave": loop filter beside the intra wavefront */
     std::vector<Surface *> pool;           /* every surface ever allocated */
     Surface *ref[8] = { nullptr };
     Surface *last = nullptr;               /* most recently reconstructed frame */
@@ -158,7 +196,7 @@ struct Vp9CudaCtx {
     std::vector<int> tstage;               /* stage id of pair i */
     size_t tused = 0;
     cudaEvent_t marks[16] = { nullptr };
-    cudaEvent_t join_ev[2] = { nullptr, nullptr };
+    cudaEvent_t join_ev[3] = { nullptr, nullptr, nullptr };
     DBuf sum_buf;
     DBuf phase_clk;                        /* optional profiling counters (set_option "phase_clk") */
     bool phase_on = false;
@@ -219,6 +257,7 @@ static Surface *surface_get(Vp9CudaCtx *c, int w, int h, int bpp)
 static void sync_all(Vp9CudaCtx *c)
 {
     cudaStreamSynchronize(c->s_up);
+    cudaStreamSynchronize(c->s_prep);
     cudaStreamSynchronize(c->stream);
     cudaStreamSynchronize(c->s_down);
 }
@@ -272,6 +311,7 @@ static void kstat_resolve(Vp9CudaCtx *c)
         return;
     cudaStreamSynchronize(c->stream);
     cudaStreamSynchronize(c->s_up);
+    cudaStreamSynchronize(c->s_prep);
     cudaStreamSynchronize(c->s_down);
     for (size_t i = 0; i < c->tused; i++) {
         float ms = 0;
@@ -316,7 +356,7 @@ static int upload_records(Vp9CudaCtx *c, DevRecords &d, const Vp9CudaFrameHeader
     r |= d.irec.reserve(n_itx * sizeof(IntraRec));
     if (n_itx) r |= d.ires.reserve((size_t)n_sb * INTRA_SB_RES * 2);
     if (n_itx) r |= d.itab.reserve((size_t)n_sb * INTRA_SB_TAB * 2);
-    r |= d.iprogress.reserve((size_t)sb_rows * 4);
+    r |= d.iprogress.reserve((size_t)2 * sb_rows * 4);
     r |= d.lfops.reserve((size_t)n_sb * 3 * sizeof(LfSched));
     r |= d.progress.reserve((size_t)3 * sb_rows * 4);
     if (r)
@@ -324,10 +364,11 @@ static int upload_records(Vp9CudaCtx *c, DevRecords &d, const Vp9CudaFrameHeader
     if (!d.uploaded) {
         CK(cudaEventCreateWithFlags(&d.uploaded, cudaEventDisableTiming));
         CK(cudaEventCreateWithFlags(&d.dev_free, cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&d.prepped, cudaEventDisableTiming));
     }
     if (d.has_free) {                       /* the previous user of this landing zone must be done */
         CK(cudaStreamWaitEvent(c->s_up, d.dev_free, 0));
-        d.has_free = false;
+        d.has_free = false;                 /* the prep stream follows the upload, hence dev_free */
     }
     kstat_begin(c, c->s_up);
     uint64_t o_blk = 0, o_tx[4] = { 0, 0, 0, 0 }, o_itx = 0, bytes = 0;
@@ -375,10 +416,42 @@ static int upload_records(Vp9CudaCtx *c, DevRecords &d, const Vp9CudaFrameHeader
  * reconstruction of one frame from device-resident records
  * ---------------------------------------------------------------------------------------- */
 template <class P, bool HBD>
-static int launch_frame(Vp9CudaCtx *c, const FrameDesc &f, const DevRecords &d)
+static int launch_frame(Vp9CudaCtx *c, FrameDesc &f, DevRecords &d)
 {
-    cudaStream_t s = c->stream;
+    cudaStream_t s = c->stream, sp = c->s_prep;
     const uint64_t P_bytes = (uint64_t)f.w * f.h * 3 / 2 * sizeof(P);
+    const bool fused = c->fuse_wave && f.n_itx && f.lf_level;
+    f.lf_follow = fused ? c->follow_mask : 0;
+    /* ---- prep stream: everything that depends on the records only (sorting the intra blocks
+     * into dependency steps, their residuals, the loop-filter edge schedule).  Runs beside the
+     * inter stage of this frame and the wavefronts of the previous one. ---- */
+    if (f.n_itx || f.lf_level) {
+        if (d.has_free)                        /* staged records: scratch still read by their previous run */
+            CK(cudaStreamWaitEvent(sp, d.dev_free, 0));
+        if (d.wait_upload)
+            CK(cudaStreamWaitEvent(sp, d.uploaded, 0));
+        if (f.n_itx) {
+            if (f.sb_cols > INTRA_MAX_SB_COLS)
+                return -EINVAL;
+            kstat_begin(c, sp);
+            k_intra_prep<<<f.sb_cols * f.sb_rows, 128, 0, sp>>>(f);
+            k_intra_res<HBD><<<f.sb_cols * f.sb_rows, IRES_WARPS * 32, 0, sp>>>(f);
+            CK(cudaMemsetAsync(f.iprogress, 0, (size_t)2 * f.sb_rows * 4, sp));
+            kstat_end(c, KS_ISCHED, 2, (uint64_t)f.n_itx * (sizeof(Vp9CudaIntraTx) + sizeof(IntraRec)), sp);
+        }
+        if (f.lf_level) {
+            kstat_begin(c, sp);
+            k_lf_sched<<<f.sb_cols * f.sb_rows, LF_SCHED_THREADS, 0, sp>>>(f);
+            CK(cudaMemsetAsync(f.progress, 0, (size_t)3 * f.sb_rows * 4, sp));
+            kstat_end(c, KS_LFOPS, 1, (uint64_t)f.sb_cols * f.sb_rows * (sizeof(Vp9CudaLoopFilterSb) + 3 * sizeof(LfSched)), sp);
+        }
+        CK(cudaEventRecord(d.prepped, sp));
+    }
+    if (d.wait_upload) {
+        CK(cudaStreamWaitEvent(s, d.uploaded, 0));
+        d.wait_upload = false;
+    }
+    /* ---- compute stream ---- */
     if (f.n_blk) {
         kstat_begin(c);
         CK(cudaMemsetAsync(f.cellmap, 0xff, (size_t)f.cols * f.rows * 4, s));
@@ -399,29 +472,25 @@ static int launch_frame(Vp9CudaCtx *c, const FrameDesc &f, const DevRecords &d)
         itx_bytes += (uint64_t)f.n_tx[t] * (16u << (2 * t)) * ((HBD ? 4 : 2) + 2 * sizeof(P));
     if (itx_launches)
         kstat_end(c, KS_ITX, itx_launches, itx_bytes);
-    if (f.n_itx) {
-        if (f.sb_cols > INTRA_MAX_SB_COLS)
-            return -EINVAL;
+    if (f.n_itx || f.lf_level)
+        CK(cudaStreamWaitEvent(s, d.prepped, 0));
+    if (fused) {
         kstat_begin(c);
-        k_intra_prep<<<f.sb_cols * f.sb_rows, 128, 0, s>>>(f);
-        k_intra_res<HBD><<<f.sb_cols * f.sb_rows, IRES_WARPS * 32, 0, s>>>(f);
-        kstat_end(c, KS_ISCHED, 2, (uint64_t)f.n_itx * (sizeof(Vp9CudaIntraTx) + sizeof(IntraRec)));
-        kstat_begin(c);
-        CK(cudaMemsetAsync(f.iprogress, 0, (size_t)f.sb_rows * 4, s));
-        k_intra<P><<<f.sb_rows, INTRA_THREADS, IntraSmem<P>::BYTES, s>>>(f);
-        kstat_end(c, KS_INTRA, 1, P_bytes);
-    }
-    if (f.lf_level) {
-        kstat_begin(c);
-        k_lf_sched<<<f.sb_cols * f.sb_rows, LF_SCHED_THREADS, 0, s>>>(f);
-        kstat_end(c, KS_LFOPS, 1, (uint64_t)f.sb_cols * f.sb_rows * (sizeof(Vp9CudaLoopFilterSb) + 3 * sizeof(LfSched)));
-        kstat_begin(c);
-        CK(cudaMemsetAsync(f.progress, 0, (size_t)3 * f.sb_rows * 4, s));
-        k_lf<P><<<3 * f.sb_rows, LF_THREADS, 0, s>>>(f);
-        kstat_end(c, KS_LF, 1, 2 * P_bytes);
+        k_wave<P><<<4 * f.sb_rows, INTRA_THREADS, WaveSmem<P>::BYTES, s>>>(f);
+        kstat_end(c, KS_WAVE, 1, 3 * P_bytes);
+    } else {
+        if (f.n_itx) {
+            kstat_begin(c);
+            k_intra<P><<<f.sb_rows, INTRA_THREADS, IntraSmem<P>::BYTES, s>>>(f);
+            kstat_end(c, KS_INTRA, 1, P_bytes);
+        }
+        if (f.lf_level) {
+            kstat_begin(c);
+            k_lf<P><<<3 * f.sb_rows, LF_THREADS, 0, s>>>(f);
+            kstat_end(c, KS_LF, 1, 2 * P_bytes);
+        }
     }
     CK(cudaGetLastError());
-    (void)d;
     return 0;
 }
 
@@ -452,6 +521,28 @@ static int make_ticket(Vp9CudaCtx *c, uint64_t *ticket, cudaStream_t st)
     if (ticket)
         *ticket = t;
     return 0;
+}
+
+/* VP9CUDA_TRACE: wait for `ev`; a frame that does not finish within 3 s gets its wavefront
+ * counters printed (read over the idle upload stream) and the process ends. */
+static void trace_wait(Vp9CudaCtx *c, const DevRecords &d, cudaEvent_t ev)
+{
+    for (int i = 0; cudaEventQuery(ev) == cudaErrorNotReady; i++) {
+        struct timespec ts = { 0, 1000000 };
+        nanosleep(&ts, nullptr);
+        if (i < 3000)
+            continue;
+        const int sb_rows = (d.hdr.h + 63) >> 6;
+        std::vector<int> ip(2 * sb_rows), lp(3 * sb_rows);
+        cudaMemcpyAsync(ip.data(), d.iprogress.p, ip.size() * 4, cudaMemcpyDeviceToHost, c->s_up);
+        cudaMemcpyAsync(lp.data(), d.progress.p, lp.size() * 4, cudaMemcpyDeviceToHost, c->s_up);
+        cudaStreamSynchronize(c->s_up);
+        fprintf(stderr, "vp9cuda: frame stuck; per superblock row: intra border / intra stored | lf Y / lf U / lf V\n");
+        for (int r = 0; r < sb_rows; r++)
+            fprintf(stderr, "  row %d: %d %d | %d %d %d\n", r, ip[r], ip[sb_rows + r], lp[r], lp[sb_rows + r], lp[2 * sb_rows + r]);
+        fflush(stderr);
+        _exit(3);
+    }
 }
 
 static int reconstruct(Vp9CudaCtx *c, DevRecords &d, uint8_t *const out_planes[3],
@@ -499,10 +590,9 @@ static int reconstruct(Vp9CudaCtx *c, DevRecords &d, uint8_t *const out_planes[3
     memcpy(f.lim_lut, h.lim_lut, 64);
     memcpy(f.mblim_lut, h.mblim_lut, 64);
 
-    if (d.wait_upload) {
-        CK(cudaStreamWaitEvent(c->stream, d.uploaded, 0));
-        d.wait_upload = false;
-    }
+    if (c->trace)
+        fprintf(stderr, "vp9cuda: frame %dx%d bpp %d blk %u itx %u lf %d fuse %d\n", h.w, h.h, h.bpp, d.n_blk, d.n_itx,
+                h.lf_level, (int)(c->fuse_wave && d.n_itx && h.lf_level));
     int r = h.bpp > 8 ? launch_frame<uint16_t, true>(c, f, d) : launch_frame<uint8_t, false>(c, f, d);
     if (r == 0 && d.dev_free) {
         CK(cudaEventRecord(d.dev_free, c->stream));
@@ -510,6 +600,8 @@ static int reconstruct(Vp9CudaCtx *c, DevRecords &d, uint8_t *const out_planes[3
     }
     if (r == 0)
         CK(cudaEventRecord(cur->ready, c->stream));
+    if (r == 0 && c->trace)
+        trace_wait(c, d, cur->ready);
     if (r < 0) {
         surface_unref(cur);
         return r;
@@ -536,7 +628,7 @@ static int reconstruct(Vp9CudaCtx *c, DevRecords &d, uint8_t *const out_planes[3
  * C ABI
  * ---------------------------------------------------------------------------------------- */
 static const char *const ks_names[KS_N] = { "cellmap", "inter_pred", "itxfm_add", "intra_sort",
-                                            "intra_wavefront", "lf_ops", "loop_filter", "h2d_records",
+                                            "intra_wavefront", "lf_ops", "loop_filter", "intra_lf_wavefront", "h2d_records",
                                             "d2h_frame" };
 
 extern "C" const char *vp9cuda_version(void)
@@ -564,6 +656,9 @@ extern "C" int vp9cuda_create(Vp9CudaCtx **out, int device, int max_w, int max_h
     CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     CK(cudaStreamCreateWithFlags(&c->s_up, cudaStreamNonBlocking));
     CK(cudaStreamCreateWithFlags(&c->s_down, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&c->s_prep, cudaStreamNonBlocking));
+    CK(cudaFuncSetAttribute(k_wave<uint8_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, WaveSmem<uint8_t>::BYTES));
+    CK(cudaFuncSetAttribute(k_wave<uint16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, WaveSmem<uint16_t>::BYTES));
     CK(cudaFuncSetAttribute(k_intra<uint8_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, IntraSmem<uint8_t>::BYTES));
     CK(cudaFuncSetAttribute(k_intra<uint16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, IntraSmem<uint16_t>::BYTES));
     c->ticket_ev.resize(256);
@@ -573,6 +668,21 @@ extern "C" int vp9cuda_create(Vp9CudaCtx **out, int device, int max_w, int max_h
         CK(cudaEventCreate(&e));
     for (auto &e : c->join_ev)
         CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+#if defined(VP9CUDA_WATCHDOG) || defined(VP9CUDA_HEARTBEAT)
+    if (!g_wd_host) {
+        int *dp = nullptr;
+        CK(cudaHostAlloc((void **)&g_wd_host, 64 * 32 * 16, cudaHostAllocMapped));
+        memset(g_wd_host, 0, 64 * 32 * 16);
+        CK(cudaHostGetDevicePointer((void **)&dp, g_wd_host, 0));
+        CK(cudaMemcpyToSymbol(vp9::g_wd_buf, &dp, sizeof(dp)));
+    }
+#endif
+    if (const char *e = getenv("VP9CUDA_TRACE"))
+        c->trace = atoi(e) != 0;
+    if (const char *e = getenv("VP9CUDA_FOLLOW_MASK"))
+        c->follow_mask = atoi(e);
+    if (const char *e = getenv("VP9CUDA_FUSE_WAVE"))
+        c->fuse_wave = atoi(e) != 0;
     if (frames_in_flight < 1) frames_in_flight = 1;
     if (frames_in_flight > 16) frames_in_flight = 16;
     for (int i = 0; i < frames_in_flight; i++) {
@@ -634,6 +744,7 @@ extern "C" void vp9cuda_destroy(Vp9CudaCtx *c)
     cudaStreamDestroy(c->stream);
     cudaStreamDestroy(c->s_up);
     cudaStreamDestroy(c->s_down);
+    cudaStreamDestroy(c->s_prep);
     delete c;
 }
 
@@ -780,8 +891,22 @@ extern "C" int vp9cuda_wait(Vp9CudaCtx *c, uint64_t ticket)
         CK(cudaStreamSynchronize(c->s_down));
         return 0;
     }
+#ifdef VP9CUDA_HEARTBEAT
+    for (int i = 0; cudaEventQuery(c->ticket_ev[ticket % c->ticket_ev.size()]) == cudaErrorNotReady; i++) {
+        struct timespec ts = { 0, 1000000 };
+        nanosleep(&ts, nullptr);
+        if (i == 3000) {
+            fprintf(stderr, "vp9cuda heartbeat: frame not finished after 3 s\n");
+            wd_dump();
+            fflush(stderr);
+            _exit(3);
+        }
+    }
+#endif
     CK(cudaEventSynchronize(c->ticket_ev[ticket % c->ticket_ev.size()]));
     CK(cudaGetLastError());
+    if (c->trace)
+        fprintf(stderr, "vp9cuda: ticket %llu done\n", (unsigned long long)ticket);
     return 0;
 }
 
@@ -879,6 +1004,10 @@ extern "C" int vp9cuda_set_option(Vp9CudaCtx *c, const char *key, int value)
         c->timing = value != 0;
         return 0;
     }
+    if (!strcmp(key, "fuse_wave")) {       /* 1 (default): k_wave; 0: separate k_intra / k_lf launches */
+        c->fuse_wave = value != 0;
+        return 0;
+    }
     if (!strcmp(key, "mark")) {            /* record timing mark `value` (0..15) on the ctx stream */
         if (value < 0 || value > 15)
             return -EINVAL;
@@ -886,6 +1015,8 @@ extern "C" int vp9cuda_set_option(Vp9CudaCtx *c, const char *key, int value)
         /* join the upload and download streams so the mark brackets everything submitted so far */
         CK(cudaEventRecord(c->join_ev[0], c->s_up));
         CK(cudaEventRecord(c->join_ev[1], c->s_down));
+        CK(cudaEventRecord(c->join_ev[2], c->s_prep));
+        CK(cudaStreamWaitEvent(c->stream, c->join_ev[2], 0));
         CK(cudaStreamWaitEvent(c->stream, c->join_ev[0], 0));
         CK(cudaStreamWaitEvent(c->stream, c->join_ev[1], 0));
         CK(cudaEventRecord(c->marks[value], c->stream));

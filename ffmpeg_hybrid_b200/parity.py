@@ -27,7 +27,8 @@ def write_stream(spec, path: Path) -> Path:
     return path
 
 
-def _run(cmd: List[str], env=None, timeout=600) -> Tuple[int, str, str]:
+def _run(cmd: List[str], env=None, timeout=None) -> Tuple[int, str, str]:
+    timeout = timeout or float(os.environ.get("VP9CUDA_TEST_TIMEOUT", "600"))
     p = subprocess.run(cmd, capture_output=True, text=True, env=env, timeout=timeout)
     return p.returncode, p.stdout, p.stderr
 
