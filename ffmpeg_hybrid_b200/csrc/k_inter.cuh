@@ -9,8 +9,8 @@
  *               Reference samples are read with coordinate clamping (= the reference's
  *               emulated_edge_mc, vp9recon.c:402-412).  Compound blocks average the two
  *               predictions in registers (vp9dsp_template.c:2051: (dst + pred + 1) >> 1).
- *               Scaled references and everything else the strip path does not cover go
- *               through the per-pixel path (vp9::mc_pixel).
+ *               Scaled references use the same strip with a sliding window of
+ *               horizontally filtered rows (mc_strip_scaled).
  *
  * Replaces inter_pred (vp9_mc_template.c:30-464) + mc_luma/chroma_{unscaled,scaled}
  * (vp9recon.c:376-628) + the mc/smc slots (vp9dsp_template.c:1969-2569).
@@ -36,76 +36,130 @@ __global__ void k_cellmap(const Vp9CudaInterBlock *__restrict__ blk, uint32_t n,
             cellmap[(row + y) * cols + col + x] = (int32_t)i;
 }
 
-/* horizontal stage for one sample */
-template <class P>
+/* horizontal stage for one sample; CLAMP = false when the caller knows every tap is inside the plane */
+template <class P, bool CLAMP>
 __device__ __forceinline__ int mc_hrow(const RefPlane<P> &r, int x, int y, int filter, int phx, int bpp)
 {
-    if (phx == 0)
-        return r.at(x, y);
-    int s[8];
+    if (CLAMP) {
+        if (phx == 0)
+            return r.at(x, y);
+        int s[8];
 #pragma unroll
-    for (int i = 0; i < 8; i++)
-        s[i] = r.at(x + i - 3, y);
-    return filt8(s, filter, phx, bpp);
+        for (int i = 0; i < 8; i++)
+            s[i] = r.at(x + i - 3, y);
+        return filt8(s, filter, phx, bpp);
+    } else {
+        const P *row = r.pix + (size_t)y * r.stride + x;
+        if (phx == 0)
+            return row[0];
+        int s[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++)
+            s[i] = row[i - 3];
+        return filt8(s, filter, phx, bpp);
+    }
 }
 
 /* NR vertically adjacent outputs at integer reference position (x, y), phases (phx, phy) */
-template <class P, int NR>
-__device__ __forceinline__ void mc_strip(const RefPlane<P> &r, int x, int y, int phx, int phy,
-                                         int filter, int bpp, int *out)
+template <class P, int NR, bool CLAMP>
+__device__ __forceinline__ void mc_strip_c(const RefPlane<P> &r, int x, int y, int phx, int phy,
+                                           int filter, int bpp, int *out)
 {
     if (phy == 0) {
 #pragma unroll
         for (int j = 0; j < NR; j++)
-            out[j] = mc_hrow(r, x, y + j, filter, phx, bpp);
+            out[j] = mc_hrow<P, CLAMP>(r, x, y + j, filter, phx, bpp);
     } else {
         int hbuf[NR + 7];
 #pragma unroll
         for (int j = 0; j < NR + 7; j++)
-            hbuf[j] = mc_hrow(r, x, y - 3 + j, filter, phx, bpp);
+            hbuf[j] = mc_hrow<P, CLAMP>(r, x, y - 3 + j, filter, phx, bpp);
 #pragma unroll
         for (int j = 0; j < NR; j++)
             out[j] = filt8(&hbuf[j], filter, phy, bpp);
     }
 }
 
-/* Prediction of pixel (X, Y) of plane pl from reference i of block b: the general path.
- * Works out which prediction call of inter_pred() the pixel belongs to. */
-template <class P>
-__device__ int inter_px_general(const FrameDesc &f, const Vp9CudaInterBlock &b, int i, int pl, int X, int Y)
+template <class P, int NR>
+__device__ __forceinline__ void mc_strip(const RefPlane<P> &r, int x, int y, int phx, int phy,
+                                         int filter, int bpp, int *out)
 {
+    /* interior strips (nearly all of them) skip the coordinate clamps of the edge emulation */
+    if (x >= 3 && x + 4 < r.w && y >= 3 && y + NR + 3 < r.h)
+        mc_strip_c<P, NR, false>(r, x, y, phx, phy, filter, bpp, out);
+    else
+        mc_strip_c<P, NR, true>(r, x, y, phx, phy, filter, bpp, out);
+}
+
+/* Scaled reference (smc slots, vp9dsp_template.c:2363-2470): NR vertically adjacent outputs at
+ * offset (ox, oy .. oy+NR-1) of a prediction call at position p.  The column's integer position
+ * and phase are fixed; the row position advances by p.dy/16 per output, so the eight
+ * horizontally filtered rows under the vertical taps slide down by 0..2 rows per output.  Same
+ * values as mc_pixel (vp9_pred.h): horizontal pass rounded and clipped to a pixel, then vertical. */
+template <class P, int NR>
+__device__ __forceinline__ void mc_strip_scaled(const RefPlane<P> &r, const McPos &p, int ox, int oy,
+                                                int filter, int bpp, int *out)
+{
+    const int ax = p.fx + ox * p.dx;
+    const int x = p.x0 + (ax >> 4), phx = ax & 15;
+    int ay = p.fy + oy * p.dy;
+    int cur = (ay >> 4) - 8;             /* the first output pulls in all eight rows */
+    int win[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };
+    /* one call site for the row filter keeps the kernel small: rolled loops, outputs collected in
+     * a 128-bit shift register (pixels are at most 12 bits wide) */
+    unsigned long long lo = 0, hi = 0;
+#pragma unroll 1
+    for (int j = 0; j < NR; j++) {
+        const int tgt = ay >> 4;
+#pragma unroll 1
+        while (cur < tgt) {
+#pragma unroll
+            for (int t = 0; t < 7; t++)
+                win[t] = win[t + 1];
+            cur++;
+            win[7] = mc_hrow<P, true>(r, x, p.y0 + cur + 4, filter, phx, bpp);
+        }
+        const unsigned long long v = (unsigned long long)filt8(win, filter, ay & 15, bpp);
+        lo = (lo >> 16) | (hi << 48);
+        hi = (hi >> 16) | (v << 48);
+        ay += p.dy;
+    }
+#pragma unroll
+    for (int j = 0; j < NR; j++) {
+        const int k = 8 - NR + j;        /* position in the 8-entry register */
+        out[j] = (int)(((k < 4 ? lo >> (16 * k) : hi >> (16 * (k - 4)))) & 0xffff);
+    }
+}
+
+/* Geometry of the prediction call of inter_pred() (vp9_mc_template.c:30-464) that covers pixel
+ * (X, Y) of plane pl for reference i of block b: origin of the call in the plane, its offset and
+ * the size of the coding block (the scaled path's MV clamp needs them), and the motion vector. */
+struct InterCall {
+    int ox0, oy0, px, py, pw, ph, mvx, mvy;
+};
+__device__ __forceinline__ InterCall inter_call(const Vp9CudaInterBlock &b, int i, int pl, int X, int Y)
+{
+    InterCall c;
     const int ch = pl > 0;
-    const int sub8 = b.bs > 9;
-    int ox0, oy0, px = 0, py = 0, pw, ph, mvx, mvy;
-    if (sub8) {
+    c.px = c.py = 0;
+    if (b.bs > 9) {
         if (!ch) {
-            int k = ((Y >> 2) & 1) * 2 + ((X >> 2) & 1);
-            px = 4 * (k & 1); py = 4 * (k >> 1); pw = ph = 8;
-            ox0 = b.col * 8 + px; oy0 = b.row * 8 + py;
-            mvx = b.mv[k][i][0]; mvy = b.mv[k][i][1];
+            const int k = ((Y >> 2) & 1) * 2 + ((X >> 2) & 1);
+            c.px = 4 * (k & 1); c.py = 4 * (k >> 1); c.pw = c.ph = 8;
+            c.ox0 = b.col * 8 + c.px; c.oy0 = b.row * 8 + c.py;
+            c.mvx = b.mv[k][i][0]; c.mvy = b.mv[k][i][1];
         } else {
-            pw = ph = 4;
-            ox0 = b.col * 4; oy0 = b.row * 4;
-            mvx = rounded_div(b.mv[0][i][0] + b.mv[1][i][0] + b.mv[2][i][0] + b.mv[3][i][0], 4);
-            mvy = rounded_div(b.mv[0][i][1] + b.mv[1][i][1] + b.mv[2][i][1] + b.mv[3][i][1], 4);
+            c.pw = c.ph = 4;
+            c.ox0 = b.col * 4; c.oy0 = b.row * 4;
+            c.mvx = rounded_div(b.mv[0][i][0] + b.mv[1][i][0] + b.mv[2][i][0] + b.mv[3][i][0], 4);
+            c.mvy = rounded_div(b.mv[0][i][1] + b.mv[1][i][1] + b.mv[2][i][1] + b.mv[3][i][1], 4);
         }
     } else {
-        pw = (bs_w8(b.bs) * 8) >> ch; ph = (bs_h8(b.bs) * 8) >> ch;
-        ox0 = (b.col * 8) >> ch; oy0 = (b.row * 8) >> ch;
-        mvx = b.mv[0][i][0]; mvy = b.mv[0][i][1];
+        c.pw = (bs_w8(b.bs) * 8) >> ch; c.ph = (bs_h8(b.bs) * 8) >> ch;
+        c.ox0 = (b.col * 8) >> ch; c.oy0 = (b.row * 8) >> ch;
+        c.mvx = b.mv[0][i][0]; c.mvy = b.mv[0][i][1];
     }
-    const int ri = b.ref[i];
-    const SurfDesc &rs = f.ref[ri];
-    RefPlane<P> rp;
-    rp.pix = (const P *)rs.pl[pl]; rp.stride = rs.stride[pl];
-    rp.w = (rs.w + ch) >> ch; rp.h = (rs.h + ch) >> ch;
-    McPos pos;
-    if (f.mvscale[ri][0])
-        pos = mc_pos_scaled(ox0, oy0, mvx, mvy, ch, px, py, pw, ph, f.cols, f.rows, f.mvscale[ri][0],
-                            f.mvscale[ri][1], f.mvstep[ri][0], f.mvstep[ri][1]);
-    else
-        pos = mc_pos_unscaled(ox0, oy0, mvx, mvy, ch);
-    return mc_pixel(rp, pos, X - ox0, Y - oy0, b.filter, f.bpp);
+    return c;
 }
 
 /* One strip of NR rows at column X starting at row Y of plane pl, all inside one 8x8 cell
@@ -115,33 +169,22 @@ __device__ __forceinline__ void inter_strip(const FrameDesc &f, const Vp9CudaInt
                                             int Y, int *out)
 {
     const int ch = pl > 0;
-    const int sub8 = b.bs > 9;
     const int nref = b.comp ? 2 : 1;
     int acc[NR];
     for (int i = 0; i < nref; i++) {
         const int ri = b.ref[i];
+        const InterCall c = inter_call(b, i, pl, X, Y);
+        const SurfDesc &rs = f.ref[ri];
+        RefPlane<P> rp;
+        rp.pix = (const P *)rs.pl[pl]; rp.stride = rs.stride[pl];
+        rp.w = (rs.w + ch) >> ch; rp.h = (rs.h + ch) >> ch;
         int v[NR];
         if (f.mvscale[ri][0]) {
-            for (int j = 0; j < NR; j++)
-                v[j] = inter_px_general<P>(f, b, i, pl, X, Y + j);
+            const McPos pos = mc_pos_scaled(c.ox0, c.oy0, c.mvx, c.mvy, ch, c.px, c.py, c.pw, c.ph, f.cols, f.rows,
+                                            f.mvscale[ri][0], f.mvscale[ri][1], f.mvstep[ri][0], f.mvstep[ri][1]);
+            mc_strip_scaled<P, NR>(rp, pos, X - c.ox0, Y - c.oy0, b.filter, f.bpp, v);
         } else {
-            int mvx, mvy;
-            if (sub8) {
-                if (!ch) {
-                    int k = ((Y >> 2) & 1) * 2 + ((X >> 2) & 1);
-                    mvx = b.mv[k][i][0]; mvy = b.mv[k][i][1];
-                } else {
-                    mvx = rounded_div(b.mv[0][i][0] + b.mv[1][i][0] + b.mv[2][i][0] + b.mv[3][i][0], 4);
-                    mvy = rounded_div(b.mv[0][i][1] + b.mv[1][i][1] + b.mv[2][i][1] + b.mv[3][i][1], 4);
-                }
-            } else {
-                mvx = b.mv[0][i][0]; mvy = b.mv[0][i][1];
-            }
-            const SurfDesc &rs = f.ref[ri];
-            RefPlane<P> rp;
-            rp.pix = (const P *)rs.pl[pl]; rp.stride = rs.stride[pl];
-            rp.w = (rs.w + ch) >> ch; rp.h = (rs.h + ch) >> ch;
-            McPos pos = mc_pos_unscaled(X, Y, mvx, mvy, ch);
+            const McPos pos = mc_pos_unscaled(X, Y, c.mvx, c.mvy, ch);
             mc_strip<P, NR>(rp, pos.x0, pos.y0, pos.fx, pos.fy, b.filter, f.bpp, v);
         }
         if (i == 0) {
@@ -157,7 +200,7 @@ __device__ __forceinline__ void inter_strip(const FrameDesc &f, const Vp9CudaInt
 }
 
 template <class P>
-__global__ void __launch_bounds__(256) k_inter(const __grid_constant__ FrameDesc f)
+__global__ void __launch_bounds__(256, sizeof(P) == 2 ? 3 : 2) k_inter(const __grid_constant__ FrameDesc f)
 {
     const int tid = threadIdx.x;
     const int X0 = blockIdx.x * 64, Y0 = blockIdx.y * 32;
