@@ -30,7 +30,7 @@ struct IntraSb {
     uint16_t count;                  /* intra transform blocks (all planes); 0 = nothing to do */
     uint16_t ntab;                   /* entries of its work table (itab) */
     uint16_t has_res;                /* any of them has coefficients */
-    uint16_t pad;
+    uint16_t needs_top;              /* some block reads intra pixels of the superblock row above */
     uint32_t pad2;
 };
 /* ... and one per intra transform block, sorted by dependency depth inside the superblock */

@@ -72,7 +72,7 @@ __global__ void __launch_bounds__(128) k_intra_prep(const __grid_constant__ Fram
     __shared__ uint32_t inf[512];
     __shared__ uint8_t loc[512];
     __shared__ uint8_t lvl[3 * 256];
-    __shared__ unsigned any_res;
+    __shared__ unsigned any_res, need_top;
     const int sb = blockIdx.x, tid = threadIdx.x;
     const Vp9CudaSbIndex si = f.sb_index[sb];
     const int n = si.itx_count;
@@ -84,7 +84,7 @@ __global__ void __launch_bounds__(128) k_intra_prep(const __grid_constant__ Fram
         }
         return;
     }
-    if (tid == 0) any_res = 0;
+    if (tid == 0) { any_res = 0; need_top = 0; }
     int m = 32;
     while (m < n) m <<= 1;
     const int sbx = sb % f.sb_cols, sby = sb / f.sb_cols;
@@ -103,6 +103,21 @@ __global__ void __launch_bounds__(128) k_intra_prep(const __grid_constant__ Fram
                      (r.eob ? 1 : 0) << 18 | (have_top ? 1 : 0) << 19;
             if (r.eob)
                 any_res = 1;
+            /* Does this block read pixels of an INTRA block of the superblock row above?  Only then
+             * must the row's wavefront wait for the row above; inter pixels are final already.
+             * Cells read: from the top-left sample to the end of a possible top-right extension. */
+            if (ly == 0 && have_top && (intra_mode_needs(cmode) & 14)) {
+                if (f.n_blk == 0) {
+                    need_top = 1;
+                } else {
+                    const int px0 = r.x4 * 4 - 1, px1 = r.x4 * 4 + (8 << r.tx) - 1;
+                    const int c0 = max(ch ? px0 >> 2 : px0 >> 3, 0), c1 = min(ch ? px1 >> 2 : px1 >> 3, f.cols - 1);
+                    const int32_t *above = f.cellmap + (size_t)(sby * 8 - 1) * f.cols;
+                    for (int cx = c0; cx <= c1; cx++)
+                        if (above[cx] < 0)
+                            need_top = 1;
+                }
+            }
         }
         keys[i] = key;
     }
@@ -243,7 +258,7 @@ __global__ void __launch_bounds__(128) k_intra_prep(const __grid_constant__ Fram
                 tab[hdr_pos[j]] = (uint16_t)(0x8000 | scnt[sidx - 1]);
         }
         if (tid == 0) {
-            IntraSb o = { g0, (uint16_t)n, (uint16_t)(totc + tots), (uint16_t)any_res, 0, 0 };
+            IntraSb o = { g0, (uint16_t)n, (uint16_t)(totc + tots), (uint16_t)any_res, (uint16_t)need_top, 0 };
             f.isb[sb] = o;
         }
     }
@@ -372,7 +387,7 @@ __device__ __forceinline__ void intra_row(const FrameDesc &f, const int row, uns
                 __threadfence_block();
             }
             asm volatile("bar.sync 1, %0;\n" ::"n"(INTRA_CT) : "memory");
-            int nsteps = 0;
+            int nsteps = 0, nrounds = 0, nchunks = 0, ntop = info[c].needs_top;
             const IntraRec *rec = recbuf + (c & 3) * INTRA_SB_RECS;
             const int16_t *res = resbuf + (c & 3) * INTRA_SB_RES;
             const uint16_t *tab = tabbuf + (c & 3) * INTRA_SB_TAB;
@@ -422,6 +437,8 @@ __device__ __forceinline__ void intra_row(const FrameDesc &f, const int row, uns
                 asm volatile("bar.sync 1, %0;\n" ::"n"(INTRA_CT) : "memory");
                 pos += cnt + 1;
                 nsteps++;
+                nrounds += (cnt + INTRA_CW - 1) / INTRA_CW;
+                nchunks += cnt;
             }
             if (threadIdx.x == 0) {
                 __threadfence_block();
@@ -431,6 +448,9 @@ __device__ __forceinline__ void intra_row(const FrameDesc &f, const int row, uns
                     atomicAdd(&f.phase_clk[13], (unsigned long long)nsteps);
                     atomicAdd(&f.phase_clk[14], 1ull);
                     atomicAdd(&f.phase_clk[15], (unsigned long long)n);
+                    atomicAdd(&f.phase_clk[16], (unsigned long long)nrounds);
+                    atomicAdd(&f.phase_clk[17], (unsigned long long)nchunks);
+                    atomicAdd(&f.phase_clk[18], (unsigned long long)ntop);
                 }
             }
         }
@@ -506,7 +526,8 @@ __device__ __forceinline__ void intra_row(const FrameDesc &f, const int row, uns
                 }
                 if (lane == 0) {
                     VP9_SPIN(sig.done < c - 2 || sig.stored < c - 3, 20, "intra top loader: ring", row, c);
-                    VP9_SPIN(*above < c + 1, 20, "intra top loader: row above", row, c);
+                    if (info[c].needs_top)
+                        VP9_SPIN(*above < c + 1, 20, "intra top loader: row above", row, c);
                     __threadfence();
                 }
                 __syncwarp();

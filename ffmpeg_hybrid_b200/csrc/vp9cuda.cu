@@ -134,13 +134,15 @@ struct DevRecords {
     cudaEvent_t uploaded = nullptr;    /* H2D of the records finished (upload stream) */
     cudaEvent_t dev_free = nullptr;    /* the kernels reading these records finished (compute stream) */
     cudaEvent_t prepped = nullptr;     /* the pixel-independent pre-passes finished (prep stream) */
+    cudaEvent_t cellmapped = nullptr;  /* the cell map is built (prep stream) */
     bool wait_upload = false, has_free = false;
     void release()
     {
         if (uploaded) cudaEventDestroy(uploaded);
         if (dev_free) cudaEventDestroy(dev_free);
         if (prepped) cudaEventDestroy(prepped);
-        uploaded = dev_free = prepped = nullptr;
+        if (cellmapped) cudaEventDestroy(cellmapped);
+        uploaded = dev_free = prepped = cellmapped = nullptr;
         blk.release(); itx.release(); coef.release(); sb_index.release(); lf.release();
         for (auto &t : tx) t.release();
         cellmap.release(); isb.release(); irec.release(); ires.release(); itab.release(); iprogress.release(); lfops.release();
@@ -365,6 +367,7 @@ static int upload_records(Vp9CudaCtx *c, DevRecords &d, const Vp9CudaFrameHeader
         CK(cudaEventCreateWithFlags(&d.uploaded, cudaEventDisableTiming));
         CK(cudaEventCreateWithFlags(&d.dev_free, cudaEventDisableTiming));
         CK(cudaEventCreateWithFlags(&d.prepped, cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&d.cellmapped, cudaEventDisableTiming));
     }
     if (d.has_free) {                       /* the previous user of this landing zone must be done */
         CK(cudaStreamWaitEvent(c->s_up, d.dev_free, 0));
@@ -430,6 +433,14 @@ static int launch_frame(Vp9CudaCtx *c, FrameDesc &f, DevRecords &d)
             CK(cudaStreamWaitEvent(sp, d.dev_free, 0));
         if (d.wait_upload)
             CK(cudaStreamWaitEvent(sp, d.uploaded, 0));
+        if (f.n_itx && f.n_blk) {
+            /* the intra pre-pass asks the cell map which neighbours are intra */
+            kstat_begin(c, sp);
+            CK(cudaMemsetAsync(f.cellmap, 0xff, (size_t)f.cols * f.rows * 4, sp));
+            k_cellmap<<<(f.n_blk + 255) / 256, 256, 0, sp>>>(f.blk, f.n_blk, f.cellmap, f.cols, f.rows);
+            kstat_end(c, KS_CELLMAP, 1, (uint64_t)f.n_blk * sizeof(Vp9CudaInterBlock) + (uint64_t)f.cols * f.rows * 4, sp);
+            CK(cudaEventRecord(d.cellmapped, sp));
+        }
         if (f.n_itx) {
             if (f.sb_cols > INTRA_MAX_SB_COLS)
                 return -EINVAL;
@@ -453,10 +464,14 @@ static int launch_frame(Vp9CudaCtx *c, FrameDesc &f, DevRecords &d)
     }
     /* ---- compute stream ---- */
     if (f.n_blk) {
-        kstat_begin(c);
-        CK(cudaMemsetAsync(f.cellmap, 0xff, (size_t)f.cols * f.rows * 4, s));
-        k_cellmap<<<(f.n_blk + 255) / 256, 256, 0, s>>>(f.blk, f.n_blk, f.cellmap, f.cols, f.rows);
-        kstat_end(c, KS_CELLMAP, 1, (uint64_t)f.n_blk * sizeof(Vp9CudaInterBlock) + (uint64_t)f.cols * f.rows * 4);
+        if (f.n_itx) {
+            CK(cudaStreamWaitEvent(s, d.cellmapped, 0));
+        } else {
+            kstat_begin(c);
+            CK(cudaMemsetAsync(f.cellmap, 0xff, (size_t)f.cols * f.rows * 4, s));
+            k_cellmap<<<(f.n_blk + 255) / 256, 256, 0, s>>>(f.blk, f.n_blk, f.cellmap, f.cols, f.rows);
+            kstat_end(c, KS_CELLMAP, 1, (uint64_t)f.n_blk * sizeof(Vp9CudaInterBlock) + (uint64_t)f.cols * f.rows * 4);
+        }
         kstat_begin(c);
         dim3 grid((f.cols * 8 + 63) / 64, (f.rows * 8 + 31) / 32);
         k_inter<P><<<grid, 256, 0, s>>>(f);
