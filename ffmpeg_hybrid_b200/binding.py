@@ -22,8 +22,14 @@ API = [
     "vp9cuda_show_existing", "vp9cuda_host_alloc", "vp9cuda_host_free", "vp9cuda_decode_frame",
     "vp9cuda_stage_frame", "vp9cuda_run_staged", "vp9cuda_free_staged", "vp9cuda_frame_checksum",
     "vp9cuda_kernel_stats", "vp9cuda_set_option", "vp9cuda_elapsed_ms", "vp9cuda_phase_clocks", "vp9cuda_slot_itxfm_add",
-    "vp9cuda_slot_intra_pred", "vp9cuda_slot_mc", "vp9cuda_slot_loop_filter",
+    "vp9cuda_slot_intra_pred", "vp9cuda_slot_mc", "vp9cuda_slot_loop_filter", "vp9cuda_map_frame", "vp9cuda_unmap_frame",
 ]
+
+
+class MappedFrame(C.Structure):
+    """Vp9CudaMappedFrame: a finished picture left in HBM for a GPU consumer."""
+    _fields_ = [("planes", C.c_void_p * 3), ("strides", C.c_ssize_t * 3),
+                ("w", C.c_int), ("h", C.c_int), ("bpp", C.c_int), ("ss_h", C.c_int), ("ss_v", C.c_int)]
 
 
 class LaneRing(C.Structure):
@@ -69,6 +75,8 @@ def load() -> C.CDLL:
                                            C.POINTER(C.c_uint64)]
         lib.vp9cuda_free_staged.argtypes = [C.c_void_p, C.c_int]
         lib.vp9cuda_frame_checksum.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_uint64)]
+        lib.vp9cuda_map_frame.argtypes = [C.c_void_p, C.c_int, C.POINTER(MappedFrame)]
+        lib.vp9cuda_unmap_frame.argtypes = [C.c_void_p, C.c_void_p]
         lib.vp9cuda_set_option.argtypes = [C.c_void_p, C.c_char_p, C.c_int]
         lib.vp9cuda_elapsed_ms.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_double)]
         lib.vp9cuda_phase_clocks.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.c_int]
@@ -214,6 +222,14 @@ class Context:
         out = (C.c_uint64 * n)()
         check(self.lib.vp9cuda_phase_clocks(self.ctx, out, n), "vp9cuda_phase_clocks")
         return list(out)
+
+    def map_frame(self, slot: int = -1) -> "MappedFrame":
+        m = MappedFrame()
+        check(self.lib.vp9cuda_map_frame(self.ctx, slot, C.byref(m)), "vp9cuda_map_frame")
+        return m
+
+    def unmap_frame(self, m: "MappedFrame") -> None:
+        check(self.lib.vp9cuda_unmap_frame(self.ctx, m.planes[0]), "vp9cuda_unmap_frame")
 
     def checksum(self, slot: int = -1) -> int:
         s = C.c_uint64()

@@ -394,6 +394,9 @@ __device__ __forceinline__ void intra_row(const FrameDesc &f, const int row, uns
             const int ntab = info[c].ntab;
             for (int pos = 0; pos < ntab;) {
                 const int cnt = tab[pos] & 0x7fff;
+                const bool probe = f.phase_clk && threadIdx.x == 32;     /* warp 1 times its chunks / barrier waits */
+                long long pt0 = 0;
+                if (probe) pt0 = clock64();
                 for (int i = warp; i < cnt; i += INTRA_CW) {
                     const unsigned ent = tab[pos + 1 + i];
                     const IntraRec r = rec[ent & 511];
@@ -434,7 +437,16 @@ __device__ __forceinline__ void intra_row(const FrameDesc &f, const int row, uns
                         *((P *)(tl + (e.by + y) * rsb) + e.bx + x) = (P)v;
                     }
                 }
+                long long pt1 = 0;
+                if (probe) pt1 = clock64();
                 asm volatile("bar.sync 1, %0;\n" ::"n"(INTRA_CT) : "memory");
+                if (probe) {
+                    const int mine = warp < cnt ? (cnt - warp + INTRA_CW - 1) / INTRA_CW : 0;
+                    atomicAdd(&f.phase_clk[19], (unsigned long long)(pt1 - pt0));
+                    atomicAdd(&f.phase_clk[20], (unsigned long long)mine);
+                    atomicAdd(&f.phase_clk[21], (unsigned long long)(clock64() - pt1));
+                    atomicAdd(&f.phase_clk[22], mine ? 0ull : (unsigned long long)(pt1 - pt0));
+                }
                 pos += cnt + 1;
                 nsteps++;
                 nrounds += (cnt + INTRA_CW - 1) / INTRA_CW;

@@ -936,6 +936,43 @@ extern "C" int vp9cuda_show_existing(Vp9CudaCtx *c, int slot, uint8_t *const out
     return r < 0 ? r : make_ticket(c, ticket, c->s_down);
 }
 
+extern "C" int vp9cuda_map_frame(Vp9CudaCtx *c, int slot, Vp9CudaMappedFrame *out)
+{
+    if (!c || !out || slot > 7)
+        return -EINVAL;
+    cudaSetDevice(c->device);
+    Surface *s;
+    {
+        std::lock_guard<std::mutex> lk(c->mu);
+        s = slot < 0 ? c->last : c->ref[slot];
+        if (!s)
+            return -EINVAL;
+        s->refs++;                 /* keeps the surface out of the pool until unmap */
+    }
+    CK(cudaEventSynchronize(s->ready));
+    const int bytes = s->bpp > 8 ? 2 : 1;
+    for (int p = 0; p < 3; p++) {
+        out->planes[p] = s->pl[p];
+        out->strides[p] = (ptrdiff_t)s->stride[p] * bytes;
+    }
+    out->w = s->w; out->h = s->h; out->bpp = s->bpp;
+    out->ss_h = out->ss_v = 1;
+    return 0;
+}
+
+extern "C" int vp9cuda_unmap_frame(Vp9CudaCtx *c, const void *plane0)
+{
+    if (!c || !plane0)
+        return -EINVAL;
+    std::lock_guard<std::mutex> lk(c->mu);
+    for (Surface *s : c->pool)
+        if (s->pl[0] == plane0 && s->refs > 0) {
+            s->refs--;
+            return 0;
+        }
+    return -EINVAL;
+}
+
 extern "C" int vp9cuda_decode_frame(Vp9CudaCtx *c, const Vp9CudaFrameHeader *hdr, const Vp9CudaFrameRecords *recs,
                                     uint8_t *const out_planes[3], const ptrdiff_t out_strides[3], uint64_t *ticket)
 {

@@ -173,6 +173,20 @@ int  vp9cuda_finish_frame(Vp9CudaCtx *ctx, uint32_t frame_id, uint8_t *const out
                           const ptrdiff_t out_strides[3], uint64_t *ticket);
 /* Block until the frame behind `ticket` is complete (pixels in out_planes valid). */
 int  vp9cuda_wait(Vp9CudaCtx *ctx, uint64_t ticket);
+/* Device-resident output (the output site is vp9.c:1853-1857): hand the finished
+ * picture to a GPU consumer without the device->host copy.  slot 0..7 = reference slot, slot < 0
+ * = the most recently reconstructed frame.  Blocks until that picture is final, then returns
+ * device pointers to the three planes (visible w x h at the top left of a 64-aligned surface),
+ * their strides in bytes, and the format.  The surface stays untouched until
+ * vp9cuda_unmap_frame(planes[0]); every map needs one unmap.  0 or negative errno. */
+typedef struct Vp9CudaMappedFrame {
+    void     *planes[3];
+    ptrdiff_t strides[3];    /* bytes */
+    int       w, h, bpp;     /* luma size; 8 -> uint8_t samples, 10/12 -> uint16_t */
+    int       ss_h, ss_v;    /* chroma subsampling (1, 1 = 4:2:0) */
+} Vp9CudaMappedFrame;
+int  vp9cuda_map_frame(Vp9CudaCtx *ctx, int slot, Vp9CudaMappedFrame *out);
+int  vp9cuda_unmap_frame(Vp9CudaCtx *ctx, const void *plane0);
 /* show_existing_frame (vp9.c:1636-1653): copy reference slot `slot` to host. */
 int  vp9cuda_show_existing(Vp9CudaCtx *ctx, int slot, uint8_t *const out_planes[3],
                            const ptrdiff_t out_strides[3], uint64_t *ticket);

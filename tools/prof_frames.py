@@ -38,7 +38,7 @@ def main():
             names = [k for k in st]
             print("frame  w    h  n_itx  levels " + " ".join(f"{k[:10]:>10s}" for k in names))
         print(f"{i:4d} {frames[i].w:5d} {frames[i].h:4d} {len(itx):6d} {nlv:6d} " + " ".join(f"{st[k]['ms']:10.3f}" for k in names))
-    pc = ctx.phase_clocks(20)
+    pc = ctx.phase_clocks(24)
     units = sum(((f.w + 63) // 64) * ((f.h + 63) // 64) for f in frames)
     for name, v, n in (("luma", pc[:5], units), ("chroma", pc[5:10], 2 * units)):
         print(f"loop filter {name}: cycles per superblock turn (wait body, Cr, wait top, R, Ce+signal):",
@@ -48,6 +48,8 @@ def main():
           f"cycles/turn wait body {pc[10] / turns:.0f}, wait top {pc[11] / turns:.0f}, compute {pc[12] / turns:.0f} "
           f"(= {pc[12] / max(pc[13], 1):.0f} per step); chunks/step {pc[17] / max(pc[13], 1):.1f}, "
           f"rounds/step {pc[16] / max(pc[13], 1):.2f}, turns that wait for the row above {pc[18] / turns:.2f}")
+    print(f"intra warp 1: {pc[20]} chunks, {(pc[19] - pc[22]) / max(pc[20], 1):.0f} cycles per chunk, idle pass {pc[22] / max(pc[13] - 0, 1):.0f} "
+          f"cycles/step, barrier wait {pc[21] / max(pc[13], 1):.0f} cycles per step")
     ctx.close()
 
 
