@@ -100,6 +100,21 @@ def small_variants() -> Dict[str, StreamSpec]:
     st.frames = _ippp(5)
     st.frames[2] = FrameSpec(intraonly=True, show=False, refreshrefmask=0x06, resetctx=0)
     out["intraonly"] = st
+    st = StreamSpec(328, 392, seed=13)                       # 2 tile rows x 2 tile columns
+    st.frames = _ippp(4, tile_cols=1, compound=True, log2_tile_rows=1)
+    out["tilerows"] = st
+    st = StreamSpec(264, 200, seed=14)                       # error-resilient / frame-parallel headers
+    st.frames = _ippp(4, errorres=True)
+    for f in st.frames:
+        f.refreshctx = False
+        f.parallelmode = True
+    out["parallel"] = st
+    st = StreamSpec(296, 232, seed=15)                       # strongest loop filter
+    st.frames = _ippp(3, lf_level=63, lf_sharpness=7)
+    out["lf63"] = st
+    st = StreamSpec(453, 267, seed=16)                       # size not a multiple of 8
+    st.frames = _ippp(4, tile_cols=1, compound=True)
+    out["odd"] = st
     st = StreamSpec(72, 40, seed=11)                         # tiny, single superblock column
     st.frames = _ippp(4, compound=True)
     out["tiny"] = st
