@@ -67,7 +67,9 @@ struct FrameDesc {
     uint16_t *itab;                /* [sb][768] per-step chunk tables (k_intra_prep) */
     int16_t *ires;                 /* [sb][6144] intra residual tiles (k_intra_res -> k_intra) */
     LfSched *lfsched;              /* [sb][plane] loop-filter edge ops sorted by dependency step */
-    int *progress;                 /* [3 planes][sb_rows] loop-filter wavefront counters */
+    int *progress;                 /* [3 planes][sb_rows] loop-filter wavefront counters, then [3][sb_rows] "row done" */
+    int *mv_reach;                 /* max vertical motion vector component of this frame, 1/8 pel (k_cellmap) */
+    int tile_y0;                   /* k_inter: first 32-row tile row of this launch (the frame may be launched in bands) */
     unsigned long long *phase_clk; /* optional: per-phase clock accumulation (profiling), or NULL */
     uint8_t lim_lut[64], mblim_lut[64];
 };

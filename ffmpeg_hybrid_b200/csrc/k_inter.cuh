@@ -24,9 +24,20 @@
 namespace vp9 {
 
 __global__ void k_cellmap(const Vp9CudaInterBlock *__restrict__ blk, uint32_t n, int32_t *cellmap,
-                          int cols, int rows)
+                          int cols, int rows, int *mv_reach)
 {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    int reach = 0;
+    if (i < n) {
+        /* how far below its own position any prediction of this frame may read (vertical MV, 1/8 pel) */
+        const int nref = blk[i].comp ? 2 : 1, nsub = blk[i].bs > 9 ? 4 : 1;
+        for (int k = 0; k < nsub; k++)
+            for (int r = 0; r < nref; r++)
+                reach = max(reach, (int)blk[i].mv[k][r][1]);
+    }
+    reach = __reduce_max_sync(0xffffffffu, reach);
+    if ((threadIdx.x & 31) == 0 && reach > 0)
+        atomicMax(mv_reach, reach);
     if (i >= n)
         return;
     int col = blk[i].col, row = blk[i].row, bs = blk[i].bs;
@@ -199,11 +210,32 @@ __device__ __forceinline__ void inter_strip(const FrameDesc &f, const Vp9CudaInt
     for (int j = 0; j < NR; j++) out[j] = acc[j];
 }
 
+/* Gate in front of a band of k_inter tile rows that is launched while the PREVIOUS frame's loop
+ * filter may still be running (inter stream): one warp waits until the superblock rows the band
+ * can reach are final, then the band's k_inter launch follows in stream order.  A single warp
+ * cannot keep the wavefront's CTAs off the machine, so nothing can deadlock.
+ * Loop-filter row r finishes pixel rows [64r - 8, 64r + 56) (chroma: [32r - 8, 32r + 24)), so
+ * luma-scale row Y is final with loop-filter row (Y + 16) >> 6 at the latest; rows finish top
+ * down.  Reach below the band's last row: integer motion (k_cellmap's maximum) + 4 taps, with
+ * slack for the rounding of the chroma / sub-8x8 average vectors. */
+__global__ void k_inter_gate(const int *dep_done, int dep_rows, int dep_whole, const int *mv_reach, int y_last)
+{
+    if (threadIdx.x == 0) {
+        int need = dep_rows - 1;
+        if (!dep_whole)
+            need = min(need, (y_last + (*(volatile const int *)mv_reach >> 3) + 12 + 16) >> 6);
+        const volatile int *done = dep_done;
+        for (int pl = 0; pl < 3; pl++)
+            VP9_SPIN(done[pl * dep_rows + need] == 0, 500, "inter gate: previous frame's loop filter", need, pl);
+        __threadfence();
+    }
+}
+
 template <class P>
 __global__ void __launch_bounds__(256, sizeof(P) == 2 ? 3 : 2) k_inter(const __grid_constant__ FrameDesc f)
 {
     const int tid = threadIdx.x;
-    const int X0 = blockIdx.x * 64, Y0 = blockIdx.y * 32;
+    const int X0 = blockIdx.x * 64, Y0 = (blockIdx.y + f.tile_y0) * 32;
     /* ---- luma: strip = column tid&63, rows (tid>>6)*8 .. +7 ---- */
     {
         const int X = X0 + (tid & 63), Y = Y0 + (tid >> 6) * 8;

@@ -387,16 +387,15 @@ __device__ __forceinline__ void intra_row(const FrameDesc &f, const int row, uns
                 __threadfence_block();
             }
             asm volatile("bar.sync 1, %0;\n" ::"n"(INTRA_CT) : "memory");
+#ifdef VP9CUDA_STEPSTATS   /* counters for tools/prof_frames.py; the chain is so tight that they cost ~4 % of the wavefront */
             int nsteps = 0, nrounds = 0, nchunks = 0, ntop = info[c].needs_top;
+#endif
             const IntraRec *rec = recbuf + (c & 3) * INTRA_SB_RECS;
             const int16_t *res = resbuf + (c & 3) * INTRA_SB_RES;
             const uint16_t *tab = tabbuf + (c & 3) * INTRA_SB_TAB;
             const int ntab = info[c].ntab;
             for (int pos = 0; pos < ntab;) {
                 const int cnt = tab[pos] & 0x7fff;
-                const bool probe = f.phase_clk && threadIdx.x == 32;     /* warp 1 times its chunks / barrier waits */
-                long long pt0 = 0;
-                if (probe) pt0 = clock64();
                 for (int i = warp; i < cnt; i += INTRA_CW) {
                     const unsigned ent = tab[pos + 1 + i];
                     const IntraRec r = rec[ent & 511];
@@ -437,32 +436,27 @@ __device__ __forceinline__ void intra_row(const FrameDesc &f, const int row, uns
                         *((P *)(tl + (e.by + y) * rsb) + e.bx + x) = (P)v;
                     }
                 }
-                long long pt1 = 0;
-                if (probe) pt1 = clock64();
                 asm volatile("bar.sync 1, %0;\n" ::"n"(INTRA_CT) : "memory");
-                if (probe) {
-                    const int mine = warp < cnt ? (cnt - warp + INTRA_CW - 1) / INTRA_CW : 0;
-                    atomicAdd(&f.phase_clk[19], (unsigned long long)(pt1 - pt0));
-                    atomicAdd(&f.phase_clk[20], (unsigned long long)mine);
-                    atomicAdd(&f.phase_clk[21], (unsigned long long)(clock64() - pt1));
-                    atomicAdd(&f.phase_clk[22], mine ? 0ull : (unsigned long long)(pt1 - pt0));
-                }
                 pos += cnt + 1;
+#ifdef VP9CUDA_STEPSTATS
                 nsteps++;
                 nrounds += (cnt + INTRA_CW - 1) / INTRA_CW;
                 nchunks += cnt;
+#endif
             }
             if (threadIdx.x == 0) {
                 __threadfence_block();
                 sig.done = c + 1;
                 ICLK(12);
                 if (f.phase_clk) {
-                    atomicAdd(&f.phase_clk[13], (unsigned long long)nsteps);
                     atomicAdd(&f.phase_clk[14], 1ull);
                     atomicAdd(&f.phase_clk[15], (unsigned long long)n);
+#ifdef VP9CUDA_STEPSTATS
+                    atomicAdd(&f.phase_clk[13], (unsigned long long)nsteps);
                     atomicAdd(&f.phase_clk[16], (unsigned long long)nrounds);
                     atomicAdd(&f.phase_clk[17], (unsigned long long)nchunks);
                     atomicAdd(&f.phase_clk[18], (unsigned long long)ntop);
+#endif
                 }
             }
         }

@@ -387,6 +387,13 @@ __device__ void lf_row(const FrameDesc &f, int pl, int row, unsigned char *ring,
             if (lane == 0)
                 sig->stored = c + 1;
         }
+        /* every pixel of this (row, plane) is written: the next frame's inter prediction may read
+         * rows [y0 - 8, y0 + S - 8) of the plane, and the rest once the row below says the same */
+        __syncwarp();
+        if (lane == 0) {
+            __threadfence();
+            *(volatile int *)(f.progress + (3 + pl) * f.sb_rows + row) = 1;
+        }
     }
 }
 

@@ -126,7 +126,7 @@ struct HBuf {
 /* device-resident records + scratch of one frame */
 struct DevRecords {
     DBuf blk, tx[4], itx, coef, sb_index, lf;
-    DBuf cellmap, isb, irec, ires, itab, iprogress, lfops, progress;
+    DBuf cellmap, isb, irec, ires, itab, iprogress, lfops, progress, misc;
     uint32_t lane_itx_base[VP9CUDA_MAX_LANES] = { 0 };
     Vp9CudaFrameHeader hdr;
     uint32_t n_blk = 0, n_tx[4] = { 0, 0, 0, 0 }, n_itx = 0;
@@ -135,6 +135,7 @@ struct DevRecords {
     cudaEvent_t dev_free = nullptr;    /* the kernels reading these records finished (compute stream) */
     cudaEvent_t prepped = nullptr;     /* the pixel-independent pre-passes finished (prep stream) */
     cudaEvent_t cellmapped = nullptr;  /* the cell map is built (prep stream) */
+    cudaEvent_t inter_done = nullptr;  /* inter prediction finished (inter stream) */
     bool wait_upload = false, has_free = false;
     void release()
     {
@@ -142,10 +143,11 @@ struct DevRecords {
         if (dev_free) cudaEventDestroy(dev_free);
         if (prepped) cudaEventDestroy(prepped);
         if (cellmapped) cudaEventDestroy(cellmapped);
-        uploaded = dev_free = prepped = cellmapped = nullptr;
+        if (inter_done) cudaEventDestroy(inter_done);
+        uploaded = dev_free = prepped = cellmapped = inter_done = nullptr;
         blk.release(); itx.release(); coef.release(); sb_index.release(); lf.release();
         for (auto &t : tx) t.release();
-        cellmap.release(); isb.release(); irec.release(); ires.release(); itab.release(); iprogress.release(); lfops.release();
+        misc.release(); cellmap.release(); isb.release(); irec.release(); ires.release(); itab.release(); iprogress.release(); lfops.release();
         progress.release();
     }
 };
@@ -179,6 +181,18 @@ struct Vp9CudaCtx {
     cudaStream_t s_up = nullptr;           /* record upload (H2D), overlaps the previous frame's kernels */
     cudaStream_t s_down = nullptr;         /* picture download (D2H), overlaps the next frame's kernels */
     cudaStream_t s_prep = nullptr;         /* pixel-independent pre-passes, overlap the previous frame / inter stage */
+    cudaStream_t s_inter = nullptr;        /* inter prediction started behind the previous frame's loop filter */
+    cudaEvent_t pre_wave = nullptr;        /* recorded on the compute stream right before a frame's wavefront launch */
+    /* the frame whose loop filter may still be running when the next frame is submitted */
+    DevRecords *prev_dev = nullptr;
+    Surface *prev_surf = nullptr;
+    bool prev_lf = false;
+    int prev_sb_rows = 0, prev_w = 0, prev_h = 0;
+    int inter_bands = 6;                   /* set_option "inter_bands" */
+    int n_sm = 0;
+    size_t ring_rr = 0;
+    bool overlap_inter = false;            /* set_option "overlap_inter": measured +3 % (C3) .. -6 % (C2), off by default */
+    bool fresh_surface = false;            /* surface_get just allocated (its clearing memset is on the compute stream) */
     int follow_mask = 3;                   /* debugging: 1 = wait for intra write-back, 2 = wait for the intra row below */
     bool trace = false;                    /* VP9CUDA_TRACE: one stderr line per submitted / finished frame */
     bool fuse_wave = true;                 /* set_option "fuse_wave": loop filter beside the intra wavefront */
@@ -198,7 +212,7 @@ struct Vp9CudaCtx {
     std::vector<int> tstage;               /* stage id of pair i */
     size_t tused = 0;
     cudaEvent_t marks[16] = { nullptr };
-    cudaEvent_t join_ev[3] = { nullptr, nullptr, nullptr };
+    cudaEvent_t join_ev[4] = { nullptr, nullptr, nullptr, nullptr };
     DBuf sum_buf;
     DBuf phase_clk;                        /* optional profiling counters (set_option "phase_clk") */
     bool phase_on = false;
@@ -211,8 +225,10 @@ static Surface *surface_get(Vp9CudaCtx *c, int w, int h, int bpp)
             s->refs = 1;
             if (s->has_d2h) {               /* a copy-out of its previous picture may still be in flight */
                 cudaStreamWaitEvent(c->stream, s->d2h_done, 0);
+                cudaStreamWaitEvent(c->s_inter, s->d2h_done, 0);
                 s->has_d2h = false;
             }
+            c->fresh_surface = false;
             return s;
         }
     /* Unused surfaces of other sizes stay cached (streams with resize frames alternate between a
@@ -252,6 +268,7 @@ static Surface *surface_get(Vp9CudaCtx *c, int w, int h, int bpp)
     cudaEventCreateWithFlags(&s->ready, cudaEventDisableTiming);
     cudaEventCreateWithFlags(&s->d2h_done, cudaEventDisableTiming);
     s->refs = 1;
+    c->fresh_surface = true;
     c->pool.push_back(s);
     return s;
 }
@@ -260,6 +277,7 @@ static void sync_all(Vp9CudaCtx *c)
 {
     cudaStreamSynchronize(c->s_up);
     cudaStreamSynchronize(c->s_prep);
+    cudaStreamSynchronize(c->s_inter);
     cudaStreamSynchronize(c->stream);
     cudaStreamSynchronize(c->s_down);
 }
@@ -314,6 +332,7 @@ static void kstat_resolve(Vp9CudaCtx *c)
     cudaStreamSynchronize(c->stream);
     cudaStreamSynchronize(c->s_up);
     cudaStreamSynchronize(c->s_prep);
+    cudaStreamSynchronize(c->s_inter);
     cudaStreamSynchronize(c->s_down);
     for (size_t i = 0; i < c->tused; i++) {
         float ms = 0;
@@ -360,7 +379,8 @@ static int upload_records(Vp9CudaCtx *c, DevRecords &d, const Vp9CudaFrameHeader
     if (n_itx) r |= d.itab.reserve((size_t)n_sb * INTRA_SB_TAB * 2);
     r |= d.iprogress.reserve((size_t)2 * sb_rows * 4);
     r |= d.lfops.reserve((size_t)n_sb * 3 * sizeof(LfSched));
-    r |= d.progress.reserve((size_t)3 * sb_rows * 4);
+    r |= d.progress.reserve((size_t)6 * sb_rows * 4);
+    r |= d.misc.reserve(64);
     if (r)
         return -ENOMEM;
     if (!d.uploaded) {
@@ -368,6 +388,7 @@ static int upload_records(Vp9CudaCtx *c, DevRecords &d, const Vp9CudaFrameHeader
         CK(cudaEventCreateWithFlags(&d.dev_free, cudaEventDisableTiming));
         CK(cudaEventCreateWithFlags(&d.prepped, cudaEventDisableTiming));
         CK(cudaEventCreateWithFlags(&d.cellmapped, cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&d.inter_done, cudaEventDisableTiming));
     }
     if (d.has_free) {                       /* the previous user of this landing zone must be done */
         CK(cudaStreamWaitEvent(c->s_up, d.dev_free, 0));
@@ -437,7 +458,8 @@ static int launch_frame(Vp9CudaCtx *c, FrameDesc &f, DevRecords &d)
             /* the intra pre-pass asks the cell map which neighbours are intra */
             kstat_begin(c, sp);
             CK(cudaMemsetAsync(f.cellmap, 0xff, (size_t)f.cols * f.rows * 4, sp));
-            k_cellmap<<<(f.n_blk + 255) / 256, 256, 0, sp>>>(f.blk, f.n_blk, f.cellmap, f.cols, f.rows);
+            CK(cudaMemsetAsync(f.mv_reach, 0, 4, sp));
+            k_cellmap<<<(f.n_blk + 255) / 256, 256, 0, sp>>>(f.blk, f.n_blk, f.cellmap, f.cols, f.rows, f.mv_reach);
             kstat_end(c, KS_CELLMAP, 1, (uint64_t)f.n_blk * sizeof(Vp9CudaInterBlock) + (uint64_t)f.cols * f.rows * 4, sp);
             CK(cudaEventRecord(d.cellmapped, sp));
         }
@@ -453,29 +475,64 @@ static int launch_frame(Vp9CudaCtx *c, FrameDesc &f, DevRecords &d)
         if (f.lf_level) {
             kstat_begin(c, sp);
             k_lf_sched<<<f.sb_cols * f.sb_rows, LF_SCHED_THREADS, 0, sp>>>(f);
-            CK(cudaMemsetAsync(f.progress, 0, (size_t)3 * f.sb_rows * 4, sp));
+            CK(cudaMemsetAsync(f.progress, 0, (size_t)6 * f.sb_rows * 4, sp));
             kstat_end(c, KS_LFOPS, 1, (uint64_t)f.sb_cols * f.sb_rows * (sizeof(Vp9CudaLoopFilterSb) + 3 * sizeof(LfSched)), sp);
         }
         CK(cudaEventRecord(d.prepped, sp));
     }
+    const bool had_upload = d.wait_upload;
     if (d.wait_upload) {
         CK(cudaStreamWaitEvent(s, d.uploaded, 0));
         d.wait_upload = false;
     }
-    /* ---- compute stream ---- */
+    /* ---- inter prediction: on the compute stream, or -- when the previous frame's loop filter is
+     * still in flight and all of its CTAs are resident -- on the inter stream right behind that
+     * wavefront, each tile waiting for the superblock rows it can reach (k_inter, dep_done) ---- */
     if (f.n_blk) {
-        if (f.n_itx) {
-            CK(cudaStreamWaitEvent(s, d.cellmapped, 0));
-        } else {
-            kstat_begin(c);
-            CK(cudaMemsetAsync(f.cellmap, 0xff, (size_t)f.cols * f.rows * 4, s));
-            k_cellmap<<<(f.n_blk + 255) / 256, 256, 0, s>>>(f.blk, f.n_blk, f.cellmap, f.cols, f.rows);
-            kstat_end(c, KS_CELLMAP, 1, (uint64_t)f.n_blk * sizeof(Vp9CudaInterBlock) + (uint64_t)f.cols * f.rows * 4);
+        const bool overlap = c->overlap_inter && c->prev_dev && c->prev_dev != &d && c->prev_lf && !c->fresh_surface;
+        bool depends = false;
+        for (int i = 0; i < 3; i++)
+            depends |= c->prev_surf && f.ref[i].pl[0] == c->prev_surf->pl[0];
+        cudaStream_t si = overlap ? c->s_inter : s;
+        if (overlap) {
+            CK(cudaStreamWaitEvent(si, c->pre_wave, 0));     /* everything older than that wavefront is final */
+            if (had_upload)
+                CK(cudaStreamWaitEvent(si, d.uploaded, 0));
         }
-        kstat_begin(c);
-        dim3 grid((f.cols * 8 + 63) / 64, (f.rows * 8 + 31) / 32);
-        k_inter<P><<<grid, 256, 0, s>>>(f);
-        kstat_end(c, KS_INTER, 1, 2 * P_bytes);
+        if (f.n_itx) {
+            CK(cudaStreamWaitEvent(si, d.cellmapped, 0));
+        } else {
+            kstat_begin(c, si);
+            CK(cudaMemsetAsync(f.cellmap, 0xff, (size_t)f.cols * f.rows * 4, si));
+            CK(cudaMemsetAsync(f.mv_reach, 0, 4, si));
+            k_cellmap<<<(f.n_blk + 255) / 256, 256, 0, si>>>(f.blk, f.n_blk, f.cellmap, f.cols, f.rows, f.mv_reach);
+            kstat_end(c, KS_CELLMAP, 1, (uint64_t)f.n_blk * sizeof(Vp9CudaInterBlock) + (uint64_t)f.cols * f.rows * 4, si);
+        }
+        kstat_begin(c, si);
+        const int gx = (f.cols * 8 + 63) / 64, gy = (f.rows * 8 + 31) / 32;
+        if (overlap && depends) {
+            /* in bands of tile rows, each behind a one-warp gate on the previous frame's loop-filter rows */
+            const int dep_rows = c->prev_sb_rows, dep_whole = c->prev_w != f.w || c->prev_h != f.h;
+            const int *dep_done = (const int *)c->prev_dev->progress.p + 3 * dep_rows;
+            const int band = dep_whole ? gy : std::max(4, (gy + c->inter_bands - 1) / c->inter_bands);
+            for (int y0 = 0; y0 < gy; y0 += band) {
+                const int n = std::min(band, gy - y0);
+                k_inter_gate<<<1, 32, 0, si>>>(dep_done, dep_rows, dep_whole, f.mv_reach, (y0 + n) * 32 - 1);
+                f.tile_y0 = y0;
+                k_inter<P><<<dim3(gx, n), 256, 0, si>>>(f);
+            }
+            f.tile_y0 = 0;
+            kstat_end(c, KS_INTER, 2 * ((gy + band - 1) / band), 2 * P_bytes, si);
+        } else {
+            k_inter<P><<<dim3(gx, gy), 256, 0, si>>>(f);
+            kstat_end(c, KS_INTER, 1, 2 * P_bytes, si);
+        }
+        if (overlap) {
+            CK(cudaEventRecord(d.inter_done, si));
+            CK(cudaStreamWaitEvent(s, d.inter_done, 0));
+            /* the previous frame's flags were read until here: its records stay untouched that long */
+            CK(cudaEventRecord(c->prev_dev->dev_free, s));
+        }
     }
     kstat_begin(c);
     uint64_t itx_launches = 0, itx_bytes = 0;
@@ -489,6 +546,10 @@ static int launch_frame(Vp9CudaCtx *c, FrameDesc &f, DevRecords &d)
         kstat_end(c, KS_ITX, itx_launches, itx_bytes);
     if (f.n_itx || f.lf_level)
         CK(cudaStreamWaitEvent(s, d.prepped, 0));
+    CK(cudaEventRecord(c->pre_wave, s));
+    c->prev_dev = &d;
+    c->prev_lf = f.lf_level != 0;
+    c->prev_sb_rows = f.sb_rows; c->prev_w = f.w; c->prev_h = f.h;
     if (fused) {
         kstat_begin(c);
         k_wave<P><<<4 * f.sb_rows, INTRA_THREADS, WaveSmem<P>::BYTES, s>>>(f);
@@ -601,6 +662,7 @@ static int reconstruct(Vp9CudaCtx *c, DevRecords &d, uint8_t *const out_planes[3
     memcpy(f.lane_itx_base, d.lane_itx_base, sizeof(f.lane_itx_base));
     f.lfsched = (LfSched *)d.lfops.p;
     f.progress = (int *)d.progress.p;
+    f.mv_reach = (int *)d.misc.p;
     f.phase_clk = c->phase_on ? (unsigned long long *)c->phase_clk.p : nullptr;
     memcpy(f.lim_lut, h.lim_lut, 64);
     memcpy(f.mblim_lut, h.mblim_lut, 64);
@@ -613,6 +675,9 @@ static int reconstruct(Vp9CudaCtx *c, DevRecords &d, uint8_t *const out_planes[3
         CK(cudaEventRecord(d.dev_free, c->stream));
         d.has_free = true;
     }
+    c->prev_surf = r == 0 ? cur : nullptr;
+    if (r < 0)
+        c->prev_dev = nullptr;
     if (r == 0)
         CK(cudaEventRecord(cur->ready, c->stream));
     if (r == 0 && c->trace)
@@ -672,6 +737,13 @@ extern "C" int vp9cuda_create(Vp9CudaCtx **out, int device, int max_w, int max_h
     CK(cudaStreamCreateWithFlags(&c->s_up, cudaStreamNonBlocking));
     CK(cudaStreamCreateWithFlags(&c->s_down, cudaStreamNonBlocking));
     CK(cudaStreamCreateWithFlags(&c->s_prep, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&c->s_inter, cudaStreamNonBlocking));
+    CK(cudaEventCreateWithFlags(&c->pre_wave, cudaEventDisableTiming));
+    CK(cudaDeviceGetAttribute(&c->n_sm, cudaDevAttrMultiProcessorCount, device));
+    if (const char *e = getenv("VP9CUDA_OVERLAP_INTER"))
+        c->overlap_inter = atoi(e) != 0;
+    if (const char *e = getenv("VP9CUDA_INTER_BANDS"))
+        c->inter_bands = std::max(1, std::min(64, atoi(e)));
     CK(cudaFuncSetAttribute(k_wave<uint8_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, WaveSmem<uint8_t>::BYTES));
     CK(cudaFuncSetAttribute(k_wave<uint16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, WaveSmem<uint16_t>::BYTES));
     CK(cudaFuncSetAttribute(k_intra<uint8_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, IntraSmem<uint8_t>::BYTES));
@@ -725,6 +797,8 @@ extern "C" int vp9cuda_flush(Vp9CudaCtx *c)
     }
     surface_unref(c->last);
     c->last = nullptr;
+    c->prev_dev = nullptr;
+    c->prev_surf = nullptr;
     for (RingSet *r : c->rings)
         r->busy = false;
     return 0;
@@ -760,6 +834,8 @@ extern "C" void vp9cuda_destroy(Vp9CudaCtx *c)
     cudaStreamDestroy(c->s_up);
     cudaStreamDestroy(c->s_down);
     cudaStreamDestroy(c->s_prep);
+    cudaStreamDestroy(c->s_inter);
+    cudaEventDestroy(c->pre_wave);
     delete c;
 }
 
@@ -791,9 +867,13 @@ extern "C" int vp9cuda_begin_frame(Vp9CudaCtx *c, const Vp9CudaFrameHeader *hdr,
         return -EINVAL;
     cudaSetDevice(c->device);
     std::lock_guard<std::mutex> lk(c->mu);
+    /* round robin, so that consecutive frames land in different device scratch and the next
+     * frame's upload / pre-passes / inter prediction can run beside this frame's wavefronts */
     RingSet *r = nullptr;
-    for (RingSet *q : c->rings)
-        if (!q->busy) { r = q; break; }
+    for (size_t i = 0; i < c->rings.size(); i++) {
+        RingSet *q = c->rings[(c->ring_rr + i) % c->rings.size()];
+        if (!q->busy) { r = q; c->ring_rr = (c->ring_rr + i + 1) % c->rings.size(); break; }
+    }
     if (!r)
         return -EBUSY;      /* caller must finish/wait a frame first */
     /* the previous user's H2D must be over before the producer scribbles on the pinned slab */
@@ -1025,6 +1105,8 @@ extern "C" int vp9cuda_free_staged(Vp9CudaCtx *c, int handle)
         return -EINVAL;
     cudaSetDevice(c->device);
     sync_all(c);
+    if (c->prev_dev == c->staged[handle])
+        c->prev_dev = nullptr;
     c->staged[handle]->release();
     delete c->staged[handle];
     c->staged[handle] = nullptr;
@@ -1056,6 +1138,16 @@ extern "C" int vp9cuda_set_option(Vp9CudaCtx *c, const char *key, int value)
         c->timing = value != 0;
         return 0;
     }
+    if (!strcmp(key, "inter_bands")) {
+        if (value < 1 || value > 64)
+            return -EINVAL;
+        c->inter_bands = value;
+        return 0;
+    }
+    if (!strcmp(key, "overlap_inter")) {   /* 1: inter prediction starts behind the previous frame's loop filter (default 0) */
+        c->overlap_inter = value != 0;
+        return 0;
+    }
     if (!strcmp(key, "fuse_wave")) {       /* 1 (default): k_wave; 0: separate k_intra / k_lf launches */
         c->fuse_wave = value != 0;
         return 0;
@@ -1069,6 +1161,8 @@ extern "C" int vp9cuda_set_option(Vp9CudaCtx *c, const char *key, int value)
         CK(cudaEventRecord(c->join_ev[1], c->s_down));
         CK(cudaEventRecord(c->join_ev[2], c->s_prep));
         CK(cudaStreamWaitEvent(c->stream, c->join_ev[2], 0));
+        CK(cudaEventRecord(c->join_ev[3], c->s_inter));
+        CK(cudaStreamWaitEvent(c->stream, c->join_ev[3], 0));
         CK(cudaStreamWaitEvent(c->stream, c->join_ev[0], 0));
         CK(cudaStreamWaitEvent(c->stream, c->join_ev[1], 0));
         CK(cudaEventRecord(c->marks[value], c->stream));

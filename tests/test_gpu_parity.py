@@ -133,6 +133,36 @@ def test_device_resident_output_matches_host_copy(workdir):
         f.free()
 
 
+def test_inter_prediction_behind_previous_loop_filter_agrees(workdir):
+    """set_option("overlap_inter", 1): frame N+1's inter prediction is launched in bands behind one-warp
+    gates on frame N's loop-filter rows (k_inter_gate); same pictures as the serial order."""
+    from ffmpeg_hybrid_b200 import binding
+    lib = binding.load()
+    for name in ("c3_small", "c2_small", "tilerows"):
+        ivf = parity.write_stream(configs.small_variants()[name], workdir / f"ov_{name}.ivf")
+        parity.dump_records(ivf, workdir / f"ov_{name}.v9r")
+        frames = binding.load_stream(lib, workdir / f"ov_{name}.v9r", pinned=True)
+        sums = {}
+        for ov, bands in ((0, 6), (1, 6), (1, 1), (1, 64)):
+            ctx = binding.Context(0)
+            ctx.option("overlap_inter", ov)
+            ctx.option("inter_bands", bands)
+            handles = [ctx.stage(f) for f in frames]
+            got = []
+            for _ in range(3):
+                tickets = [ctx.run_staged(h) for h in handles]     # back to back: frames really overlap
+                ctx.wait(tickets[-1])
+                got.append(ctx.checksum(-1))
+                for i, h in enumerate(handles):                     # and one by one for every frame's picture
+                    ctx.wait(ctx.run_staged(h))
+                    got.append(ctx.checksum(-1))
+            sums[(ov, bands)] = got
+            ctx.close()
+        assert len(set(map(tuple, sums.values()))) == 1, name
+        for f in frames:
+            f.free()
+
+
 def test_fused_and_separate_wavefront_launches_agree(workdir):
     """k_wave (intra + loop-filter wavefronts in one launch) against separate k_intra / k_lf launches."""
     from ffmpeg_hybrid_b200 import binding

@@ -46,10 +46,8 @@ def main():
     turns = max(pc[14], 1)
     print(f"intra: non-empty turns {pc[14]}, steps/turn {pc[13] / turns:.1f}, blocks/turn {pc[15] / turns:.1f}, "
           f"cycles/turn wait body {pc[10] / turns:.0f}, wait top {pc[11] / turns:.0f}, compute {pc[12] / turns:.0f} "
-          f"(= {pc[12] / max(pc[13], 1):.0f} per step); chunks/step {pc[17] / max(pc[13], 1):.1f}, "
+          f"(= {pc[12] / max(pc[13], 1):.0f} per step); [-DVP9CUDA_STEPSTATS builds only] chunks/step {pc[17] / max(pc[13], 1):.1f}, "
           f"rounds/step {pc[16] / max(pc[13], 1):.2f}, turns that wait for the row above {pc[18] / turns:.2f}")
-    print(f"intra warp 1: {pc[20]} chunks, {(pc[19] - pc[22]) / max(pc[20], 1):.0f} cycles per chunk, idle pass {pc[22] / max(pc[13] - 0, 1):.0f} "
-          f"cycles/step, barrier wait {pc[21] / max(pc[13], 1):.0f} cycles per step")
     ctx.close()
 
 
