@@ -38,7 +38,9 @@
 
 namespace vp9 {
 
+#ifndef INTRA_CW
 #define INTRA_CW 16                         /* compute warps */
+#endif
 #define INTRA_CT (INTRA_CW * 32)
 #define INTRA_THREADS (INTRA_CT + 3 * 32)   /* + body loader, top loader, storer */
 #define INTRA_MAX_SB_COLS 256
