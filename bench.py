@@ -173,6 +173,22 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
+    # keep this rank's host threads and its pinned buffers on the CPU cores next to its GPU
+    affinity = None
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(torch.cuda.current_device() if "CUDA_VISIBLE_DEVICES" not in os.environ
+                                              else int(os.environ["CUDA_VISIBLE_DEVICES"].split(",")[local]))
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+        ideal = {64 * i + b for i, w in enumerate(words) for b in range(64) if w >> b & 1}
+        mine = sorted(ideal & os.sched_getaffinity(0))
+        if world > 1 and mine:
+            os.sched_setaffinity(0, mine)
+            affinity = f"{len(mine)} cores near the GPU (nvmlDeviceGetCpuAffinity)"
+    except Exception:  # noqa: BLE001
+        pass
+
     from ffmpeg_hybrid_b200 import binding, parity
     lib = binding.load()
 
@@ -315,7 +331,8 @@ def main():
                    "parallelism": f"{world} independent stream(s), one per GPU, no collective",
                    "l2": "inputs larger than L2: %.0f MB of records + a %d-surface reference pool per step"
                          % (h2d_per_step / 1e6, 4),
-                   "timing": "CUDA events on the library stream, max over ranks"},
+                   "timing": "CUDA events on the library stream, max over ranks",
+                   "host_affinity": affinity},
         "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": h2d_per_step,
                 "d2h_bytes_per_step": d2h_per_step, "ms_per_step": ms_e2e / args.steps},
         "gpu_launches": gpu_launches, "clocks": clocks, "roofline": roofline,
