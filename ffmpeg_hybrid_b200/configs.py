@@ -115,6 +115,13 @@ def small_variants() -> Dict[str, StreamSpec]:
     st = StreamSpec(453, 267, seed=16)                       # size not a multiple of 8
     st.frames = _ippp(4, tile_cols=1, compound=True)
     out["odd"] = st
+    st = StreamSpec(264, 200, seed=17)                       # hidden frame + shown frame in one superframe packet,
+    st.frames = _ippp(5, compound=True)                      # later shown again with show_existing_frame
+    st.frames[2].show = False
+    st.frames[2].refreshrefmask = 0x04
+    st.frames[2].superframe = True
+    st.frames[4] = FrameSpec(show_existing=2)
+    out["superframe"] = st
     st = StreamSpec(72, 40, seed=11)                         # tiny, single superblock column
     st.frames = _ippp(4, compound=True)
     out["tiny"] = st

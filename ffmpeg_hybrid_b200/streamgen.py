@@ -148,6 +148,9 @@ class FrameSpec:
     comppredmode: int = PRED_SWITCHABLE   # used only when sign biases differ
     bytes_per_sb: int = 1536              # over-provisioned payload per 64x64 superblock
     tile_bytes: Optional[List[int]] = None  # exact per-tile sizes (after trimming)
+    show_existing: int = -1               # 0..7: header-only frame that shows reference slot N (vp9.c:1636-1653)
+    superframe: bool = False              # packed into one packet with the NEXT frame (superframe index,
+                                          # split again by bsf/vp9_superframe_split.c:41-137)
 
 
 @dataclass
@@ -241,6 +244,10 @@ def encode_frame(st: StreamSpec, fs: FrameSpec, cur_w: int, cur_h: int,
     bw.u(2, 2)
     bw.u(1, st.profile & 1)
     bw.u(1, st.profile >> 1)
+    if fs.show_existing >= 0:
+        bw.u(1, 1)                        # show_existing_frame
+        bw.u(3, fs.show_existing)
+        return bw.bytes()
     bw.u(1, 0)                            # show_existing_frame
     bw.u(1, 0 if fs.keyframe else 1)
     bw.u(1, 1 if fs.show else 0)
@@ -375,6 +382,9 @@ def resolve_sizes(st: StreamSpec) -> List[tuple]:
     slots = [(st.width, st.height)] * 8
     sizes = []
     for fs in st.frames:
+        if fs.show_existing >= 0:
+            sizes.append(slots[fs.show_existing])
+            continue
         if fs.keyframe or fs.intraonly:
             w, h = fs.width or st.width, fs.height or st.height
         elif fs.size_from_ref >= 0:
@@ -392,6 +402,9 @@ def resolve_sizes(st: StreamSpec) -> List[tuple]:
 def tile_counts(st: StreamSpec) -> List[int]:
     out = []
     for fs, (w, h) in zip(st.frames, resolve_sizes(st)):
+        if fs.show_existing >= 0:
+            out.append(0)
+            continue
         mn, mx = tile_col_limits((w + 63) >> 6)
         l2c = min(max(fs.log2_tile_cols, mn), mx)
         out.append((1 << l2c) * (1 << fs.log2_tile_rows))
@@ -403,9 +416,20 @@ def encode_stream(st: StreamSpec) -> bytes:
     out = bytearray()
     out += b"DKIF" + struct.pack("<HH4sHHIIII", 0, 32, b"VP90", st.width, st.height,
                                  30, 1, len(st.frames), 0)
+    group: List[bytes] = []
     for i, (fs, (w, h)) in enumerate(zip(st.frames, sizes)):
         rng = np.random.default_rng([st.seed, i])
-        fr = encode_frame(st, fs, w, h, rng)
-        out += struct.pack("<IQ", len(fr), i)
-        out += fr
+        group.append(encode_frame(st, fs, w, h, rng))
+        if fs.superframe and i + 1 < len(st.frames) and len(group) < 8:
+            continue
+        if len(group) == 1:
+            pkt = group[0]
+        else:
+            # superframe index (VP9 bitstream spec annex B): marker, frame sizes, marker
+            mag = max(1, max((len(g).bit_length() + 7) // 8 for g in group))
+            marker = bytes([0xC0 | (mag - 1) << 3 | (len(group) - 1)])
+            pkt = b"".join(group) + marker + b"".join(len(g).to_bytes(mag, "little") for g in group) + marker
+        out += struct.pack("<IQ", len(pkt), i)
+        out += pkt
+        group = []
     return bytes(out)
