@@ -18,11 +18,14 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include "libavutil/buffer.h"
 #include "libavutil/frame.h"
+#include "libavutil/imgutils.h"
 #include "libavutil/log.h"
 #include "libavutil/mem.h"
 
 #include "avcodec.h"
+#include "packet.h"
 #include "vp9data.h"
 #include "vp9dec.h"
 #include "vp9cuda_glue.h"
@@ -37,6 +40,8 @@ typedef struct SinkApi {
     int  (*submit_tile)(Vp9CudaCtx *, uint32_t, int, const Vp9CudaLaneCounts *);
     int  (*finish_frame)(Vp9CudaCtx *, uint32_t, uint8_t *const[3], const ptrdiff_t[3], uint64_t *);
     int  (*wait)(Vp9CudaCtx *, uint64_t);
+    void *(*host_alloc)(size_t);             /* pinned host memory (NULL in the dump sink) */
+    void (*host_free)(void *);
 } SinkApi;
 
 struct VP9CudaGlue {
@@ -57,6 +62,14 @@ struct VP9CudaGlue {
     int lvl_w[3], lvl_h[3];
     size_t lvl_cap[3];
     uint32_t lvl_tag;
+    /* one frame in flight: the picture handed out by the NEXT ff_vp9cuda_deliver call */
+    int pipeline;
+    /* output pictures in pinned memory, so that the copy-out is a real asynchronous DMA */
+    AVBufferPool *frame_pool;
+    size_t frame_pool_size;
+    AVFrame *pending;
+    int pending_valid;
+    uint64_t pending_ticket, last_ticket;
 };
 
 /* ------------------------------------------------------------------------------------------
@@ -213,6 +226,74 @@ static int dump_wait(Vp9CudaCtx *c, uint64_t t) { return 0; }
 
 static VP9CudaGlue *glue_of(const VP9Context *s) { return s->cuda; }
 
+/* ------------------------------------------------------------------------------------------
+ * get_buffer2 in pinned memory.  The back end copies every finished picture into the decoder's
+ * AVFrame; into pageable memory that copy blocks the calling thread, into pinned memory it is an
+ * asynchronous DMA that runs beside the next frame's entropy decode.  Installed only when the
+ * application left the default allocator in place.  Buffers may outlive the decoder, so the
+ * free callback reaches the library through a process-wide pointer (the library stays loaded).
+ * ---------------------------------------------------------------------------------------- */
+static void (*pinned_host_free)(void *);
+
+static void pinned_buffer_free(void *opaque, uint8_t *data)
+{
+    pinned_host_free(data);
+}
+
+static AVBufferRef *pinned_buffer_alloc(void *opaque, size_t size)
+{
+    VP9CudaGlue *g = opaque;
+    AVBufferRef *ref;
+    uint8_t *p = g->api.host_alloc(size);
+    if (!p)
+        return NULL;
+    ref = av_buffer_create(p, size, pinned_buffer_free, NULL, 0);
+    if (!ref)
+        g->api.host_free(p);
+    return ref;
+}
+
+static int vp9cuda_get_buffer2(AVCodecContext *avctx, AVFrame *frame, int flags)
+{
+    VP9Context *s = avctx->priv_data;
+    VP9CudaGlue *g = s->cuda;
+    int w = frame->width, h = frame->height, ret, i;
+    int align[AV_NUM_DATA_POINTERS], linesize[4];
+    ptrdiff_t ls[4];
+    size_t plane[4], total = 0, off = 0;
+
+    if (!g || !g->api.host_alloc)
+        return avcodec_default_get_buffer2(avctx, frame, flags);
+    avcodec_align_dimensions2(avctx, &w, &h, align);
+    if ((ret = av_image_fill_linesizes(linesize, frame->format, w)) < 0)
+        return ret;
+    for (i = 0; i < 4; i++)
+        ls[i] = linesize[i] = FFALIGN(linesize[i], 64);
+    if ((ret = av_image_fill_plane_sizes(plane, frame->format, h, ls)) < 0)
+        return ret;
+    for (i = 0; i < 4; i++)
+        total += FFALIGN(plane[i], 64);
+    total += 64;
+    if (!g->frame_pool || g->frame_pool_size < total) {
+        /* one pool, sized for the largest picture seen (streams with resize frames alternate) */
+        av_buffer_pool_uninit(&g->frame_pool);
+        g->frame_pool = av_buffer_pool_init2(total, g, pinned_buffer_alloc, NULL);
+        if (!g->frame_pool)
+            return AVERROR(ENOMEM);
+        g->frame_pool_size = total;
+    }
+    frame->buf[0] = av_buffer_pool_get(g->frame_pool);
+    if (!frame->buf[0])
+        return AVERROR(ENOMEM);
+    for (i = 0; i < 4; i++) {
+        frame->linesize[i] = linesize[i];
+        frame->data[i] = plane[i] ? frame->buf[0]->data + off : NULL;
+        off += FFALIGN(plane[i], 64);
+    }
+    frame->extended_data = frame->data;
+    return 0;
+}
+
 int ff_vp9cuda_init(AVCodecContext *avctx)
 {
     VP9Context *s = avctx->priv_data;
@@ -242,7 +323,7 @@ int ff_vp9cuda_init(AVCodecContext *avctx)
                     if (!g->api.f) { av_log(avctx, AV_LOG_ERROR, "vp9cuda: missing symbol %s\n", #f); \
                                      dlclose(g->dl); av_free(g); return AVERROR(ENODEV); } } while (0)
         SYM(create); SYM(destroy); SYM(flush); SYM(begin_frame); SYM(tile_ring);
-        SYM(submit_tile); SYM(finish_frame); SYM(wait);
+        SYM(submit_tile); SYM(finish_frame); SYM(wait); SYM(host_alloc); SYM(host_free);
 #undef SYM
     }
     if (getenv("VP9CUDA_DEVICE"))
@@ -255,6 +336,20 @@ int ff_vp9cuda_init(AVCodecContext *avctx)
         av_free(g);
         return AVERROR(ENODEV);
     }
+    g->pipeline = !getenv("VP9CUDA_PIPELINE") || atoi(getenv("VP9CUDA_PIPELINE"));
+    if (g->api.host_alloc && avctx->get_buffer2 == avcodec_default_get_buffer2 &&
+        (!getenv("VP9CUDA_PINNED_FRAMES") || atoi(getenv("VP9CUDA_PINNED_FRAMES")))) {
+        pinned_host_free = g->api.host_free;
+        avctx->get_buffer2 = vp9cuda_get_buffer2;
+    }
+    g->pending = av_frame_alloc();
+    if (!g->pending) {
+        g->api.destroy(g->ctx);
+        if (g->dl)
+            dlclose(g->dl);
+        av_free(g);
+        return AVERROR(ENOMEM);
+    }
     s->cuda = g;
     return 0;
 }
@@ -265,8 +360,10 @@ void ff_vp9cuda_uninit(AVCodecContext *avctx)
     VP9CudaGlue *g = s->cuda;
     if (!g)
         return;
+    av_frame_free(&g->pending);
+    av_buffer_pool_uninit(&g->frame_pool);
     g->api.destroy(g->ctx);
-    if (g->dl)
+    if (g->dl && !pinned_host_free)    /* pinned pictures handed to the application may still be alive */
         dlclose(g->dl);
     for (int p = 0; p < 3; p++)
         av_freep(&g->lvl[p]);
@@ -277,8 +374,13 @@ void ff_vp9cuda_uninit(AVCodecContext *avctx)
 void ff_vp9cuda_flush(AVCodecContext *avctx)
 {
     VP9Context *s = avctx->priv_data;
-    if (s->cuda)
+    if (s->cuda) {
         s->cuda->api.flush(s->cuda->ctx);
+        if (s->cuda->pending_valid)
+            av_frame_unref(s->cuda->pending);
+        s->cuda->pending_valid = 0;
+        s->cuda->last_ticket = 0;
+    }
 }
 
 int ff_vp9cuda_begin_frame(AVCodecContext *avctx)
@@ -601,6 +703,49 @@ int ff_vp9cuda_end_frame(AVCodecContext *avctx)
     ret = g->api.finish_frame(g->ctx, g->fring.frame_id, planes, strides, &ticket);
     if (ret < 0)
         return AVERROR_EXTERNAL;
+    g->last_ticket = ticket;
+    if (g->pipeline)
+        return 0;                    /* ff_vp9cuda_deliver waits when it hands the picture out */
     ret = g->api.wait(g->ctx, ticket);
     return ret < 0 ? AVERROR_EXTERNAL : 0;
+}
+
+int ff_vp9cuda_deliver(AVCodecContext *avctx, AVFrame *frame, int *got_frame, AVFrame *src, const AVPacket *pkt)
+{
+    VP9Context *s = avctx->priv_data;
+    VP9CudaGlue *g = s->cuda;
+    int ret;
+
+    if (!g->pipeline) {
+        if (!src)
+            return 0;
+        /* a frame's own ticket was waited for in end_frame; show_existing_frame shows an older one */
+        if ((ret = av_frame_ref(frame, src)) < 0)
+            return ret;
+        if (pkt) {
+            frame->pts     = pkt->pts;
+            frame->pkt_dts = pkt->dts;
+        }
+        *got_frame = 1;
+        return 0;
+    }
+    if (g->pending_valid) {
+        if (g->pending_ticket && g->api.wait(g->ctx, g->pending_ticket) < 0)
+            return AVERROR_EXTERNAL;
+        av_frame_move_ref(frame, g->pending);
+        g->pending_valid = 0;
+        *got_frame = 1;
+    }
+    if (src) {
+        if ((ret = av_frame_ref(g->pending, src)) < 0)
+            return ret;
+        if (pkt) {
+            g->pending->pts     = pkt->pts;
+            g->pending->pkt_dts = pkt->dts;
+        }
+        /* tickets complete in order: the newest one covers the copy-out of any older picture */
+        g->pending_ticket = g->last_ticket;
+        g->pending_valid = 1;
+    }
+    return 0;
 }

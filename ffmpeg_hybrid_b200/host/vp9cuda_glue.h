@@ -32,7 +32,17 @@ int  ff_vp9cuda_begin_frame(struct AVCodecContext *avctx);
 void ff_vp9cuda_emit_block(struct VP9TileData *td);
 /* ff_vp9_loopfilter_sb, in place of filter_plane_cols/rows */
 void ff_vp9cuda_emit_lf(struct VP9Context *s, const struct VP9Filter *lflvl, int row, int col);
-/* vp9_decode_frame, after the tile loop: submit, reconstruct, copy CUR_FRAME back, wait */
+/* vp9_decode_frame, after the tile loop: submit, reconstruct, copy CUR_FRAME back (asynchronously
+ * when pipelined) */
 int  ff_vp9cuda_end_frame(struct AVCodecContext *avctx);
+/* vp9_decode_frame's output sites (vp9.c:1636-1653 show_existing_frame, :1853-1857 end of frame)
+ * and the drain call: `src` is the picture this call would normally return (NULL: none -- hidden
+ * frame or drain).  Pipelined (default, $VP9CUDA_PIPELINE=0 turns it off), the picture is held back
+ * until the next call so that its reconstruction and copy-out run beside the next frame's
+ * entropy decode; the decoder therefore advertises AV_CODEC_CAP_DELAY.  `pkt` != NULL stamps the
+ * picture with the packet's timestamps (show_existing_frame). */
+struct AVPacket;
+int  ff_vp9cuda_deliver(struct AVCodecContext *avctx, struct AVFrame *frame, int *got_frame,
+                        struct AVFrame *src, const struct AVPacket *pkt);
 
 #endif /* AVCODEC_VP9CUDA_GLUE_H */
