@@ -360,7 +360,8 @@ def main():
             bestk = max(got, key=got.get)
             line["full_decode"] = {"value": got[bestk], "unit": "frames/s", "host": bestk, "all": got,
                                    "what": "IVF packets -> libavcodec overlay (host entropy decode, one producer lane "
-                                           "per tile column) -> vp9cuda -> pictures in host memory, decoder's own clock"}
+                                           "per tile column, one frame in flight, pinned output frames) -> vp9cuda -> "
+                                           "pictures in host memory, decoder's own clock"}
         except Exception as e:  # noqa: BLE001
             line["full_decode"] = {"error": str(e)[:200]}
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
