@@ -2,7 +2,10 @@
  * k_inter.cuh -- K2: inter prediction for a whole frame (frame-centric, no dependencies).
  *
  *   k_cellmap : one thread per inter block record, writes the record index into every 8x8
- *               cell the block covers (the per-superblock mode / motion-vector map).
+ *               cell the block covers (the per-superblock mode / motion-vector map) and folds
+ *               the frame's largest downward motion vector into mv_reach.
+ *   k_inter_gate : optional (set_option "overlap_inter"): one warp in front of a band of k_inter
+ *               tile rows, waits for the previous frame's loop-filter rows the band can reach.
  *   k_inter   : one CTA per 64x32 luma tile (+ the two 32x16 chroma tiles under it).  A thread
  *               owns a vertical strip (8 luma or 4 chroma rows of one column): it filters the
  *               rows it needs horizontally once, then slides the vertical 8-tap over them.
