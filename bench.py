@@ -2,9 +2,13 @@
 """bench.py -- decoded frames/s of the VP9 reconstruction path on B200 (BASELINE.json metric).
 
 A "step" is one pass of the hot path over one synthetic stream (all its coded frames, in
-decode order).  Per GPU the workload is one independent stream (seed differs per rank):
-weak scaling, no inter-GPU traffic, no collective on the data path (torch.distributed is only
-the start barrier and the max-over-ranks of the device time).
+decode order).  Per GPU the workload is one independent stream: weak scaling, no inter-GPU
+traffic, no collective on the data path (torch.distributed is only the start barrier and the
+max-over-ranks of the device time).  Every rank generates and decodes its own copy of the SAME
+synthetic content, so that the work per GPU is fixed as N grows (streams of other seeds differ
+by up to 10 % in intra-block count and therefore in decode time: 752-832 frames/s over six
+seeds of C3 on one B200); --distinct-streams gives every rank its own seed instead and the
+slowest stream then sets the time.
 
   value : frames/s with every frame's records already resident in HBM (vp9cuda_run_staged),
           pictures stay in HBM.  Device time from CUDA events on the library's own stream.
@@ -41,6 +45,13 @@ WORKLOADS = {
     "c4": "7680x4320 8-bit all-keyframe stress stream, 8 frames",
     "c5": "3840x2160 8-bit C2-style stream (one of 8 independent streams), 30 frames",
 }
+
+
+def stream_index(args, rank: int) -> int:
+    """Which synthetic stream a rank decodes: 0 everywhere unless --distinct-streams / VP9BENCH_STREAM."""
+    if "VP9BENCH_STREAM" in os.environ:
+        return int(os.environ["VP9BENCH_STREAM"])
+    return rank if args.distinct_streams else 0
 
 
 def make_spec(workload: str, rank: int, frames: int):
@@ -102,7 +113,7 @@ def run_reference(args, rank, world):
     tmp = Path(tempfile.mkdtemp(prefix="vp9ref_"))
     ivfs, shown = [], 0
     for r in range(n_streams):
-        spec = make_spec(args.workload, r, args.frames)
+        spec = make_spec(args.workload, stream_index(args, r), args.frames)
         shown = sum(1 for f in spec.frames if f.show)
         ivfs.append(parity.write_stream(spec, tmp / f"s{r}.ivf"))
     threads = max(1, cores // n_streams)
@@ -131,6 +142,7 @@ def run_reference(args, rank, world):
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u16" if args.workload == "c3" else "u8",
         "data": "synthetic",
         "config": {"workload": f"{args.workload}: {WORKLOADS[args.workload]}", "streams": n_streams,
+                   "stream_content": "own seed per stream" if args.distinct_streams else "same content in every stream",
                    "frames_per_stream": shown, "decoder": "reference libavcodec vp9 (C-only DSP, no x86 asm)",
                    "threads_per_stream": threads, "thread_type": best,
                    "fps_by_thread_type": {k: n_streams * shown * args.steps / v for k, v in per_type.items()}},
@@ -151,6 +163,8 @@ def main():
     ap.add_argument("--impl", default="vp9cuda", choices=["vp9cuda", "reference"])
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
     ap.add_argument("--frames", type=int, default=0, help="shown frames per stream (0 = config default)")
+    ap.add_argument("--distinct-streams", action="store_true",
+                    help="every rank decodes a stream of its own seed (default: same content on every rank)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-full-decode", action="store_true")
     args = ap.parse_args()
@@ -171,6 +185,8 @@ def main():
         import torch.distributed as dist_
         dist = dist_
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"        # keep stdout to the one JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     # keep this rank's host threads and its pinned buffers on the CPU cores next to its GPU
@@ -194,7 +210,8 @@ def main():
 
     # ---- workload: synthetic stream -> (host entropy decode, untimed) record stream ----------
     tmp = Path(tempfile.mkdtemp(prefix=f"vp9bench_r{rank}_"))
-    spec = make_spec(args.workload, rank, args.frames)
+    # VP9BENCH_STREAM=k: decode stream k on this rank (to tell stream content from rank effects)
+    spec = make_spec(args.workload, stream_index(args, rank), args.frames)
     ivf = parity.write_stream(spec, tmp / "s.ivf")
     parity.dump_records(ivf, tmp / "s.v9r")
     frames = binding.load_stream(lib, tmp / "s.v9r", pinned=True)
@@ -327,6 +344,8 @@ def main():
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u16" if big.bpp > 8 else "u8", "data": "synthetic",
         "config": {"workload": f"{args.workload}: {WORKLOADS[args.workload]}", "streams_per_gpu": 1,
+                   "stream_content": "own seed per rank" if args.distinct_streams else
+                                     "every rank generates and decodes its own copy of the same content",
                    "coded_frames_per_step": n_coded, "shown_frames_per_step": n_shown,
                    "parallelism": f"{world} independent stream(s), one per GPU, no collective",
                    "l2": "inputs larger than L2: %.0f MB of records + a %d-surface reference pool per step"
