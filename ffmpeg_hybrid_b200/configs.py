@@ -122,6 +122,20 @@ def small_variants() -> Dict[str, StreamSpec]:
     st.frames[2].superframe = True
     st.frames[4] = FrameSpec(show_existing=2)
     out["superframe"] = st
+    st = StreamSpec(328, 264, seed=18)                       # segmentation: per-segment quantiser / loop-filter
+    st.frames = _ippp(6, compound=True)                      # level / reference / skip, every map mode
+    none = (None, None, None, False)
+    deltas = [none, (40, -10, None, False), (-30, 12, None, False), (90, None, None, False),
+              (None, 20, None, False), (-50, -16, 1, False), (10, 4, None, True), (25, None, 0, False)]
+    absolute = [(60, 16, None, False), (0, 0, None, False), (255, 63, None, False), (120, 40, None, False),
+                none, (30, 8, 2, False), (200, 50, None, True), (90, 24, None, False)]
+    tree = (120, 100, 140, 128, 90, 160, 110)
+    st.frames[0].segmentation = {"probs": tree, "feats": deltas}                      # key frame: map + data
+    st.frames[1].segmentation = {"probs": tree, "pred_probs": (200, 128, 60)}          # temporally predicted map
+    st.frames[2].segmentation = {}                                                      # map and data kept
+    st.frames[3].segmentation = {"probs": (128, None, 128, 128, None, 128, 128), "abs": True, "feats": absolute}
+    st.frames[4].segmentation = {"pred_probs": None, "probs": tree}                     # coded map, no prediction
+    out["segment"] = st                                      # frame 5: segmentation off again
     st = StreamSpec(72, 40, seed=11)                         # tiny, single superblock column
     st.frames = _ippp(4, compound=True)
     out["tiny"] = st

@@ -149,6 +149,11 @@ class FrameSpec:
     bytes_per_sb: int = 1536              # over-provisioned payload per 64x64 superblock
     tile_bytes: Optional[List[int]] = None  # exact per-tile sizes (after trimming)
     show_existing: int = -1               # 0..7: header-only frame that shows reference slot N (vp9.c:1636-1653)
+    # segmentation header (vp9.c:713-743); None = disabled.  Keys: "probs" (7 tree probabilities or
+    # None = no map update), "pred_probs" (3, or None = no temporal prediction), "abs" and "feats"
+    # (8 x (q delta | None, lf delta | None, ref 0..3 | None, skip bool), or None = no data update).
+    # The segment ids themselves come out of the tile payload like every other block symbol.
+    segmentation: Optional[dict] = None
     superframe: bool = False              # packed into one packet with the NEXT frame (superframe index,
                                           # split again by bsf/vp9_superframe_split.c:41-137)
 
@@ -331,7 +336,45 @@ def encode_frame(st: StreamSpec, fs: FrameSpec, cur_w: int, cur_h: int,
         else:
             bw.u(1, 0)
     lossless = fs.yac_qi == 0 and not (fs.ydc_qdelta or fs.uvdc_qdelta or fs.uvac_qdelta)
-    bw.u(1, 0)                            # segmentation disabled
+    seg = fs.segmentation
+    if seg is None:
+        bw.u(1, 0)                        # segmentation disabled
+    else:                                 # vp9.c:713-743
+        bw.u(1, 1)
+        probs = seg.get("probs")
+        bw.u(1, 1 if probs is not None else 0)
+        if probs is not None:
+            for pr in probs:
+                if pr is None or pr == 255:
+                    bw.u(1, 0)
+                else:
+                    bw.u(1, 1)
+                    bw.u(8, pr)
+            pred = seg.get("pred_probs")
+            bw.u(1, 1 if pred is not None else 0)
+            if pred is not None:
+                for pr in pred:
+                    if pr is None or pr == 255:
+                        bw.u(1, 0)
+                    else:
+                        bw.u(1, 1)
+                        bw.u(8, pr)
+        feats = seg.get("feats")
+        bw.u(1, 1 if feats is not None else 0)
+        if feats is not None:
+            bw.u(1, 1 if seg.get("abs") else 0)
+            assert len(feats) == 8
+            for q, lf, ref, skip in feats:
+                bw.u(1, 0 if q is None else 1)
+                if q is not None:
+                    bw.s_inv(8, q)
+                bw.u(1, 0 if lf is None else 1)
+                if lf is not None:
+                    bw.s_inv(6, lf)
+                bw.u(1, 0 if ref is None else 1)
+                if ref is not None:
+                    bw.u(2, ref)
+                bw.u(1, 1 if skip else 0)
     # tiles (vp9.c:800-812)
     sb_cols = (cur_w + 63) >> 6
     sb_rows = (cur_h + 63) >> 6
