@@ -136,6 +136,18 @@ def small_variants() -> Dict[str, StreamSpec]:
     st.frames[3].segmentation = {"probs": (128, None, 128, 128, None, 128, 128), "abs": True, "feats": absolute}
     st.frames[4].segmentation = {"pred_probs": None, "probs": tree}                     # coded map, no prediction
     out["segment"] = st                                      # frame 5: segmentation off again
+    st = StreamSpec(512, 320, seed=19)                       # reference scaling at its limits (vp9.c:854-877):
+    kw = dict(filtermode=FILTER_SWITCHABLE, txfmmode=TX_SWITCHABLE)      # 2:1 down, 16:1 up, non-integer and
+    st.frames = [                                                        # anisotropic ratios, scaled + unscaled
+        FrameSpec(keyframe=True, refreshrefmask=0xFF),                   # references (and compound) in one frame
+        FrameSpec(show=False, width=256, height=160, refreshrefmask=1 << 3, refidx=(0, 1, 2), **kw),
+        FrameSpec(intraonly=True, show=False, width=32, height=20, refreshrefmask=1 << 4, resetctx=0),
+        FrameSpec(refreshrefmask=1 << 5, refidx=(4, 4, 4), **kw),
+        FrameSpec(width=352, height=224, refreshrefmask=1 << 6, refidx=(0, 5, 1), signbias=(0, 0, 1), **kw),
+        FrameSpec(refreshrefmask=1 << 1, refidx=(0, 6, 3), signbias=(0, 1, 0), **kw),
+        FrameSpec(width=416, height=260, refreshrefmask=1 << 2, refidx=(6, 0, 3), signbias=(0, 0, 1), **kw),
+    ]
+    out["scale_mix"] = st
     st = StreamSpec(72, 40, seed=11)                         # tiny, single superblock column
     st.frames = _ippp(4, compound=True)
     out["tiny"] = st
