@@ -148,6 +148,9 @@ def small_variants() -> Dict[str, StreamSpec]:
         FrameSpec(width=416, height=260, refreshrefmask=1 << 2, refidx=(6, 0, 3), signbias=(0, 0, 1), **kw),
     ]
     out["scale_mix"] = st
+    st = StreamSpec(4096, 136, seed=20)                      # 16 tile columns (the most a 4096-wide frame may
+    st.frames = _ippp(3, tile_cols=4, compound=True, log2_tile_rows=1)   # have, vp9.c:800-810) x 2 tile rows
+    out["manytiles"] = st
     st = StreamSpec(72, 40, seed=11)                         # tiny, single superblock column
     st.frames = _ippp(4, compound=True)
     out["tiny"] = st

@@ -40,10 +40,11 @@ def test_baseline_configs_bit_exact(name, full, workdir):
     ivf.unlink()
 
 
-def test_tile_threaded_host_is_bit_exact(workdir):
+@pytest.mark.parametrize("name,threads", [("c2_small", 4), ("manytiles", 16), ("segment", 4)])
+def test_tile_threaded_host_is_bit_exact(name, threads, workdir):
     """slice threading: one producer lane per tile column (vp9.c:1442-1520)"""
-    ivf = parity.write_stream(configs.small_variants()["c2_small"], workdir / "mt.ivf")
-    assert parity.cuda_md5(ivf, threads=4, thread_type="slice") == GOLDEN["c2_small"]["framemd5"]
+    ivf = parity.write_stream(configs.small_variants()[name], workdir / "mt.ivf")
+    assert parity.cuda_md5(ivf, threads=threads, thread_type="slice") == GOLDEN[name]["framemd5"]
 
 
 def _md5_of(out, w, h, bpp):
