@@ -7,7 +7,8 @@ from __future__ import annotations
 
 from typing import Dict
 
-from .streamgen import (FILTER_SWITCHABLE, PRED_SWITCHABLE, TX_SWITCHABLE, FrameSpec, StreamSpec)
+from .streamgen import (FILTER_SWITCHABLE, PRED_SWITCHABLE, TX_4X4, TX_8X8, TX_16X16, TX_32X32, TX_SWITCHABLE,
+                        FrameSpec, StreamSpec)
 
 
 def _ippp(n: int, tile_cols: int = 0, compound: bool = False, **kw) -> list:
@@ -151,6 +152,20 @@ def small_variants() -> Dict[str, StreamSpec]:
     st = StreamSpec(4096, 136, seed=20)                      # 16 tile columns (the most a 4096-wide frame may
     st.frames = _ippp(3, tile_cols=4, compound=True, log2_tile_rows=1)   # have, vp9.c:800-810) x 2 tile rows
     out["manytiles"] = st
+    st = StreamSpec(296, 200, seed=21)                       # every fixed interpolation filter (header literals
+    st.frames = _ippp(6, compound=True)                      # 0..3 incl. bilinear) x every fixed transform mode,
+    for i, f in enumerate(st.frames):                        # integer-precision motion vectors on odd frames
+        f.txfmmode = (TX_32X32, TX_4X4, TX_8X8, TX_16X16, TX_32X32, TX_SWITCHABLE)[i]
+        if i:
+            f.filtermode = (0, 1, 2, 3, FILTER_SWITCHABLE)[i - 1]
+            f.highprecisionmvs = i % 2 == 0
+    out["filters_tx"] = st
+    st = StreamSpec(264, 168, seed=22)                       # coarsest quantiser: largest coefficients the 8-bit
+    st.frames = _ippp(3, compound=True, yac_qi=255, ydc_qdelta=15, uvdc_qdelta=-15, uvac_qdelta=15)
+    out["maxq"] = st                                         # (int16, wrapping) transform path sees
+    st = StreamSpec(200, 136, profile=2, bitdepth=12, seed=23)   # ... and the 12-bit (int32) one
+    st.frames = _ippp(3, compound=True, yac_qi=255, ydc_qdelta=15, uvdc_qdelta=15, uvac_qdelta=-15)
+    out["maxq12"] = st
     st = StreamSpec(72, 40, seed=11)                         # tiny, single superblock column
     st.frames = _ippp(4, compound=True)
     out["tiny"] = st
