@@ -170,3 +170,18 @@ def small_variants() -> Dict[str, StreamSpec]:
     st.frames = _ippp(4, compound=True)
     out["tiny"] = st
     return out
+
+
+def damaged_variants() -> Dict[str, StreamSpec]:
+    """Streams with one deliberately broken frame: the decoder must report the error for that packet,
+    keep its reference slots as they were and decode the following packets like the reference does."""
+    out: Dict[str, StreamSpec] = {}
+    for name, frame, damage in (("bad_marker", 2, "marker:1"), ("bad_tilesize", 3, "tilesize"),
+                                ("bad_first_tile", 1, "marker:0")):
+        st = c2(frames=6, w=456, h=264, seed=30 + len(out))
+        st.frames[frame].damage = damage
+        out[name] = st
+    st = c1(frames=5, seed=34)                               # second key frame with a broken sync code
+    st.frames[2] = FrameSpec(keyframe=True, refreshrefmask=0xFF, damage="sync")
+    out["bad_sync"] = st
+    return out

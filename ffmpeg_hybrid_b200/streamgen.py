@@ -154,6 +154,10 @@ class FrameSpec:
     # (8 x (q delta | None, lf delta | None, ref 0..3 | None, skip bool), or None = no data update).
     # The segment ids themselves come out of the tile payload like every other block symbol.
     segmentation: Optional[dict] = None
+    # deliberately damaged frame for the error-path tests: "marker:K" sets the marker bool of tile K
+    # (vp9.c:1345 -> AVERROR_INVALIDDATA in the middle of the frame), "tilesize" writes a tile size
+    # beyond the packet (vp9.c:1336-1341), "sync" breaks a key frame's sync code (vp9.c:552)
+    damage: Optional[str] = None
     superframe: bool = False              # packed into one packet with the NEXT frame (superframe index,
                                           # split again by bsf/vp9_superframe_split.c:41-137)
 
@@ -260,7 +264,7 @@ def encode_frame(st: StreamSpec, fs: FrameSpec, cur_w: int, cur_h: int,
     inter = False
     allowcomp = False
     if fs.keyframe:
-        bw.u(24, VP9_SYNCCODE)
+        bw.u(24, VP9_SYNCCODE ^ (1 if fs.damage == "sync" else 0))
         _color_config(bw, st)
         bw.u(16, cur_w - 1)
         bw.u(16, cur_h - 1)
@@ -409,12 +413,14 @@ def encode_frame(st: StreamSpec, fs: FrameSpec, cur_w: int, cur_h: int,
             full = 16 + (r1 - r0) * (c1 - c0) * fs.bytes_per_sb
             payload = rng.integers(0, 256, size=max(full, n), dtype=np.uint8)
             payload[0] &= 0x7F           # tile marker bool must decode to 0
+            if fs.damage == f"marker:{k}":
+                payload[0] |= 0x80
             payload = payload[:n]
             if tr == ntr - 1 and tc == ntc - 1:
                 payload[-1] = 0          # never look like a superframe index (0b110xxxxx)
             payload = payload.tobytes()
             if not (tr == ntr - 1 and tc == ntc - 1):
-                out += struct.pack(">I", len(payload))
+                out += struct.pack(">I", len(payload) + (1 << 20 if fs.damage == "tilesize" and k == 0 else 0))
             out += payload
             k += 1
     return bytes(out)

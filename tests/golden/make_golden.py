@@ -35,6 +35,16 @@ def main():
         print(name, len(md5), "frames")
         p.unlink()
     (Path(__file__).parent / "framemd5.json").write_text(json.dumps(out, indent=1) + "\n")
+    # streams with one deliberately broken frame: the pictures that still come out + the failing packet
+    bad = {}
+    for name, spec in configs.damaged_variants().items():
+        data = encode_stream(spec)
+        p = tmp / f"{name}.ivf"
+        p.write_bytes(data)
+        bad[name] = {"ivf_sha256": hashlib.sha256(data).hexdigest(), "ivf_bytes": len(data),
+                     "output": parity.ref_md5(p, allow_errors=True)}
+        p.unlink()
+    (Path(__file__).parent / "damaged.json").write_text(json.dumps(bad, indent=1) + "\n")
 
 
 if __name__ == "__main__":

@@ -86,6 +86,21 @@ def test_ctypes_record_path_and_resident_replay(name, workdir):
             f.free()
 
 
+DAMAGED = json.loads((ROOT / "tests" / "golden" / "damaged.json").read_text())
+
+
+@pytest.mark.parametrize("threads", [1, 4])
+@pytest.mark.parametrize("name", sorted(configs.damaged_variants()))
+def test_damaged_streams_fail_like_the_reference(name, threads, workdir):
+    """a broken frame (bad sync code, tile size beyond the packet, tile marker set in the first / a later
+    tile column, i.e. after begin_frame and after other tiles were submitted) is reported for the same
+    packet, the frame in flight is abandoned, the reference slots stay as they were and the following
+    packets decode to the reference's pictures"""
+    ivf = parity.write_stream(configs.damaged_variants()[name], workdir / f"{name}.ivf")
+    out = parity.cuda_md5(ivf, threads=threads, thread_type="slice" if threads > 1 else None, allow_errors=True)
+    assert out == DAMAGED[name]["output"]
+
+
 def test_errors_are_reported_not_hidden():
     from ffmpeg_hybrid_b200 import binding
     import ctypes as C

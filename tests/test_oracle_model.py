@@ -23,6 +23,21 @@ def test_stream_generator_is_deterministic(name):
     assert hashlib.sha256(data).hexdigest() == GOLDEN[name]["ivf_sha256"]
 
 
+DAMAGED = json.loads((ROOT / "tests" / "golden" / "damaged.json").read_text())
+
+
+@pytest.mark.parametrize("name", sorted(configs.damaged_variants()))
+def test_reference_on_damaged_streams_matches_golden(name, workdir):
+    """one deliberately broken frame per stream: which packet fails and which pictures still come out
+    (vp9.c:552, :1336-1345: error before / in the middle of the tile loop, reference slots untouched)"""
+    spec = configs.damaged_variants()[name]
+    assert hashlib.sha256(encode_stream(spec)).hexdigest() == DAMAGED[name]["ivf_sha256"]
+    ivf = parity.write_stream(spec, workdir / f"{name}.ivf")
+    out = parity.ref_md5(ivf, allow_errors=True)
+    assert out == DAMAGED[name]["output"]
+    assert sum(l.startswith("decode error") for l in out) == 1
+
+
 @pytest.mark.parametrize("name", SMALL)
 def test_reference_matches_golden(name, workdir):
     ivf = parity.write_stream(configs.small_variants()[name], workdir / f"{name}.ivf")

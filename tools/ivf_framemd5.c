@@ -103,7 +103,7 @@ int main(int argc, char **argv)
     AVPacket *pkt = av_packet_alloc();
     AVFrame *fr = av_frame_alloc();
     long pos = rl32(buf + 4) >> 16 ? 32 : 32; /* header length field is 16-bit at +6; always 32 */
-    int rc = 0;
+    int rc = 0, npkt = 0;
     double t0 = now_s();
     while (pos + 12 <= sz) {
         unsigned fsz = rl32(buf + pos);
@@ -115,11 +115,14 @@ int main(int argc, char **argv)
         pos += 12 + fsz;
         int r = avcodec_send_packet(c, pkt);
         av_packet_unref(pkt);
-        if (r < 0) { fprintf(stderr, "decode error %d at packet pts %ld\n", r, (long)pkt->pts); rc = 1; break; }
+        /* a damaged packet is reported and skipped, the following packets are still decoded and the
+         * decoder is drained at the end (what fftools does): the exit code says that something failed */
+        if (r < 0) { fprintf(stderr, "decode error %d at packet %d\n", r, npkt); rc = 1; }
+        npkt++;
         while ((r = avcodec_receive_frame(c, fr)) >= 0) { emit(fr); av_frame_unref(fr); }
-        if (r != AVERROR(EAGAIN) && r != AVERROR_EOF) { fprintf(stderr, "decode error %d\n", r); rc = 1; break; }
+        if (r != AVERROR(EAGAIN) && r != AVERROR_EOF) { fprintf(stderr, "decode error %d\n", r); rc = 1; }
     }
-    if (!rc) {
+    {
         avcodec_send_packet(c, NULL);
         int r;
         while ((r = avcodec_receive_frame(c, fr)) >= 0) { emit(fr); av_frame_unref(fr); }
