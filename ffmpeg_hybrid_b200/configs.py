@@ -166,6 +166,19 @@ def small_variants() -> Dict[str, StreamSpec]:
     st = StreamSpec(200, 136, profile=2, bitdepth=12, seed=23)   # ... and the 12-bit (int32) one
     st.frames = _ippp(3, compound=True, yac_qi=255, ydc_qdelta=15, uvdc_qdelta=15, uvac_qdelta=-15)
     out["maxq12"] = st
+    st = StreamSpec(200, 120, seed=24)                       # key frames that change the size mid-stream (surface
+    kw = dict(filtermode=FILTER_SWITCHABLE, txfmmode=TX_SWITCHABLE)      # pool re-created), size taken from a
+    st.frames = [                                                        # reference, non-reference frames, one slot
+        FrameSpec(keyframe=True, refreshrefmask=0xFF),                   # named three times
+        FrameSpec(refreshrefmask=0x00, refidx=(0, 0, 0), **kw),
+        FrameSpec(refreshrefmask=0x02, refidx=(0, 1, 2), size_from_ref=1, **kw),
+        FrameSpec(keyframe=True, refreshrefmask=0xFF, width=328, height=264),
+        FrameSpec(refreshrefmask=0x05, refidx=(2, 2, 5), size_from_ref=0, signbias=(0, 0, 1), **kw),
+        FrameSpec(refreshrefmask=0x00, refidx=(0, 2, 7), size_from_ref=2, **kw),
+        FrameSpec(keyframe=True, refreshrefmask=0xFF, width=72, height=40),
+        FrameSpec(refreshrefmask=0x80, refidx=(7, 3, 1), size_from_ref=2, signbias=(1, 0, 0), **kw),
+    ]
+    out["keyresize"] = st
     st = StreamSpec(72, 40, seed=11)                         # tiny, single superblock column
     st.frames = _ippp(4, compound=True)
     out["tiny"] = st
