@@ -103,6 +103,64 @@ class ClockSampler(threading.Thread):
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": self.sm_max, "reasons": sorted(self.reasons)}
 
 
+def concurrent_leg(binding, torch, frames, n_shown, device, steps):
+    """frames/s of 2 and 4 copies of the stream decoded side by side on one GPU (records resident)."""
+    out = {}
+    for S in (2, 4):
+        ctxs = [binding.Context(device=device, frames_in_flight=3) for _ in range(S)]
+        handles = [[c.stage(f) for f in frames] for c in ctxs]
+        go, done = threading.Barrier(S + 1), threading.Barrier(S + 1)
+        sums, errs = [None] * S, []
+
+        def worker(i):
+            try:
+                c, hs = ctxs[i], handles[i]
+                t = 0
+                for _ in range(2):
+                    for h in hs:
+                        t = c.run_staged(h, None)
+                c.wait(t)
+                go.wait()
+                for _ in range(steps):
+                    for h in hs:
+                        t = c.run_staged(h, None)
+                c.wait(t)
+                sums[i] = c.checksum(-1)
+            except Exception as e:  # noqa: BLE001
+                errs.append(repr(e))
+                go.abort()
+            finally:
+                try:
+                    done.wait()
+                except threading.BrokenBarrierError:
+                    pass
+
+        ts = [threading.Thread(target=worker, args=(i,)) for i in range(S)]
+        for t in ts:
+            t.start()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        try:
+            torch.cuda.synchronize()
+            go.wait()                   # the workers have finished (and waited for) their warm-up passes
+            e0.record()
+            done.wait()
+            e1.record()
+            torch.cuda.synchronize()
+        except threading.BrokenBarrierError:
+            done.abort()
+        for t in ts:
+            t.join()
+        for c in ctxs:
+            c.close()
+        if errs or len(set(sums)) != 1:
+            raise RuntimeError(f"{S} streams: {errs or sums}")
+        out[f"{S}_streams"] = S * n_shown * steps / (e0.elapsed_time(e1) * 1e-3)
+    out.update(unit="frames/s (aggregate, one GPU)", steps=steps,
+               what="copies of the stream (closed GOPs) decoded side by side, one context + host thread each, "
+                    "records resident, CUDA events around all of them")
+    return out
+
+
 def run_reference(args, rank, world):
     """Reference arm: ffvp9_ref on the host cores, rank 0 only."""
     if rank != 0:
@@ -166,6 +224,7 @@ def main():
     ap.add_argument("--distinct-streams", action="store_true",
                     help="every rank decodes a stream of its own seed (default: same content on every rank)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-concurrent", action="store_true", help="skip the side-by-side streams leg")
     ap.add_argument("--no-full-decode", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "vp9cuda" else args.warmup
@@ -377,6 +436,15 @@ def main():
         if p.returncode or not m:
             raise RuntimeError(p.stderr[-200:])
         return float(m.group(1))
+
+    if world == 1 and not args.no_concurrent:
+        # For information: S closed GOPs (copies of the stream) decoded side by side on this one GPU, one
+        # context and one host thread each, records resident.  The wavefront is latency-bound, so a second
+        # stream fills issue slots the first leaves idle; `value` above stays one stream per GPU.
+        try:
+            line["concurrent_streams"] = concurrent_leg(binding, torch, frames, n_shown, local, min(args.steps, 3))
+        except Exception as e:  # noqa: BLE001
+            line["concurrent_streams"] = {"error": str(e)[:200]}
 
     if rank == 0 and not args.no_full_decode:
         # packets in -> pictures on the host through the libavcodec overlay, host entropy decode included;

@@ -86,6 +86,56 @@ def test_ctypes_record_path_and_resident_replay(name, workdir):
             f.free()
 
 
+def test_streams_decoded_side_by_side_on_one_gpu(workdir):
+    """several streams in one process, one context each, driven from their own host threads at the same
+    time: the wavefront kernels of different contexts share the GPU -- a CTA only
+    ever waits for lower-numbered CTAs of its own launch, so they cannot block each other -- and every
+    stream still gives the reference's pictures"""
+    import threading
+    from ffmpeg_hybrid_b200 import binding
+    lib = binding.load()
+    names = ["c3_small", "c2_small", "c4_small", "hbd12", "segment", "scale_mix"]
+    jobs = {}
+    for name in names:
+        ivf = parity.write_stream(configs.small_variants()[name], workdir / f"{name}_mp.ivf")
+        parity.dump_records(ivf, workdir / f"{name}_mp.v9r")
+        jobs[name] = binding.load_stream(lib, workdir / f"{name}_mp.v9r", pinned=True)
+    got = {n: [] for n in names}
+    errs = []
+    start = threading.Barrier(len(names))
+
+    def worker(name):
+        try:
+            ctx = binding.Context(0)
+            frames = jobs[name]
+            start.wait()
+            for _ in range(3):                       # three passes: the streams drift against each other
+                pics = []
+                for f in frames:
+                    out = binding.OutFrame(lib, f.w, f.h, f.bpp)
+                    ctx.wait(ctx.decode(f, out))
+                    if not f.invisible:
+                        pics.append(_md5_of(out, f.w, f.h, f.bpp))
+                    out.free()
+                got[name].append(pics)
+            ctx.close()
+        except Exception as e:  # noqa: BLE001
+            errs.append((name, repr(e)))
+
+    ts = [threading.Thread(target=worker, args=(n,)) for n in names]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join()
+    assert not errs, errs
+    for name in names:
+        want = [" ".join(l.split()[1:]) for l in GOLDEN[name]["framemd5"]]
+        assert got[name] == [want] * 3, name
+    for frames in jobs.values():
+        for f in frames:
+            f.free()
+
+
 DAMAGED = json.loads((ROOT / "tests" / "golden" / "damaged.json").read_text())
 
 
