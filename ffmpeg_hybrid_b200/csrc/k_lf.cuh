@@ -452,8 +452,11 @@ template <class P> struct WaveSmem {
     static constexpr int BYTES = IntraSmem<P>::BYTES > LfSmem<P>::BYTES ? IntraSmem<P>::BYTES : LfSmem<P>::BYTES;
 };
 
+#ifndef VP9_WAVE_CTAS_PER_SM
+#define VP9_WAVE_CTAS_PER_SM 1
+#endif
 template <class P>
-__global__ void __launch_bounds__(INTRA_THREADS) k_wave(const __grid_constant__ FrameDesc f)
+__global__ void __launch_bounds__(INTRA_THREADS, VP9_WAVE_CTAS_PER_SM) k_wave(const __grid_constant__ FrameDesc f)
 {
     extern __shared__ __align__(16) unsigned char sm[];
     __shared__ IntraSig isig;
