@@ -39,7 +39,7 @@
 namespace vp9 {
 
 #ifndef INTRA_CW
-#define INTRA_CW 16                         /* compute warps */
+#define INTRA_CW 20                         /* compute warps */
 #endif
 #define INTRA_CT (INTRA_CW * 32)
 #define INTRA_THREADS (INTRA_CT + 3 * 32)   /* + body loader, top loader, storer */
