@@ -10,13 +10,19 @@ by up to 10 % in intra-block count and therefore in decode time: 752-832 frames/
 seeds of C3 on one B200); --distinct-streams gives every rank its own seed instead and the
 slowest stream then sets the time.
 
-  value : frames/s with every frame's records already resident in HBM (vp9cuda_run_staged),
-          pictures stay in HBM.  Device time from CUDA events on the library's own stream.
+  value : RECONSTRUCTION ONLY: frames/s with every frame's records already resident in HBM
+          (vp9cuda_run_staged), pictures stay in HBM.  Device time from CUDA events on the
+          library's own stream, per-stage instrumentation off (stage times come from a separate
+          untimed pass).  Compare with cpu_baseline.recon_only, not with cpu_baseline.value.
   e2e   : frames/s through the C ABI with HOST buffers: per frame the records go host->device
-          from pinned memory (vp9cuda_decode_frame) and every shown picture comes back
-          device->host into pinned memory.
-  full_decode : for information, packets in -> pictures out through the libavcodec overlay
-          (host entropy decode included), the same front end the reference arm runs.
+          from pinned memory (vp9cuda_decode_frame) and EVERY shown picture comes back
+          device->host into pinned memory.  Still reconstruction only (records, not packets).
+  full_decode : packets in -> pictures out through the libavcodec overlay (host entropy decode
+          included), the same front end and the same work the reference arm does; this is the
+          number to hold against cpu_baseline.value.  Beside it the host's ceiling: the same
+          decoder with the record sink pointed at /dev/null (entropy decode only).
+  workloads.c3p : the same measurements on C3 authored for a parallel host (frame-parallel
+          headers, 8 tile columns; configs.c3p), reference decoder timed on the same stream.
   --impl reference : the unmodified reference software decoder (oracle/_ref/ffvp9_ref, built
           from /root/reference by oracle/Makefile) on all host cores, same stream(s).
 
@@ -38,7 +44,10 @@ from pathlib import Path
 ROOT = Path(__file__).resolve().parent
 sys.path.insert(0, str(ROOT))
 
+LOOPS = 3   # passes over the stream per decoder run; the first one is the warm-up (tools/ivf_framemd5.c -loop)
+
 WORKLOADS = {
+    "c3p": "3840x2160 10-bit profile 2 like c3, frame-parallel headers (no backward adaptation), 8 tile columns",
     "c1": "352x288 8-bit profile 0, 30 frames",
     "c2": "1920x1080 8-bit profile 0 IPPP, 4 tile columns, compound, switchable filters, 60 frames",
     "c3": "3840x2160 10-bit profile 2, 32x32 transforms, scaled-reference (resize) frames, 30 shown + hidden frames",
@@ -62,6 +71,8 @@ def make_spec(workload: str, rank: int, frames: int):
         return configs.c2(frames=frames or 60, seed=2 + 100 * rank)
     if workload == "c3":
         return configs.c3(frames=frames or 30, seed=3 + 100 * rank)
+    if workload == "c3p":
+        return configs.c3p(frames=frames or 30, seed=3 + 100 * rank)
     if workload == "c4":
         return configs.c4(frames=frames or 8, seed=4 + 100 * rank)
     if workload == "c5":
@@ -161,6 +172,34 @@ def concurrent_leg(binding, torch, frames, n_shown, device, steps):
     return out
 
 
+def run_decoders(binary, ivfs, threads, ttype, loops=LOOPS, env=None):
+    """Decode every stream of `ivfs` at the same time, one process each (`-null`: no hashing); returns
+    aggregate frames/s from the decoders' own steady-state clocks (tools/ivf_framemd5.c -loop: the first
+    pass over a stream is the warm-up)."""
+    procs = [subprocess.Popen([str(binary), "-threads", str(threads), "-thread_type", ttype, "-null", "-loop", str(loops),
+                               str(p)], stdout=subprocess.DEVNULL, stderr=subprocess.PIPE, text=True, env=env)
+             for p in ivfs]
+    frames, secs = 0, 0.0
+    for p in procs:
+        _, err = p.communicate()
+        m = re.search(r"frames=(\d+) seconds=([0-9.]+)", err)
+        if p.returncode or not m:
+            raise RuntimeError(f"{Path(binary).name} failed: {err[-300:]}")
+        frames += int(m.group(1))
+        secs = max(secs, float(m.group(2)))
+    return frames / secs
+
+
+def reference_numbers(ivfs, cores, loops=LOOPS):
+    """the reference decoder on `cores` host threads over the given streams (side by side when there are
+    several): both of libavcodec's thread models (frame xor slice, pthread.c:49-65), the faster one counts"""
+    from ffmpeg_hybrid_b200 import parity
+    threads = max(1, cores // len(ivfs))
+    got = {tt: run_decoders(parity.REF_BIN, ivfs, threads, tt, loops) for tt in ("frame", "slice")}
+    best = max(got, key=got.get)
+    return got[best], best, threads, got
+
+
 def run_reference(args, rank, world):
     """Reference arm: ffvp9_ref on the host cores, rank 0 only."""
     if rank != 0:
@@ -174,39 +213,39 @@ def run_reference(args, rank, world):
         spec = make_spec(args.workload, stream_index(args, r), args.frames)
         shown = sum(1 for f in spec.frames if f.show)
         ivfs.append(parity.write_stream(spec, tmp / f"s{r}.ivf"))
-    threads = max(1, cores // n_streams)
-
-    def one_pass(ttype):
-        t0 = time.perf_counter()
-        procs = [subprocess.Popen([str(parity.REF_BIN), "-threads", str(threads), "-thread_type", ttype, "-null", str(p)],
-                                  stdout=subprocess.DEVNULL, stderr=subprocess.PIPE) for p in ivfs]
-        for p in procs:
-            p.communicate()
-            if p.returncode:
-                raise SystemExit("reference decoder failed")
-        return time.perf_counter() - t0
-    # both of libavcodec's thread models (frame xor slice, pthread.c:49-65); the faster one is reported
-    per_type = {}
-    for ttype in ("frame", "slice"):
-        for _ in range(args.warmup):
-            one_pass(ttype)
-        per_type[ttype] = sum(one_pass(ttype) for _ in range(args.steps))
-    best = min(per_type, key=per_type.get)
-    total = per_type[best]
-    fps = n_streams * shown * args.steps / total
+    # a "step" = one pass over the stream(s); warm-up passes are the -loop warm-up of every run
+    loops = max(2, args.steps + 1)
+    t0 = time.perf_counter()
+    fps, best, threads, per_type = reference_numbers(ivfs, cores, loops)
+    wall = time.perf_counter() - t0
+    extra = {}
+    if n_streams == 1 and cores >= 8:
+        # one stream cannot use more cores than it has tile columns / frames in flight: the same cores
+        # decoding cores/4 copies of the stream side by side (4 threads each) is the CPU's best figure
+        k = cores // 4
+        copies = [ivfs[0]] * k
+        try:
+            m_fps, m_best, m_thr, m_all = reference_numbers(copies, cores, 2)
+            extra = {"multi_stream": {"value": m_fps, "unit": "frames/s (aggregate)", "streams": k,
+                                      "threads_per_stream": m_thr, "thread_type": m_best,
+                                      "what": "the same stream decoded side by side by that many reference processes"}}
+        except Exception as e:  # noqa: BLE001
+            extra = {"multi_stream": {"error": str(e)[:200]}}
     line = {
         "impl": "reference", "metric": "decoded_frames_per_sec", "value": fps, "unit": "frames/s",
-        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u16" if args.workload == "c3" else "u8",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * n_streams * shown / fps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u16" if args.workload in ("c3", "c3p") else "u8",
         "data": "synthetic",
         "config": {"workload": f"{args.workload}: {WORKLOADS[args.workload]}", "streams": n_streams,
                    "stream_content": "own seed per stream" if args.distinct_streams else "same content in every stream",
-                   "frames_per_stream": shown, "decoder": "reference libavcodec vp9 (C-only DSP, no x86 asm)",
-                   "threads_per_stream": threads, "thread_type": best,
-                   "fps_by_thread_type": {k: n_streams * shown * args.steps / v for k, v in per_type.items()}},
+                   "frames_per_stream": shown, "decoder": "reference libavcodec vp9 (C-only DSP, no x86 asm): "
+                   "packets -> pictures, entropy decode + reconstruction",
+                   "threads_per_stream": threads, "thread_type": best, "fps_by_thread_type": per_type,
+                   "passes_per_run": loops, "wall_s": wall},
         "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": threads * n_streams, "kind": "reference",
-                         "sample": f"{args.steps} full passes over {n_streams} stream(s) of {shown} shown frames, "
-                                   f"-thread_type {best} (faster of frame / slice)"},
+                         "sample": f"{loops - 1} timed passes (after one warm-up pass) over {n_streams} stream(s) of {shown} "
+                                   f"shown frames, -thread_type {best} (faster of frame / slice)", **extra},
         "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line), flush=True)
@@ -291,8 +330,12 @@ def main():
 
     ctx = binding.Context(device=local, frames_in_flight=3)
     big = max(frames, key=lambda f: f.w * f.h)
-    outs = [binding.OutFrame(lib, big.w, big.h, big.bpp) for _ in range(2)]
-    d2h_per_step = sum(outs[0].nbytes for f in frames if not f.invisible and (f.w, f.h) == (big.w, big.h))
+    # two pinned output pictures per picture size, used alternately: EVERY shown frame is copied out
+    outs = {}
+    for f in frames:
+        if not f.invisible and (f.w, f.h) not in outs:
+            outs[(f.w, f.h)] = [binding.OutFrame(lib, f.w, f.h, f.bpp) for _ in range(2)]
+    d2h_per_step = sum(outs[(f.w, f.h)][0].nbytes for f in frames if not f.invisible)
 
     def barrier():
         if dist is not None:
@@ -316,8 +359,13 @@ def main():
         return t
     for _ in range(args.warmup):
         ctx.wait(step_resident())
+    # stage split: one untimed pass with per-stage CUDA events on; the timed region below runs without them
     ctx.option("reset_stats")
     ctx.option("timing", 1)
+    ctx.wait(step_resident())
+    stats = ctx.kernel_stats()
+    ctx.option("timing", 0)
+    ctx.option("reset_stats")
     sampler = ClockSampler(local)
     sampler.start()
     barrier()
@@ -329,8 +377,7 @@ def main():
     ctx.wait(t)
     barrier()
     ms_res = max_over_ranks(ctx.elapsed_ms(0, 1))
-    stats = ctx.kernel_stats()
-    ctx.option("timing", 0)
+    launches_timed = sum(v["launches"] for v in ctx.kernel_stats().values())
     checksum_resident = ctx.checksum(-1)
 
     if os.environ.get("VP9CUDA_PHASE"):
@@ -347,8 +394,8 @@ def main():
         k = 0
         for f in frames:
             o = None
-            if not f.invisible and (f.w, f.h) == (big.w, big.h):
-                o = outs[k & 1]
+            if not f.invisible:
+                o = outs[(f.w, f.h)][k & 1]
                 k += 1
             t = ctx.decode(f, o)
         return t
@@ -399,9 +446,11 @@ def main():
                         "overlap the compute stream, so stage times sum to more than the step",
                 "avg_launch_ms": d["ms"] / d["launches"],
                 "algorithmic_bytes_per_launch": d["bytes"] / d["launches"],
-                "stage_ms_per_step": {k: v["ms"] / args.steps for k, v in stats.items()},
+                "stage_ms_per_step": {k: v["ms"] for k, v in stats.items()},
+                "stage_timing": "CUDA events around every stage on the stream it is launched on, in a separate pass over the "
+                                "same step right before the timed region (the timed region itself runs without them)",
                 "stage_share": {k: v["ms"] / max(sum(x["ms"] for x in stats.values()), 1e-9) for k, v in stats.items()}}
-    gpu_launches = sum(v["launches"] for v in stats.values())
+    gpu_launches = launches_timed
 
     total_shown = n_shown * args.steps * world
     value = total_shown / (ms_res * 1e-3)
@@ -413,6 +462,8 @@ def main():
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u16" if big.bpp > 8 else "u8", "data": "synthetic",
         "config": {"workload": f"{args.workload}: {WORKLOADS[args.workload]}", "streams_per_gpu": 1,
+                   "value_scope": "reconstruction only: records (entropy-decoded beforehand) resident in HBM -> pictures in HBM; "
+                                  "hold it against cpu_baseline.recon_only. Packets -> pictures is full_decode.",
                    "stream_content": "own seed per rank" if args.distinct_streams else
                                      "every rank generates and decodes its own copy of the same content",
                    "coded_frames_per_step": n_coded, "shown_frames_per_step": n_shown,
@@ -428,14 +479,7 @@ def main():
     }
 
     cores = os.cpu_count() or 1
-
-    def timed_decoder(binary, threads, ttype, env=None):
-        p = subprocess.run([str(binary), "-threads", str(threads), "-thread_type", ttype, "-null", str(ivf)],
-                           capture_output=True, text=True, env=env)
-        m = re.search(r"fps=([0-9.]+)", p.stderr)
-        if p.returncode or not m:
-            raise RuntimeError(p.stderr[-200:])
-        return float(m.group(1))
+    share = max(1, cores // world)            # host threads this rank may use when all ranks decode at once
 
     if world == 1 and not args.no_concurrent:
         # For information: S closed GOPs (copies of the stream) decoded side by side on this one GPU, one
@@ -446,32 +490,86 @@ def main():
         except Exception as e:  # noqa: BLE001
             line["concurrent_streams"] = {"error": str(e)[:200]}
 
-    if rank == 0 and not args.no_full_decode:
-        # packets in -> pictures on the host through the libavcodec overlay, host entropy decode included;
-        # same front end and the same "-null" (no hashing) as the CPU baseline below
-        try:
-            env = dict(os.environ, VP9CUDA_LIB=str(parity.CUDA_LIB), VP9CUDA_DEVICE=str(local))
-            env.pop("VP9CUDA_DUMP", None)
-            got = {f"{t} threads ({tt})": timed_decoder(parity.CUDA_BIN, t, tt, env)
-                   for t, tt in ((1, "slice"), (min(cores, 8), "slice"))}
-            bestk = max(got, key=got.get)
-            line["full_decode"] = {"value": got[bestk], "unit": "frames/s", "host": bestk, "all": got,
-                                   "what": "IVF packets -> libavcodec overlay (host entropy decode, one producer lane "
-                                           "per tile column, one frame in flight, pinned output frames) -> vp9cuda -> "
-                                           "pictures in host memory, decoder's own clock"}
-        except Exception as e:  # noqa: BLE001
-            line["full_decode"] = {"error": str(e)[:200]}
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        got = {tt: timed_decoder(parity.REF_BIN, cores, tt) for tt in ("frame", "slice")}
+    def sum_over_ranks(v):
+        if dist is None:
+            return v
+        t = torch.tensor([v], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    def host_legs(stream, with_cpu):
+        """packets -> pictures through the libavcodec overlay (the work the reference arm does), the host's
+        ceiling (same decoder, record sink /dev/null = entropy decode only) and the reference decoder itself,
+        all on the same stream, same front end, same `-null`, steady state after one warm-up pass"""
+        env = dict(os.environ, VP9CUDA_LIB=str(parity.CUDA_LIB), VP9CUDA_DEVICE=str(local))
+        env.pop("VP9CUDA_DUMP", None)
+        null_env = dict(os.environ, VP9CUDA_DUMP="/dev/null")
+        modes = [(share, "frame"), (min(share, 8), "slice")] + ([(1, "slice")] if world == 1 else [])
+        out = {}
+        barrier()
+        got = {f"{t} threads ({tt})": sum_over_ranks(run_decoders(parity.CUDA_BIN, [stream], t, tt, LOOPS, env))
+               for t, tt in modes}
         bestk = max(got, key=got.get)
-        line["cpu_baseline"] = {"value": got[bestk], "unit": "frames/s", "cores": cores, "kind": "reference",
-                                "sample": f"one pass over the same stream ({n_shown} shown frames), ffvp9_ref -threads {cores} "
-                                          f"-thread_type {bestk} (faster of frame {got['frame']:.1f} / slice {got['slice']:.1f} "
-                                          "frames/s; C-only DSP, no x86 asm)"}
+        out["full_decode"] = {"value": got[bestk], "unit": "frames/s", "host": bestk, "all": got,
+                              "what": "IVF packets -> libavcodec overlay (host entropy decode on frame threads = one "
+                                      "frame per worker, or on tile threads = one lane per tile column; pinned output "
+                                      "frames) -> vp9cuda -> pictures in host memory; decoder's own clock, %d passes after "
+                                      "one warm-up pass; aggregate over %d rank(s) decoding at the same time" % (LOOPS - 1, world)}
+        barrier()
+        ceil = {f"{t} threads ({tt})": sum_over_ranks(run_decoders(parity.CUDA_BIN, [stream], t, tt, LOOPS, null_env))
+                for t, tt in modes}
+        out["entropy_only"] = {"value": ceil[bestk], "unit": "frames/s", "host": bestk, "all": ceil,
+                               "what": "the same decoder with the record sink pointed at /dev/null: the host's serial "
+                                       "bool-decoder work alone, i.e. the ceiling of full_decode on this host",
+                               "full_decode_over_ceiling": got[bestk] / ceil[bestk]}
+        if with_cpu:
+            fps, best, threads, per_type = reference_numbers([stream], cores)
+            one = run_decoders(parity.REF_BIN, [stream], 1, "slice", 2)
+            ent1 = ceil.get("1 threads (slice)") or run_decoders(parity.CUDA_BIN, [stream], 1, "slice", 2, null_env)
+            recon1 = 1.0 / max(1.0 / one - 1.0 / ent1, 1e-9)
+            out["cpu_baseline"] = {
+                "value": fps, "unit": "frames/s", "cores": cores, "kind": "reference",
+                "sample": f"{LOOPS - 1} passes (after one warm-up pass) over the same stream ({n_shown} shown frames), ffvp9_ref "
+                          f"-threads {cores} -thread_type {best} (faster of frame {per_type['frame']:.1f} / slice "
+                          f"{per_type['slice']:.1f} frames/s; C-only DSP, no x86 asm); packets -> pictures",
+                "one_thread": one,
+                "recon_only": {"value_one_thread": recon1, "value_all_cores_ideal": recon1 * cores, "unit": "frames/s",
+                               "what": "reconstruction share of the reference: 1 / (1/ref - 1/entropy_only) on one thread "
+                                       "(entropy_only = the overlay decoder with the record sink at /dev/null); the all-core "
+                                       "figure assumes perfect scaling over %d cores and is the like-for-like baseline for "
+                                       "`value` and `e2e`" % cores,
+                               "entropy_only_one_thread": ent1},
+            }
+            out["ratios"] = {"full_decode_over_cpu": got[bestk] / fps,
+                             "value_over_cpu_recon_only_ideal": value / (recon1 * cores),
+                             "e2e_over_cpu_recon_only_ideal": e2e_value / (recon1 * cores),
+                             "value_over_cpu_whole_decoder": value / fps,
+                             "note": "the driver's ratio divides e2e (records -> pictures) by the reference arm (packets -> "
+                                     "pictures); full_decode_over_cpu is the decoder-for-decoder figure"}
+        return out
+
+    if not args.no_full_decode:
+        try:
+            line.update(host_legs(ivf, with_cpu=world == 1 and not args.no_cpu_baseline))
+        except Exception as e:  # noqa: BLE001
+            line["full_decode"] = {"error": str(e)[:300]}
+        if args.workload == "c3" and world == 1:
+            # the same on C3 authored for a parallel host (frame-parallel headers, 8 tile columns)
+            try:
+                pspec = make_spec("c3p", stream_index(args, rank), args.frames)
+                pivf = parity.write_stream(pspec, tmp / "p.ivf")
+                line["workloads"] = {"c3p": dict(host_legs(pivf, with_cpu=not args.no_cpu_baseline),
+                                                 workload="c3p: " + WORKLOADS["c3p"])}
+                line["workloads"]["c3p"].get("ratios", {}).pop("value_over_cpu_recon_only_ideal", None)
+                line["workloads"]["c3p"].get("ratios", {}).pop("e2e_over_cpu_recon_only_ideal", None)
+                line["workloads"]["c3p"].get("ratios", {}).pop("value_over_cpu_whole_decoder", None)
+            except Exception as e:  # noqa: BLE001
+                line["workloads"] = {"c3p": {"error": str(e)[:300]}}
     if rank == 0:
         print(json.dumps(line), flush=True)
-    for o in outs:
-        o.free()
+    for pair in outs.values():
+        for o in pair:
+            o.free()
     for f in frames:
         f.free()
     ctx.close()

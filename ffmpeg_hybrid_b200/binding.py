@@ -18,7 +18,7 @@ MAX_LANES = 64
 
 API = [
     "vp9cuda_version", "vp9cuda_create", "vp9cuda_destroy", "vp9cuda_flush", "vp9cuda_begin_frame",
-    "vp9cuda_tile_ring", "vp9cuda_submit_tile", "vp9cuda_finish_frame", "vp9cuda_wait",
+    "vp9cuda_tile_ring", "vp9cuda_submit_tile", "vp9cuda_finish_frame", "vp9cuda_abort_frame", "vp9cuda_wait", "vp9cuda_get_stat",
     "vp9cuda_show_existing", "vp9cuda_host_alloc", "vp9cuda_host_free", "vp9cuda_decode_frame",
     "vp9cuda_stage_frame", "vp9cuda_run_staged", "vp9cuda_free_staged", "vp9cuda_frame_checksum",
     "vp9cuda_kernel_stats", "vp9cuda_set_option", "vp9cuda_elapsed_ms", "vp9cuda_phase_clocks", "vp9cuda_slot_itxfm_add",
@@ -34,19 +34,23 @@ class MappedFrame(C.Structure):
 
 class LaneRing(C.Structure):
     _fields_ = [("blk", C.c_void_p), ("blk_cap", C.c_uint32),
-                ("tx", C.c_void_p * 4), ("tx_cap", C.c_uint32 * 4),
+                ("tx", C.c_void_p), ("tx_cap", C.c_uint32),
                 ("itx", C.c_void_p), ("itx_cap", C.c_uint32),
                 ("coef", C.c_void_p), ("coef_cap", C.c_uint32),
                 ("coef_base", C.c_uint32), ("reserved", C.c_uint32)]
 
 
 class LaneCounts(C.Structure):
-    _fields_ = [("blk", C.c_uint32), ("tx", C.c_uint32 * 4), ("itx", C.c_uint32), ("coef", C.c_uint32)]
+    _fields_ = [("blk", C.c_uint32), ("tx", C.c_uint32), ("itx", C.c_uint32), ("coef", C.c_uint32)]
 
 
 class FrameRecords(C.Structure):
     _fields_ = [("lanes", C.POINTER(LaneRing)), ("counts", C.POINTER(LaneCounts)),
                 ("sb_index", C.c_void_p), ("lf", C.c_void_p)]
+
+
+class FrameRing(C.Structure):
+    _fields_ = [("sb_index", C.c_void_p), ("lf", C.c_void_p), ("n_sb", C.c_uint32), ("frame_id", C.c_uint32)]
 
 
 _lib = None
@@ -80,6 +84,13 @@ def load() -> C.CDLL:
         lib.vp9cuda_set_option.argtypes = [C.c_void_p, C.c_char_p, C.c_int]
         lib.vp9cuda_elapsed_ms.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_double)]
         lib.vp9cuda_phase_clocks.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.c_int]
+        lib.vp9cuda_begin_frame.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(FrameRing)]
+        lib.vp9cuda_tile_ring.argtypes = [C.c_void_p, C.c_uint32, C.c_int, C.POINTER(LaneRing)]
+        lib.vp9cuda_submit_tile.argtypes = [C.c_void_p, C.c_uint32, C.c_int, C.POINTER(LaneCounts)]
+        lib.vp9cuda_finish_frame.argtypes = [C.c_void_p, C.c_uint32, C.POINTER(C.c_void_p), C.POINTER(C.c_ssize_t),
+                                             C.POINTER(C.c_uint64)]
+        lib.vp9cuda_get_stat.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(C.c_uint64)]
+        lib.vp9cuda_abort_frame.argtypes = [C.c_void_p, C.c_uint32]
         lib.vp9cuda_kernel_stats.argtypes = [C.c_void_p, C.POINTER(C.c_char_p), C.POINTER(C.c_double),
                                              C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.c_int]
         _lib = lib
@@ -107,15 +118,13 @@ class HostFrame:
         for i, l in enumerate(fr.lanes):
             r = self.lanes[i]
             r.blk = self._put(l.blk)
-            for t in range(4):
-                r.tx[t] = self._put(l.tx[t])
+            r.tx = self._put(l.tx)
             r.itx = self._put(l.itx)
             r.coef = self._put(l.coef)
             r.coef_base = l.coef_base
             c = self.counts[i]
             c.blk = int(l.counts["blk"])
-            for t in range(4):
-                c.tx[t] = int(l.counts["tx"][t])
+            c.tx = int(l.counts["tx"])
             c.itx = int(l.counts["itx"])
             c.coef = int(l.counts["coef"])
         self.recs = FrameRecords()
@@ -176,10 +185,15 @@ class OutFrame:
 
 
 class Context:
-    def __init__(self, device: int = 0, frames_in_flight: int = 2):
+    def __init__(self, device: int = 0, frames_in_flight: int = 2, max_w: int = 0, max_h: int = 0, max_bpp: int = 12):
         self.lib = load()
         self.ctx = C.c_void_p()
-        check(self.lib.vp9cuda_create(C.byref(self.ctx), device, 0, 0, 12, frames_in_flight), "vp9cuda_create")
+        check(self.lib.vp9cuda_create(C.byref(self.ctx), device, max_w, max_h, max_bpp, frames_in_flight), "vp9cuda_create")
+
+    def stat(self, key: str) -> int:
+        v = C.c_uint64()
+        check(self.lib.vp9cuda_get_stat(self.ctx, key.encode(), C.byref(v)), f"get_stat({key})")
+        return v.value
 
     def close(self) -> None:
         if self.ctx:
@@ -206,6 +220,47 @@ class Context:
         strides = out.strides if out is not None else None
         check(self.lib.vp9cuda_run_staged(self.ctx, handle, planes, strides, C.byref(t)), "vp9cuda_run_staged")
         return t.value
+
+    def begin(self, fr: "v9r.Frame") -> "FrameRing":
+        """vp9cuda_begin_frame for a dumped frame; returns the frame ring (its frame_id names the frame)"""
+        ring = FrameRing()
+        hdr = (C.c_char * v9r.HDR_DTYPE.itemsize).from_buffer_copy(fr.hdr.tobytes())
+        check(self.lib.vp9cuda_begin_frame(self.ctx, C.addressof(hdr), C.byref(ring)), "vp9cuda_begin_frame")
+        return ring
+
+    def produce(self, fr: "v9r.Frame", ring: "FrameRing", splits: int = 1) -> None:
+        """what the libavcodec glue does between begin_frame and finish_frame: write the lanes' records into
+        the pinned rings and submit them in `splits` growing portions per lane"""
+        ceb = v9r.COEF32_DTYPE.itemsize if fr.hdr["bpp"] > 8 else v9r.COEF16_DTYPE.itemsize
+        for i, l in enumerate(fr.lanes):
+            lr = LaneRing()
+            check(self.lib.vp9cuda_tile_ring(self.ctx, ring.frame_id, i, C.byref(lr)), "vp9cuda_tile_ring")
+            assert lr.coef_base == l.coef_base, "the dump and the library place the lanes alike"
+            tot = {k: int(l.counts[k]) for k in ("blk", "tx", "itx", "coef")}
+            assert tot["blk"] <= lr.blk_cap and tot["tx"] <= lr.tx_cap and tot["itx"] <= lr.itx_cap and tot["coef"] <= lr.coef_cap
+            done = dict.fromkeys(tot, 0)
+            for k in range(1, splits + 1):
+                upto = {n: tot[n] * k // splits for n in tot}
+                for name, ptr_, data, sz in (("blk", lr.blk, l.blk, v9r.BLK_SIZE), ("tx", lr.tx, l.tx, v9r.TX_SIZE),
+                                             ("itx", lr.itx, l.itx, v9r.ITX_SIZE), ("coef", lr.coef, l.coef, ceb)):
+                    a, b = done[name] * sz, upto[name] * sz
+                    if b > a:
+                        C.memmove(ptr_ + a, data[a:b], b - a)
+                done = upto
+                c = LaneCounts(upto["blk"], upto["tx"], upto["itx"], upto["coef"])
+                check(self.lib.vp9cuda_submit_tile(self.ctx, ring.frame_id, i, C.byref(c)), "vp9cuda_submit_tile")
+        C.memmove(ring.sb_index, fr.sb_index, len(fr.sb_index))
+        C.memmove(ring.lf, fr.lf, len(fr.lf))
+
+    def finish(self, ring: "FrameRing", out: Optional[OutFrame]) -> int:
+        t = C.c_uint64()
+        planes = out.planes if out is not None else None
+        strides = out.strides if out is not None else None
+        check(self.lib.vp9cuda_finish_frame(self.ctx, ring.frame_id, planes, strides, C.byref(t)), "vp9cuda_finish_frame")
+        return t.value
+
+    def abort(self, ring: "FrameRing") -> None:
+        check(self.lib.vp9cuda_abort_frame(self.ctx, ring.frame_id), "vp9cuda_abort_frame")
 
     def wait(self, ticket: int) -> None:
         check(self.lib.vp9cuda_wait(self.ctx, ticket), "vp9cuda_wait")

@@ -61,6 +61,18 @@ def c3(frames: int = 30, seed: int = 3, w: int = 3840, h: int = 2160) -> StreamS
     return st
 
 
+def c3p(frames: int = 30, seed: int = 3, w: int = 3840, h: int = 2160) -> StreamSpec:
+    """C3 authored for a parallel host (SURVEY.md section 7 "hard parts" (b)): the same 4K 10-bit
+    content model, but every frame sets frame_parallel_decoding_mode (no backward probability
+    adaptation, so the entropy decode of frame N+1 does not wait for frame N, vp9.c:1731-1756) and
+    the frames carry 8 tile columns instead of 4."""
+    st = c3(frames=frames, seed=seed, w=w, h=h)
+    for f in st.frames:
+        f.parallelmode = True
+        f.log2_tile_cols = 3
+    return st
+
+
 def c4(frames: int = 8, seed: int = 4, w: int = 7680, h: int = 4320) -> StreamSpec:
     """8K 8-bit, all key frames (intra + loop-filter wavefront bound); second half at max LF level."""
     st = StreamSpec(w, h, seed=seed)
@@ -81,6 +93,7 @@ def small_variants() -> Dict[str, StreamSpec]:
     out["c1_small"] = c1(frames=6)
     out["c2_small"] = c2(frames=5, w=456, h=264)           # non-multiple-of-8 size, 4 tile cols cap
     out["c3_small"] = c3(frames=8, w=400, h=240)
+    out["c3p_small"] = c3p(frames=8, w=528, h=240)          # frame-parallel headers + 2 tile columns
     out["c4_small"] = c4(frames=2, w=520, h=392)
     st = StreamSpec(200, 136, profile=2, bitdepth=12, seed=7)  # 12-bit
     st.frames = _ippp(4, compound=True)
@@ -194,6 +207,10 @@ def damaged_variants() -> Dict[str, StreamSpec]:
         st = c2(frames=6, w=456, h=264, seed=30 + len(out))
         st.frames[frame].damage = damage
         out[name] = st
+    st = c2(frames=14, w=456, h=264, seed=35)                # four broken frames in one stream, two of them back
+    for frame, damage in ((2, "marker:1"), (5, "tilesize"), (6, "marker:0"), (10, "marker:1")):   # to back: every
+        st.frames[frame].damage = damage                     # failed frame must give its ring set back
+    out["bad_many"] = st
     st = c1(frames=5, seed=34)                               # second key frame with a broken sync code
     st.frames[2] = FrameSpec(keyframe=True, refreshrefmask=0xFF, damage="sync")
     out["bad_sync"] = st

@@ -38,8 +38,8 @@ struct IntraRec {
     uint8_t lx, ly;                  /* position inside the superblock plane, 4-pixel units */
     uint8_t plane, tx, mode /* edge-converted */, txtp, flags /* 1 left, 2 right, 4 top */, pad;
     uint16_t eob;
-    uint16_t run;                    /* unused */
-    uint32_t coef_off;               /* first coefficient in the frame's arena */
+    uint16_t ncoef;                  /* coefficient entries (non-zero coefficients) */
+    uint32_t coef_off;               /* first entry in the frame's coefficient stream */
 };
 
 /* Everything a kernel needs to know about the frame being reconstructed. */
@@ -50,16 +50,19 @@ struct FrameDesc {
     uint16_t mvscale[3][2];
     uint8_t mvstep[3][2];
     uint8_t lossless, lf_level;
-    /* records (device pointers), lanes already concatenated */
-    const Vp9CudaInterBlock *blk;  uint32_t n_blk;
-    const Vp9CudaTx *tx[4];        uint32_t n_tx[4];
+    /* records (device pointers); lane l owns elements [lane_*_base[l], lane_*_base[l] + lane_*_cnt[l]) */
+    const Vp9CudaInterBlock *blk;  uint32_t n_blk;     /* totals over the lanes */
+    const Vp9CudaTx *tx;           uint32_t n_tx;
     const Vp9CudaIntraTx *itx;     uint32_t n_itx;
-    const void *coef;              /* int16_t (8-bit) or int32_t units, arena indexed by coef_off */
+    const void *coef;              /* Vp9CudaCoef16 (8-bit) or Vp9CudaCoef32 entries, indexed by coef_off */
     const Vp9CudaSbIndex *sb_index;
     const Vp9CudaLoopFilterSb *lf;
+    int n_lanes;
+    uint32_t lane_blk_base[VP9CUDA_MAX_LANES], lane_blk_cnt[VP9CUDA_MAX_LANES];
+    uint32_t lane_tx_base[VP9CUDA_MAX_LANES], lane_tx_cnt[VP9CUDA_MAX_LANES];
+    uint32_t lane_itx_base[VP9CUDA_MAX_LANES]; /* first itx record of each lane */
     /* scratch */
     int32_t *cellmap;              /* cols*rows: index into blk, -1 = not inter */
-    uint32_t lane_itx_base[VP9CUDA_MAX_LANES]; /* first itx record of each lane in the concatenated list */
     IntraSb *isb;                  /* [sb] intra work of each superblock */
     IntraRec *irec;                /* n_itx records regrouped per superblock, sorted by depth */
     int *iprogress;                /* [2][sb_rows] intra wavefront counters: border row stored, superblock stored */

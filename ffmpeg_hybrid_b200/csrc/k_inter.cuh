@@ -1,7 +1,7 @@
 /*
  * k_inter.cuh -- K2: inter prediction for a whole frame (frame-centric, no dependencies).
  *
- *   k_cellmap : one thread per inter block record, writes the record index into every 8x8
+ *   k_cellmap : one thread per inter block record (grid.y = producer lane), writes the record index into every 8x8
  *               cell the block covers (the per-superblock mode / motion-vector map) and folds
  *               the frame's largest downward motion vector into mv_reach.
  *   k_inter_gate : optional (set_option "overlap_inter"): one warp in front of a band of k_inter
@@ -26,28 +26,31 @@
 
 namespace vp9 {
 
-__global__ void k_cellmap(const Vp9CudaInterBlock *__restrict__ blk, uint32_t n, int32_t *cellmap,
-                          int cols, int rows, int *mv_reach)
+__global__ void k_cellmap(const __grid_constant__ FrameDesc f)
 {
-    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    /* blockIdx.y = producer lane; its records sit at lane_blk_base[lane] */
+    const int lane = blockIdx.y;
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x, n = f.lane_blk_cnt[lane];
+    const uint32_t i = f.lane_blk_base[lane] + k;
+    const Vp9CudaInterBlock *__restrict__ blk = f.blk;
     int reach = 0;
-    if (i < n) {
+    if (k < n) {
         /* how far below its own position any prediction of this frame may read (vertical MV, 1/8 pel) */
         const int nref = blk[i].comp ? 2 : 1, nsub = blk[i].bs > 9 ? 4 : 1;
-        for (int k = 0; k < nsub; k++)
+        for (int q = 0; q < nsub; q++)
             for (int r = 0; r < nref; r++)
-                reach = max(reach, (int)blk[i].mv[k][r][1]);
+                reach = max(reach, (int)blk[i].mv[q][r][1]);
     }
     reach = __reduce_max_sync(0xffffffffu, reach);
     if ((threadIdx.x & 31) == 0 && reach > 0)
-        atomicMax(mv_reach, reach);
-    if (i >= n)
+        atomicMax(f.mv_reach, reach);
+    if (k >= n)
         return;
     int col = blk[i].col, row = blk[i].row, bs = blk[i].bs;
-    int w = min(bs_w8(bs), cols - col), h = min(bs_h8(bs), rows - row);
+    int w = min(bs_w8(bs), f.cols - col), h = min(bs_h8(bs), f.rows - row);
     for (int y = 0; y < h; y++)
         for (int x = 0; x < w; x++)
-            cellmap[(row + y) * cols + col + x] = (int32_t)i;
+            f.cellmap[(row + y) * f.cols + col + x] = (int32_t)i;
 }
 
 /* horizontal stage for one sample; CLAMP = false when the caller knows every tap is inside the plane */

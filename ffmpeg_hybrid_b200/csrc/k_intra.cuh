@@ -199,7 +199,7 @@ __global__ void __launch_bounds__(128) k_intra_prep(const __grid_constant__ Fram
         o.flags = (v >> 16 & 3) | (v >> 19 & 1) << 2;
         o.pad = 0;
         o.eob = r.eob;
-        o.run = 0;
+        o.ncoef = r.ncoef;
         o.coef_off = r.coef_off;
         f.irec[g0 + k] = o;
     }
@@ -281,9 +281,11 @@ template <bool HBD>
 __global__ void __launch_bounds__(IRES_WARPS * 32) k_intra_res(const __grid_constant__ FrameDesc f)
 {
     typedef typename ItxTypes<HBD>::C C;
+    typedef typename ItxTypes<HBD>::E E;
+    __shared__ __align__(16) C dense_s[IRES_WARPS][32 * 32];
     __shared__ C tmp_s[IRES_WARPS][32 * 33];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    C *tmp = tmp_s[warp];
+    C *tmp = tmp_s[warp], *dense = dense_s[warp];
     /* one warp per (superblock, record); superblock = blockIdx.y keeps the residual tile address cheap */
     const int sb = blockIdx.x;
     const IntraSb si = f.isb[sb];
@@ -296,12 +298,12 @@ __global__ void __launch_bounds__(IRES_WARPS * 32) k_intra_res(const __grid_cons
             continue;
         const int S = r.plane ? 32 : 64;
         ResBlk blk = { tile + res_plane_off(r.plane) + r.ly * 4 * S + r.lx * 4, S };
-        const C *coef = (const C *)f.coef + r.coef_off;
+        const E *ent = (const E *)f.coef + r.coef_off;
         switch (r.tx) {
-        case 0: if (lane < 4)  itx_block<HBD, 4, ResBlk, true>(coef, tmp, lane, r.txtp, r.eob, f.bpp, blk, 0xfu); break;
-        case 1: if (lane < 8)  itx_block<HBD, 8, ResBlk, true>(coef, tmp, lane, r.txtp, r.eob, f.bpp, blk, 0xffu); break;
-        case 2: if (lane < 16) itx_block<HBD, 16, ResBlk, true>(coef, tmp, lane, r.txtp, r.eob, f.bpp, blk, 0xffffu); break;
-        default: itx_block<HBD, 32, ResBlk, true>(coef, tmp, lane, r.txtp, r.eob, f.bpp, blk, 0xffffffffu); break;
+        case 0: if (lane < 4)  itx_entries<HBD, 4, ResBlk, true>(ent, r.ncoef, dense, tmp, lane, r.txtp, r.eob, f.bpp, blk, 0xfu); break;
+        case 1: if (lane < 8)  itx_entries<HBD, 8, ResBlk, true>(ent, r.ncoef, dense, tmp, lane, r.txtp, r.eob, f.bpp, blk, 0xffu); break;
+        case 2: if (lane < 16) itx_entries<HBD, 16, ResBlk, true>(ent, r.ncoef, dense, tmp, lane, r.txtp, r.eob, f.bpp, blk, 0xffffu); break;
+        default: itx_entries<HBD, 32, ResBlk, true>(ent, r.ncoef, dense, tmp, lane, r.txtp, r.eob, f.bpp, blk, 0xffffffffu); break;
         }
         __syncwarp();
     }

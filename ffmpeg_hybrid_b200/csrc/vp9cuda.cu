@@ -22,7 +22,11 @@
 #include <unistd.h>
 
 #include <algorithm>
+#include <atomic>
+#include <chrono>
+#include <condition_variable>
 #include <mutex>
+#include <set>
 #include <vector>
 
 #include "vp9cuda.h"
@@ -80,11 +84,20 @@ struct Surface {
     bool has_d2h = false;
 };
 
-/* growable device buffer */
+/* per-superblock record capacities of a lane ring (include/vp9cuda.h, Vp9CudaLaneRing) */
+enum { CAP_BLK = 64, CAP_TX = 384, CAP_ITX = 384, CAP_COEF = 6144 };
+inline int coef_entry_bytes(int bpp) { return bpp > 8 ? (int)sizeof(Vp9CudaCoef32) : (int)sizeof(Vp9CudaCoef16); }
+inline size_t ring_bytes_per_sb(int ceb)
+{
+    return (size_t)CAP_BLK * sizeof(Vp9CudaInterBlock) + (size_t)CAP_TX * sizeof(Vp9CudaTx) +
+           (size_t)CAP_ITX * sizeof(Vp9CudaIntraTx) + (size_t)CAP_COEF * ceb;     /* a multiple of 64 */
+}
+
+/* device buffer that only ever grows; every (re)allocation is counted (vp9cuda_get_stat "allocs") */
 struct DBuf {
     void *p = nullptr;
     size_t cap = 0;
-    int reserve(size_t n)
+    int reserve(size_t n, std::atomic<uint64_t> &allocs)
     {
         if (n <= cap)
             return 0;
@@ -92,22 +105,23 @@ struct DBuf {
             cudaFree(p);
         p = nullptr;
         cap = 0;
-        size_t want = n + n / 4 + 256;
+        size_t want = n + 256;
         if (cudaMalloc(&p, want) != cudaSuccess) {
             fprintf(stderr, "vp9cuda: cudaMalloc(%zu) failed\n", want);
             return -ENOMEM;
         }
+        allocs++;
         cap = want;
         return 0;
     }
     void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
 };
 
-/* growable pinned host buffer */
+/* pinned host buffer, same rules */
 struct HBuf {
     void *p = nullptr;
     size_t cap = 0;
-    int reserve(size_t n)
+    int reserve(size_t n, std::atomic<uint64_t> &allocs)
     {
         if (n <= cap)
             return 0;
@@ -117,19 +131,26 @@ struct HBuf {
         cap = 0;
         if (cudaMallocHost(&p, n) != cudaSuccess)
             return -ENOMEM;
+        allocs++;
         cap = n;
         return 0;
     }
     void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
 };
 
-/* device-resident records + scratch of one frame */
+/* device-resident records + scratch of one frame.  Every record type is one array; lane l owns
+ * the elements from lane_*_base[l] on (ring path: capacity-based, so that submit_tile can copy a
+ * lane's new records to a fixed place while other lanes are still being produced; one-shot /
+ * staged path: lanes packed back to back). */
 struct DevRecords {
-    DBuf blk, tx[4], itx, coef, sb_index, lf;
+    DBuf blk, tx, itx, coef, sb_index, lf;
     DBuf cellmap, isb, irec, ires, itab, iprogress, lfops, progress, misc;
-    uint32_t lane_itx_base[VP9CUDA_MAX_LANES] = { 0 };
+    uint32_t lane_blk_base[VP9CUDA_MAX_LANES] = { 0 }, lane_tx_base[VP9CUDA_MAX_LANES] = { 0 },
+             lane_itx_base[VP9CUDA_MAX_LANES] = { 0 };
+    uint32_t lane_blk_cnt[VP9CUDA_MAX_LANES] = { 0 }, lane_tx_cnt[VP9CUDA_MAX_LANES] = { 0 };
     Vp9CudaFrameHeader hdr;
-    uint32_t n_blk = 0, n_tx[4] = { 0, 0, 0, 0 }, n_itx = 0;
+    uint32_t n_blk = 0, n_tx = 0, n_itx = 0, max_blk = 0, max_tx = 0;
+    uint64_t n_coef = 0;
     bool used = false;
     cudaEvent_t uploaded = nullptr;    /* H2D of the records finished (upload stream) */
     cudaEvent_t dev_free = nullptr;    /* the kernels reading these records finished (compute stream) */
@@ -137,6 +158,40 @@ struct DevRecords {
     cudaEvent_t cellmapped = nullptr;  /* the cell map is built (prep stream) */
     cudaEvent_t inter_done = nullptr;  /* inter prediction finished (inter stream) */
     bool wait_upload = false, has_free = false;
+    int make_events()
+    {
+        if (uploaded)
+            return 0;
+        if (cudaEventCreateWithFlags(&uploaded, cudaEventDisableTiming) != cudaSuccess ||
+            cudaEventCreateWithFlags(&dev_free, cudaEventDisableTiming) != cudaSuccess ||
+            cudaEventCreateWithFlags(&prepped, cudaEventDisableTiming) != cudaSuccess ||
+            cudaEventCreateWithFlags(&cellmapped, cudaEventDisableTiming) != cudaSuccess ||
+            cudaEventCreateWithFlags(&inter_done, cudaEventDisableTiming) != cudaSuccess)
+            return -EIO;
+        return 0;
+    }
+    /* room for a frame of n_sb superblocks (cols x rows 8x8 cells) with the given record counts */
+    int reserve(std::atomic<uint64_t> &allocs, uint32_t n_sb, int cols, int rows, int sb_rows, uint64_t cap_blk,
+                uint64_t cap_tx, uint64_t cap_itx, uint64_t cap_coef, int ceb, bool intra)
+    {
+        int r = 0;
+        r |= blk.reserve(cap_blk * sizeof(Vp9CudaInterBlock), allocs);
+        r |= tx.reserve(cap_tx * sizeof(Vp9CudaTx), allocs);
+        r |= itx.reserve(cap_itx * sizeof(Vp9CudaIntraTx), allocs);
+        r |= coef.reserve(cap_coef * ceb, allocs);
+        r |= sb_index.reserve((size_t)n_sb * sizeof(Vp9CudaSbIndex), allocs);
+        r |= lf.reserve((size_t)n_sb * sizeof(Vp9CudaLoopFilterSb), allocs);
+        r |= cellmap.reserve((size_t)cols * rows * 4, allocs);
+        r |= isb.reserve((size_t)n_sb * sizeof(IntraSb), allocs);
+        r |= irec.reserve(cap_itx * sizeof(IntraRec), allocs);
+        if (intra) r |= ires.reserve((size_t)n_sb * INTRA_SB_RES * 2, allocs);
+        if (intra) r |= itab.reserve((size_t)n_sb * INTRA_SB_TAB * 2, allocs);
+        r |= iprogress.reserve((size_t)2 * sb_rows * 4, allocs);
+        r |= lfops.reserve((size_t)n_sb * 3 * sizeof(LfSched), allocs);
+        r |= progress.reserve((size_t)6 * sb_rows * 4, allocs);
+        r |= misc.reserve(64, allocs);
+        return r ? -ENOMEM : make_events();
+    }
     void release()
     {
         if (uploaded) cudaEventDestroy(uploaded);
@@ -145,24 +200,26 @@ struct DevRecords {
         if (cellmapped) cudaEventDestroy(cellmapped);
         if (inter_done) cudaEventDestroy(inter_done);
         uploaded = dev_free = prepped = cellmapped = inter_done = nullptr;
-        blk.release(); itx.release(); coef.release(); sb_index.release(); lf.release();
-        for (auto &t : tx) t.release();
+        blk.release(); tx.release(); itx.release(); coef.release(); sb_index.release(); lf.release();
         misc.release(); cellmap.release(); isb.release(); irec.release(); ires.release(); itab.release(); iprogress.release(); lfops.release();
         progress.release();
     }
 };
 
-/* pinned rings of one frame in flight (begin_frame / tile_ring / submit_tile / finish_frame) */
+/* pinned rings of one frame in flight (begin_frame / tile_ring / submit_tile / finish_frame):
+ * one slab, lane l's part starts sb_prefix[l] superblocks in */
 struct RingSet {
-    HBuf mem[VP9CUDA_MAX_LANES];           /* one slab per lane */
+    HBuf mem, sb_index, lf;
     Vp9CudaLaneRing ring[VP9CUDA_MAX_LANES];
-    Vp9CudaLaneCounts counts[VP9CUDA_MAX_LANES];
-    HBuf sb_index, lf;
+    Vp9CudaLaneCounts counts[VP9CUDA_MAX_LANES];   /* submitted so far (cumulative) */
+    Vp9CudaLaneCounts sent[VP9CUDA_MAX_LANES];     /* host->device copy enqueued so far */
     Vp9CudaFrameHeader hdr;
     uint32_t frame_id = 0;
+    uint64_t seq = 0;                      /* position in decode order */
     uint32_t n_sb = 0;
     cudaEvent_t consumed = nullptr;        /* H2D of this set finished */
     bool busy = false;
+    std::mutex mu;                         /* counts / sent */
     DevRecords dev;
 };
 
@@ -201,10 +258,19 @@ struct Vp9CudaCtx {
     Surface *last = nullptr;               /* most recently reconstructed frame */
     std::vector<RingSet *> rings;
     std::vector<DevRecords *> staged;
+    std::vector<DevRecords *> oneshot;     /* landing zones of vp9cuda_decode_frame, round robin */
+    size_t oneshot_rr = 0;
     uint32_t next_frame_id = 1;
-    uint64_t next_ticket = 1;
+    std::atomic<uint64_t> next_ticket{1};
     std::vector<cudaEvent_t> ticket_ev;    /* ring of events, ticket % size */
-    std::mutex mu;
+    std::mutex mu;                         /* ring-set bookkeeping and the decode order */
+    std::mutex gpu_mu;                     /* surface pool, reference slots, kernel sequencing */
+    std::condition_variable cv;            /* a ring set became free / it is the next frame's turn */
+    uint64_t next_begin_seq = 0;           /* decode order: handed out by begin_frame ... */
+    uint64_t next_finish_seq = 0;          /* ... and honoured by finish_frame */
+    std::set<uint64_t> aborted;            /* frames given back before it was their turn */
+    int max_w = 0, max_h = 0, max_bpp = 0;
+    std::atomic<uint64_t> n_allocs{0}, n_frames{0}, n_aborted{0}, h2d_bytes{0}, early_h2d_bytes{0}, d2h_bytes{0};
     KStat ks[KS_N];
     bool timing = false;
     /* per-stage timing without host syncs: event pairs from a pool, resolved in kernel_stats() */
@@ -263,6 +329,7 @@ static Surface *surface_get(Vp9CudaCtx *c, int w, int h, int bpp)
             delete s;
             return nullptr;
         }
+        c->n_allocs++;
         cudaMemsetAsync(s->pl[p], 0, n, c->stream);
     }
     cudaEventCreateWithFlags(&s->ready, cudaEventDisableTiming);
@@ -343,97 +410,135 @@ static void kstat_resolve(Vp9CudaCtx *c)
 }
 
 /* ------------------------------------------------------------------------------------------
- * record upload: host (pinned or pageable) -> DevRecords, lanes concatenated per record type,
- * coefficients placed at their lane's coef_base
+ * record upload: host (pinned or pageable) -> DevRecords
  * ---------------------------------------------------------------------------------------- */
+static int check_header(const Vp9CudaFrameHeader *h, uint32_t *n_sb_out)
+{
+    if (!h->w || !h->h || h->w > 64 * INTRA_MAX_SB_COLS || h->h > 65535 ||
+        (h->bpp != 8 && h->bpp != 10 && h->bpp != 12) || h->ss_h != 1 || h->ss_v != 1 ||
+        h->n_lanes < 1 || h->n_lanes > VP9CUDA_MAX_LANES)
+        return -EINVAL;
+    const uint32_t n_sb = ((h->w + 63) >> 6) * ((h->h + 63) >> 6);
+    uint64_t sum = 0;
+    for (int l = 0; l < h->n_lanes; l++)
+        sum += h->lane_sbs[l];
+    if (sum > n_sb)
+        return -EINVAL;
+    *n_sb_out = n_sb;
+    return 0;
+}
+
+/* copy records [from, to) of one lane from its ring to the lane's place in the device arrays */
+static int copy_lane_range(Vp9CudaCtx *c, DevRecords &d, const Vp9CudaLaneRing &g, int lane,
+                           const Vp9CudaLaneCounts &from, const Vp9CudaLaneCounts &to, int ceb, uint64_t *bytes)
+{
+    if (to.blk > from.blk) {
+        const size_t n = (size_t)(to.blk - from.blk) * sizeof(Vp9CudaInterBlock);
+        CK(cudaMemcpyAsync((char *)d.blk.p + ((size_t)d.lane_blk_base[lane] + from.blk) * sizeof(Vp9CudaInterBlock),
+                           g.blk + from.blk, n, cudaMemcpyHostToDevice, c->s_up));
+        *bytes += n;
+    }
+    if (to.tx > from.tx) {
+        const size_t n = (size_t)(to.tx - from.tx) * sizeof(Vp9CudaTx);
+        CK(cudaMemcpyAsync((char *)d.tx.p + ((size_t)d.lane_tx_base[lane] + from.tx) * sizeof(Vp9CudaTx),
+                           g.tx + from.tx, n, cudaMemcpyHostToDevice, c->s_up));
+        *bytes += n;
+    }
+    if (to.itx > from.itx) {
+        const size_t n = (size_t)(to.itx - from.itx) * sizeof(Vp9CudaIntraTx);
+        CK(cudaMemcpyAsync((char *)d.itx.p + ((size_t)d.lane_itx_base[lane] + from.itx) * sizeof(Vp9CudaIntraTx),
+                           g.itx + from.itx, n, cudaMemcpyHostToDevice, c->s_up));
+        *bytes += n;
+    }
+    if (to.coef > from.coef) {
+        const size_t n = (size_t)(to.coef - from.coef) * ceb;
+        CK(cudaMemcpyAsync((char *)d.coef.p + ((size_t)g.coef_base + from.coef) * ceb,
+                           (const char *)g.coef + (size_t)from.coef * ceb, n, cudaMemcpyHostToDevice, c->s_up));
+        *bytes += n;
+    }
+    return 0;
+}
+
+/* the per-superblock arrays + bookkeeping once every lane's records are on their way */
+static int upload_frame_tail(Vp9CudaCtx *c, DevRecords &d, const Vp9CudaFrameHeader *hdr, uint32_t n_sb,
+                             const Vp9CudaLaneCounts *counts, const Vp9CudaSbIndex *sb_index,
+                             const Vp9CudaLoopFilterSb *lf, uint64_t *bytes)
+{
+    uint64_t n_blk = 0, n_tx = 0, n_itx = 0, n_coef = 0;
+    uint32_t max_blk = 0, max_tx = 0;
+    for (int l = 0; l < hdr->n_lanes; l++) {
+        d.lane_blk_cnt[l] = counts[l].blk;
+        d.lane_tx_cnt[l] = counts[l].tx;
+        n_blk += counts[l].blk; n_tx += counts[l].tx; n_itx += counts[l].itx; n_coef += counts[l].coef;
+        max_blk = std::max(max_blk, counts[l].blk);
+        max_tx = std::max(max_tx, counts[l].tx);
+    }
+    if (n_itx || n_tx) {
+        CK(cudaMemcpyAsync(d.sb_index.p, sb_index, (size_t)n_sb * sizeof(Vp9CudaSbIndex), cudaMemcpyHostToDevice, c->s_up));
+        *bytes += (uint64_t)n_sb * sizeof(Vp9CudaSbIndex);
+    }
+    if (hdr->lf_level) {
+        CK(cudaMemcpyAsync(d.lf.p, lf, (size_t)n_sb * sizeof(Vp9CudaLoopFilterSb), cudaMemcpyHostToDevice, c->s_up));
+        *bytes += (uint64_t)n_sb * sizeof(Vp9CudaLoopFilterSb);
+    }
+    CK(cudaEventRecord(d.uploaded, c->s_up));
+    d.wait_upload = true;
+    d.hdr = *hdr;
+    d.n_blk = (uint32_t)n_blk; d.n_tx = (uint32_t)n_tx; d.n_itx = (uint32_t)n_itx; d.n_coef = n_coef;
+    d.max_blk = max_blk; d.max_tx = max_tx;
+    d.used = true;
+    return 0;
+}
+
+/* one-shot / staged path: all records of a frame from caller memory, lanes packed back to back */
 static int upload_records(Vp9CudaCtx *c, DevRecords &d, const Vp9CudaFrameHeader *hdr,
                           const Vp9CudaFrameRecords *recs)
 {
-    const int cb = hdr->bpp > 8 ? 4 : 2;
+    uint32_t n_sb = 0;
+    int r = check_header(hdr, &n_sb);
+    if (r < 0)
+        return r;
+    const int ceb = coef_entry_bytes(hdr->bpp);
     const int nl = hdr->n_lanes;
-    if (nl < 1 || nl > VP9CUDA_MAX_LANES)
-        return -EINVAL;
-    const uint32_t n_sb = ((hdr->w + 63) >> 6) * ((hdr->h + 63) >> 6);
     const int cols = (hdr->w + 7) >> 3, rows = (hdr->h + 7) >> 3, sb_rows = (hdr->h + 63) >> 6;
-    uint64_t n_blk = 0, n_tx[4] = { 0, 0, 0, 0 }, n_itx = 0, coef_extent = 0;
+    uint64_t n_blk = 0, n_tx = 0, n_itx = 0, coef_extent = 0;
     for (int l = 0; l < nl; l++) {
         const Vp9CudaLaneCounts &n = recs->counts[l];
-        n_blk += n.blk; n_itx += n.itx;
-        for (int t = 0; t < 4; t++) n_tx[t] += n.tx[t];
+        d.lane_blk_base[l] = (uint32_t)n_blk; d.lane_tx_base[l] = (uint32_t)n_tx; d.lane_itx_base[l] = (uint32_t)n_itx;
+        n_blk += n.blk; n_tx += n.tx; n_itx += n.itx;
         uint64_t e = (uint64_t)recs->lanes[l].coef_base + n.coef;
         if (n.coef && e > coef_extent) coef_extent = e;
     }
-    if (coef_extent > 0xffffffffull)
+    if (coef_extent > 0xffffffffull || n_blk > 0x7fffffffull || n_tx > 0x7fffffffull || n_itx > 0x7fffffffull)
         return -EINVAL;
-    int r = 0;
-    r |= d.blk.reserve(n_blk * sizeof(Vp9CudaInterBlock));
-    for (int t = 0; t < 4; t++) r |= d.tx[t].reserve(n_tx[t] * sizeof(Vp9CudaTx));
-    r |= d.itx.reserve(n_itx * sizeof(Vp9CudaIntraTx));
-    r |= d.coef.reserve(coef_extent * cb);
-    r |= d.sb_index.reserve(n_sb * sizeof(Vp9CudaSbIndex));
-    r |= d.lf.reserve(n_sb * sizeof(Vp9CudaLoopFilterSb));
-    r |= d.cellmap.reserve((size_t)cols * rows * 4);
-    r |= d.isb.reserve((size_t)n_sb * sizeof(IntraSb));
-    r |= d.irec.reserve(n_itx * sizeof(IntraRec));
-    if (n_itx) r |= d.ires.reserve((size_t)n_sb * INTRA_SB_RES * 2);
-    if (n_itx) r |= d.itab.reserve((size_t)n_sb * INTRA_SB_TAB * 2);
-    r |= d.iprogress.reserve((size_t)2 * sb_rows * 4);
-    r |= d.lfops.reserve((size_t)n_sb * 3 * sizeof(LfSched));
-    r |= d.progress.reserve((size_t)6 * sb_rows * 4);
-    r |= d.misc.reserve(64);
-    if (r)
-        return -ENOMEM;
-    if (!d.uploaded) {
-        CK(cudaEventCreateWithFlags(&d.uploaded, cudaEventDisableTiming));
-        CK(cudaEventCreateWithFlags(&d.dev_free, cudaEventDisableTiming));
-        CK(cudaEventCreateWithFlags(&d.prepped, cudaEventDisableTiming));
-        CK(cudaEventCreateWithFlags(&d.cellmapped, cudaEventDisableTiming));
-        CK(cudaEventCreateWithFlags(&d.inter_done, cudaEventDisableTiming));
-    }
+    r = d.reserve(c->n_allocs, n_sb, cols, rows, sb_rows, n_blk, n_tx, n_itx, coef_extent, ceb, n_itx != 0);
+    if (r < 0)
+        return r;
     if (d.has_free) {                       /* the previous user of this landing zone must be done */
         CK(cudaStreamWaitEvent(c->s_up, d.dev_free, 0));
         d.has_free = false;                 /* the prep stream follows the upload, hence dev_free */
     }
     kstat_begin(c, c->s_up);
-    uint64_t o_blk = 0, o_tx[4] = { 0, 0, 0, 0 }, o_itx = 0, bytes = 0;
-    for (int l = 0; l < nl; l++) {
-        const Vp9CudaLaneCounts &n = recs->counts[l];
-        const Vp9CudaLaneRing &g = recs->lanes[l];
-        if (n.blk)
-            CK(cudaMemcpyAsync((char *)d.blk.p + o_blk * sizeof(Vp9CudaInterBlock), g.blk,
-                               n.blk * sizeof(Vp9CudaInterBlock), cudaMemcpyHostToDevice, c->s_up));
-        for (int t = 0; t < 4; t++)
-            if (n.tx[t])
-                CK(cudaMemcpyAsync((char *)d.tx[t].p + o_tx[t] * sizeof(Vp9CudaTx), g.tx[t],
-                                   n.tx[t] * sizeof(Vp9CudaTx), cudaMemcpyHostToDevice, c->s_up));
-        if (n.itx)
-            CK(cudaMemcpyAsync((char *)d.itx.p + o_itx * sizeof(Vp9CudaIntraTx), g.itx,
-                               n.itx * sizeof(Vp9CudaIntraTx), cudaMemcpyHostToDevice, c->s_up));
-        if (n.coef)
-            CK(cudaMemcpyAsync((char *)d.coef.p + (size_t)g.coef_base * cb, g.coef, (size_t)n.coef * cb,
-                               cudaMemcpyHostToDevice, c->s_up));
-        d.lane_itx_base[l] = (uint32_t)o_itx;
-        bytes += n.blk * sizeof(Vp9CudaInterBlock) + n.itx * sizeof(Vp9CudaIntraTx) + (uint64_t)n.coef * cb;
-        for (int t = 0; t < 4; t++) bytes += n.tx[t] * sizeof(Vp9CudaTx);
-        o_blk += n.blk; o_itx += n.itx;
-        for (int t = 0; t < 4; t++) o_tx[t] += n.tx[t];
-    }
-    if (n_itx) {
-        CK(cudaMemcpyAsync(d.sb_index.p, recs->sb_index, n_sb * sizeof(Vp9CudaSbIndex), cudaMemcpyHostToDevice, c->s_up));
-        bytes += n_sb * sizeof(Vp9CudaSbIndex);
-    }
-    if (hdr->lf_level) {
-        CK(cudaMemcpyAsync(d.lf.p, recs->lf, n_sb * sizeof(Vp9CudaLoopFilterSb), cudaMemcpyHostToDevice, c->s_up));
-        bytes += n_sb * sizeof(Vp9CudaLoopFilterSb);
-    }
+    uint64_t bytes = 0;
+    const Vp9CudaLaneCounts zero = { 0, 0, 0, 0 };
+    for (int l = 0; l < nl; l++)
+        if ((r = copy_lane_range(c, d, recs->lanes[l], l, zero, recs->counts[l], ceb, &bytes)) < 0)
+            return r;
+    r = upload_frame_tail(c, d, hdr, n_sb, recs->counts, recs->sb_index, recs->lf, &bytes);
     kstat_end(c, KS_H2D, 0, bytes, c->s_up);
-    CK(cudaEventRecord(d.uploaded, c->s_up));
-    d.wait_upload = true;
-    d.hdr = *hdr;
-    d.n_blk = (uint32_t)n_blk; d.n_itx = (uint32_t)n_itx;
-    for (int t = 0; t < 4; t++) d.n_tx[t] = (uint32_t)n_tx[t];
-    d.used = true;
-    return 0;
+    c->h2d_bytes += bytes;
+    return r;
+}
+
+/* ring path: size one ring set (pinned slab + device records) for n_sb superblocks */
+static int ringset_reserve(Vp9CudaCtx *c, RingSet *r, uint32_t n_sb, int cols, int rows, int sb_rows, int ceb)
+{
+    if (r->mem.reserve((size_t)n_sb * ring_bytes_per_sb(ceb), c->n_allocs) ||
+        r->sb_index.reserve((size_t)n_sb * sizeof(Vp9CudaSbIndex), c->n_allocs) ||
+        r->lf.reserve((size_t)n_sb * sizeof(Vp9CudaLoopFilterSb), c->n_allocs))
+        return -ENOMEM;
+    return r->dev.reserve(c->n_allocs, n_sb, cols, rows, sb_rows, (uint64_t)n_sb * CAP_BLK, (uint64_t)n_sb * CAP_TX,
+                          (uint64_t)n_sb * CAP_ITX, (uint64_t)n_sb * CAP_COEF, ceb, true);
 }
 
 /* ------------------------------------------------------------------------------------------
@@ -459,13 +564,11 @@ static int launch_frame(Vp9CudaCtx *c, FrameDesc &f, DevRecords &d)
             kstat_begin(c, sp);
             CK(cudaMemsetAsync(f.cellmap, 0xff, (size_t)f.cols * f.rows * 4, sp));
             CK(cudaMemsetAsync(f.mv_reach, 0, 4, sp));
-            k_cellmap<<<(f.n_blk + 255) / 256, 256, 0, sp>>>(f.blk, f.n_blk, f.cellmap, f.cols, f.rows, f.mv_reach);
+            k_cellmap<<<dim3((d.max_blk + 255) / 256, f.n_lanes), 256, 0, sp>>>(f);
             kstat_end(c, KS_CELLMAP, 1, (uint64_t)f.n_blk * sizeof(Vp9CudaInterBlock) + (uint64_t)f.cols * f.rows * 4, sp);
             CK(cudaEventRecord(d.cellmapped, sp));
         }
         if (f.n_itx) {
-            if (f.sb_cols > INTRA_MAX_SB_COLS)
-                return -EINVAL;
             kstat_begin(c, sp);
             k_intra_prep<<<f.sb_cols * f.sb_rows, 128, 0, sp>>>(f);
             k_intra_res<HBD><<<f.sb_cols * f.sb_rows, IRES_WARPS * 32, 0, sp>>>(f);
@@ -505,7 +608,7 @@ static int launch_frame(Vp9CudaCtx *c, FrameDesc &f, DevRecords &d)
             kstat_begin(c, si);
             CK(cudaMemsetAsync(f.cellmap, 0xff, (size_t)f.cols * f.rows * 4, si));
             CK(cudaMemsetAsync(f.mv_reach, 0, 4, si));
-            k_cellmap<<<(f.n_blk + 255) / 256, 256, 0, si>>>(f.blk, f.n_blk, f.cellmap, f.cols, f.rows, f.mv_reach);
+            k_cellmap<<<dim3((d.max_blk + 255) / 256, f.n_lanes), 256, 0, si>>>(f);
             kstat_end(c, KS_CELLMAP, 1, (uint64_t)f.n_blk * sizeof(Vp9CudaInterBlock) + (uint64_t)f.cols * f.rows * 4, si);
         }
         kstat_begin(c, si);
@@ -534,16 +637,12 @@ static int launch_frame(Vp9CudaCtx *c, FrameDesc &f, DevRecords &d)
             CK(cudaEventRecord(c->prev_dev->dev_free, s));
         }
     }
-    kstat_begin(c);
-    uint64_t itx_launches = 0, itx_bytes = 0;
-    if (f.n_tx[0]) { k_itx<P, HBD, 4><<<(f.n_tx[0] + 31) / 32, 128, 0, s>>>(f); itx_launches++; }
-    if (f.n_tx[1]) { k_itx<P, HBD, 8><<<(f.n_tx[1] + 15) / 16, 128, 0, s>>>(f); itx_launches++; }
-    if (f.n_tx[2]) { k_itx<P, HBD, 16><<<(f.n_tx[2] + 7) / 8, 128, 0, s>>>(f); itx_launches++; }
-    if (f.n_tx[3]) { k_itx<P, HBD, 32><<<(f.n_tx[3] + 3) / 4, 128, 0, s>>>(f); itx_launches++; }
-    for (int t = 0; t < 4; t++)
-        itx_bytes += (uint64_t)f.n_tx[t] * (16u << (2 * t)) * ((HBD ? 4 : 2) + 2 * sizeof(P));
-    if (itx_launches)
-        kstat_end(c, KS_ITX, itx_launches, itx_bytes);
+    if (f.n_tx) {
+        kstat_begin(c);
+        k_itx<P, HBD><<<dim3((d.max_tx + 3) / 4, f.n_lanes), 128, 0, s>>>(f);
+        /* bytes: the coefficient entries of the frame (intra blocks included: the stream is shared) */
+        kstat_end(c, KS_ITX, 1, d.n_coef * sizeof(typename ItxTypes<HBD>::E));
+    }
     if (f.n_itx || f.lf_level)
         CK(cudaStreamWaitEvent(s, d.prepped, 0));
     CK(cudaEventRecord(c->pre_wave, s));
@@ -584,6 +683,7 @@ static int copy_out(Vp9CudaCtx *c, Surface *s, uint8_t *const out_planes[3], con
         total += (uint64_t)w * h * bytes;
     }
     kstat_end(c, KS_D2H, 0, total, c->s_down);
+    c->d2h_bytes += total;
     CK(cudaEventRecord(s->d2h_done, c->s_down));
     s->has_d2h = true;
     return 0;
@@ -591,7 +691,7 @@ static int copy_out(Vp9CudaCtx *c, Surface *s, uint8_t *const out_planes[3], con
 
 static int make_ticket(Vp9CudaCtx *c, uint64_t *ticket, cudaStream_t st)
 {
-    uint64_t t = c->next_ticket++;
+    uint64_t t = c->next_ticket.fetch_add(1);
     cudaEvent_t ev = c->ticket_ev[t % c->ticket_ev.size()];
     CK(cudaEventRecord(ev, st));
     if (ticket)
@@ -625,7 +725,8 @@ static int reconstruct(Vp9CudaCtx *c, DevRecords &d, uint8_t *const out_planes[3
                        const ptrdiff_t out_strides[3], uint64_t *ticket)
 {
     const Vp9CudaFrameHeader &h = d.hdr;
-    if (h.ss_h != 1 || h.ss_v != 1 || (h.bpp != 8 && h.bpp != 10 && h.bpp != 12) || !h.w || !h.h)
+    uint32_t n_sb_chk = 0;
+    if (check_header(&h, &n_sb_chk) < 0)
         return -EINVAL;
     Surface *cur = surface_get(c, h.w, h.h, h.bpp);
     if (!cur)
@@ -648,8 +749,13 @@ static int reconstruct(Vp9CudaCtx *c, DevRecords &d, uint8_t *const out_planes[3
     f.sb_cols = (h.w + 63) >> 6; f.sb_rows = (h.h + 63) >> 6;
     f.lossless = h.lossless; f.lf_level = h.lf_level;
     f.blk = (const Vp9CudaInterBlock *)d.blk.p; f.n_blk = d.n_blk;
-    for (int t = 0; t < 4; t++) { f.tx[t] = (const Vp9CudaTx *)d.tx[t].p; f.n_tx[t] = d.n_tx[t]; }
+    f.tx = (const Vp9CudaTx *)d.tx.p; f.n_tx = d.n_tx;
     f.itx = (const Vp9CudaIntraTx *)d.itx.p; f.n_itx = d.n_itx;
+    f.n_lanes = h.n_lanes;
+    memcpy(f.lane_blk_base, d.lane_blk_base, sizeof(f.lane_blk_base));
+    memcpy(f.lane_blk_cnt, d.lane_blk_cnt, sizeof(f.lane_blk_cnt));
+    memcpy(f.lane_tx_base, d.lane_tx_base, sizeof(f.lane_tx_base));
+    memcpy(f.lane_tx_cnt, d.lane_tx_cnt, sizeof(f.lane_tx_cnt));
     f.coef = d.coef.p;
     f.sb_index = (const Vp9CudaSbIndex *)d.sb_index.p;
     f.lf = (const Vp9CudaLoopFilterSb *)d.lf.p;
@@ -695,6 +801,7 @@ static int reconstruct(Vp9CudaCtx *c, DevRecords &d, uint8_t *const out_planes[3
         }
     surface_unref(c->last);
     c->last = cur;             /* keeps the "current" hold until the next frame */
+    c->n_frames++;
     if (out_planes && out_planes[0]) {
         r = copy_out(c, cur, out_planes, out_strides);
         if (r < 0)
@@ -711,27 +818,15 @@ static const char *const ks_names[KS_N] = { "cellmap", "inter_pred", "itxfm_add"
                                             "intra_wavefront", "lf_ops", "loop_filter", "intra_lf_wavefront", "h2d_records",
                                             "d2h_frame" };
 
+#define VP9CUDA_STR2(x) #x
+#define VP9CUDA_STR(x) VP9CUDA_STR2(x)
 extern "C" const char *vp9cuda_version(void)
 {
-    return "vp9cuda 0.1 (sm_100a) abi " "1";
+    return "vp9cuda 0.2 (sm_100a) abi " VP9CUDA_STR(VP9CUDA_ABI_VERSION);
 }
 
-extern "C" int vp9cuda_create(Vp9CudaCtx **out, int device, int max_w, int max_h, int max_bpp,
-                              int frames_in_flight)
+static int create_impl(Vp9CudaCtx *c, int device, int max_w, int max_h, int max_bpp, int frames_in_flight)
 {
-    (void)max_w; (void)max_h; (void)max_bpp;
-    int n = 0;
-    if (!out)
-        return -EINVAL;
-    *out = nullptr;
-    if (cudaGetDeviceCount(&n) != cudaSuccess || n <= 0) {
-        fprintf(stderr, "vp9cuda: no CUDA device; this back end has no CPU path\n");
-        return -ENODEV;
-    }
-    if (device < 0 || device >= n)
-        return -ENODEV;
-    CK(cudaSetDevice(device));
-    Vp9CudaCtx *c = new Vp9CudaCtx;
     c->device = device;
     CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     CK(cudaStreamCreateWithFlags(&c->s_up, cudaStreamNonBlocking));
@@ -748,7 +843,7 @@ extern "C" int vp9cuda_create(Vp9CudaCtx **out, int device, int max_w, int max_h
     CK(cudaFuncSetAttribute(k_wave<uint16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, WaveSmem<uint16_t>::BYTES));
     CK(cudaFuncSetAttribute(k_intra<uint8_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, IntraSmem<uint8_t>::BYTES));
     CK(cudaFuncSetAttribute(k_intra<uint16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, IntraSmem<uint16_t>::BYTES));
-    c->ticket_ev.resize(256);
+    c->ticket_ev.assign(256, nullptr);
     for (auto &e : c->ticket_ev)
         CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     for (auto &e : c->marks)
@@ -770,19 +865,75 @@ extern "C" int vp9cuda_create(Vp9CudaCtx **out, int device, int max_w, int max_h
         c->follow_mask = atoi(e);
     if (const char *e = getenv("VP9CUDA_FUSE_WAVE"))
         c->fuse_wave = atoi(e) != 0;
-    if (frames_in_flight < 1) frames_in_flight = 1;
-    if (frames_in_flight > 16) frames_in_flight = 16;
+    frames_in_flight = std::max(1, std::min(32, frames_in_flight));
+    c->max_w = max_w; c->max_h = max_h; c->max_bpp = max_bpp;
     for (int i = 0; i < frames_in_flight; i++) {
         RingSet *r = new RingSet;
         memset(r->ring, 0, sizeof(r->ring));
         memset(r->counts, 0, sizeof(r->counts));
-        CK(cudaEventCreateWithFlags(&r->consumed, cudaEventDisableTiming));
+        memset(r->sent, 0, sizeof(r->sent));
         c->rings.push_back(r);
+        CK(cudaEventCreateWithFlags(&r->consumed, cudaEventDisableTiming));
+        if (max_w > 0 && max_h > 0) {
+            /* everything a frame of the largest size can need, now, so that the frame path never allocates */
+            const uint32_t n_sb = ((max_w + 63) >> 6) * ((max_h + 63) >> 6);
+            if (ringset_reserve(c, r, n_sb, (max_w + 7) >> 3, (max_h + 7) >> 3, (max_h + 63) >> 6,
+                                coef_entry_bytes(max_bpp)) < 0)
+                return -ENOMEM;
+        }
     }
     for (int k = 0; k < KS_N; k++)
         c->ks[k].name = ks_names[k];
+    return 0;
+}
+
+extern "C" int vp9cuda_create(Vp9CudaCtx **out, int device, int max_w, int max_h, int max_bpp,
+                              int frames_in_flight)
+{
+    int n = 0;
+    if (!out)
+        return -EINVAL;
+    *out = nullptr;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n <= 0) {
+        fprintf(stderr, "vp9cuda: no CUDA device; this back end has no CPU path\n");
+        return -ENODEV;
+    }
+    if (device < 0 || device >= n)
+        return -ENODEV;
+    if (max_w < 0 || max_h < 0 || max_w > 64 * INTRA_MAX_SB_COLS || max_h > 65535 ||
+        (max_w && max_h && max_bpp != 8 && max_bpp != 10 && max_bpp != 12))
+        return -EINVAL;
+    CK(cudaSetDevice(device));
+    Vp9CudaCtx *c = new Vp9CudaCtx;
+    int r = create_impl(c, device, max_w, max_h, max_bpp, frames_in_flight);
+    if (r < 0) {
+        vp9cuda_destroy(c);      /* releases whatever the half-built context holds */
+        return r;
+    }
     *out = c;
     return 0;
+}
+
+static void advance_turn(Vp9CudaCtx *c)      /* c->mu held */
+{
+    c->next_finish_seq++;
+    while (c->aborted.erase(c->next_finish_seq))
+        c->next_finish_seq++;
+    c->cv.notify_all();
+}
+
+/* give a begun frame back: c->mu held */
+static void abort_set(Vp9CudaCtx *c, RingSet *r)
+{
+    /* copies submit_tile may have enqueued still read the slab: begin_frame waits for this event */
+    cudaEventRecord(r->consumed, c->s_up);
+    r->busy = false;
+    c->n_aborted++;
+    if (r->seq == c->next_finish_seq)
+        advance_turn(c);
+    else
+        c->aborted.insert(r->seq);
+    c->cv.notify_all();
 }
 
 extern "C" int vp9cuda_flush(Vp9CudaCtx *c)
@@ -790,6 +941,13 @@ extern "C" int vp9cuda_flush(Vp9CudaCtx *c)
     if (!c)
         return -EINVAL;
     cudaSetDevice(c->device);
+    {
+        std::lock_guard<std::mutex> lk(c->mu);
+        for (RingSet *r : c->rings)
+            if (r->busy)
+                abort_set(c, r);
+    }
+    std::lock_guard<std::mutex> gk(c->gpu_mu);
     sync_all(c);
     for (int i = 0; i < 8; i++) {
         surface_unref(c->ref[i]);
@@ -799,8 +957,6 @@ extern "C" int vp9cuda_flush(Vp9CudaCtx *c)
     c->last = nullptr;
     c->prev_dev = nullptr;
     c->prev_surf = nullptr;
-    for (RingSet *r : c->rings)
-        r->busy = false;
     return 0;
 }
 
@@ -809,33 +965,36 @@ extern "C" void vp9cuda_destroy(Vp9CudaCtx *c)
     if (!c)
         return;
     cudaSetDevice(c->device);
-    sync_all(c);
+    if (c->stream)
+        sync_all(c);
     for (Surface *s : c->pool) {
         for (int p = 0; p < 3; p++) cudaFree(s->pl[p]);
         cudaEventDestroy(s->ready); cudaEventDestroy(s->d2h_done);
         delete s;
     }
     for (RingSet *r : c->rings) {
-        for (auto &m : r->mem) m.release();
+        r->mem.release();
         r->sb_index.release(); r->lf.release();
         r->dev.release();
-        cudaEventDestroy(r->consumed);
+        if (r->consumed) cudaEventDestroy(r->consumed);
         delete r;
     }
     for (DevRecords *d : c->staged)
         if (d) { d->release(); delete d; }
-    for (auto &e : c->ticket_ev) cudaEventDestroy(e);
-    for (auto &e : c->marks) cudaEventDestroy(e);
-    for (auto &e : c->join_ev) cudaEventDestroy(e);
+    for (DevRecords *d : c->oneshot)
+        if (d) { d->release(); delete d; }
+    for (auto &e : c->ticket_ev) if (e) cudaEventDestroy(e);
+    for (auto &e : c->marks) if (e) cudaEventDestroy(e);
+    for (auto &e : c->join_ev) if (e) cudaEventDestroy(e);
     for (auto &e : c->tpool) cudaEventDestroy(e);
     c->sum_buf.release();
     c->phase_clk.release();
-    cudaStreamDestroy(c->stream);
-    cudaStreamDestroy(c->s_up);
-    cudaStreamDestroy(c->s_down);
-    cudaStreamDestroy(c->s_prep);
-    cudaStreamDestroy(c->s_inter);
-    cudaEventDestroy(c->pre_wave);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    if (c->s_up) cudaStreamDestroy(c->s_up);
+    if (c->s_down) cudaStreamDestroy(c->s_down);
+    if (c->s_prep) cudaStreamDestroy(c->s_prep);
+    if (c->s_inter) cudaStreamDestroy(c->s_inter);
+    if (c->pre_wave) cudaEventDestroy(c->pre_wave);
     delete c;
 }
 
@@ -863,58 +1022,64 @@ static RingSet *ring_of(Vp9CudaCtx *c, uint32_t frame_id)
 
 extern "C" int vp9cuda_begin_frame(Vp9CudaCtx *c, const Vp9CudaFrameHeader *hdr, Vp9CudaFrameRing *ring)
 {
-    if (!c || !hdr || !ring || hdr->n_lanes < 1 || hdr->n_lanes > VP9CUDA_MAX_LANES)
+    uint32_t n_sb = 0;
+    if (!c || !hdr || !ring || check_header(hdr, &n_sb) < 0)
         return -EINVAL;
     cudaSetDevice(c->device);
-    std::lock_guard<std::mutex> lk(c->mu);
+    std::unique_lock<std::mutex> lk(c->mu);
     /* round robin, so that consecutive frames land in different device scratch and the next
      * frame's upload / pre-passes / inter prediction can run beside this frame's wavefronts */
     RingSet *r = nullptr;
-    for (size_t i = 0; i < c->rings.size(); i++) {
-        RingSet *q = c->rings[(c->ring_rr + i) % c->rings.size()];
-        if (!q->busy) { r = q; c->ring_rr = (c->ring_rr + i + 1) % c->rings.size(); break; }
-    }
-    if (!r)
-        return -EBUSY;      /* caller must finish/wait a frame first */
-    /* the previous user's H2D must be over before the producer scribbles on the pinned slab */
-    CK(cudaEventSynchronize(r->consumed));
-    const int cb = hdr->bpp > 8 ? 4 : 2;
-    const uint32_t n_sb = ((hdr->w + 63) >> 6) * ((hdr->h + 63) >> 6);
-    uint32_t coef_base = 0;
-    for (int l = 0; l < hdr->n_lanes; l++) {
-        const size_t sbs = hdr->lane_sbs[l] ? hdr->lane_sbs[l] : 1;
-        Vp9CudaLaneRing &g = r->ring[l];
-        g.blk_cap = (uint32_t)(sbs * 64);
-        g.tx_cap[0] = (uint32_t)(sbs * 384); g.tx_cap[1] = (uint32_t)(sbs * 96);
-        g.tx_cap[2] = (uint32_t)(sbs * 24);  g.tx_cap[3] = (uint32_t)(sbs * 6);
-        g.itx_cap = (uint32_t)(sbs * 384);
-        g.coef_cap = (uint32_t)(sbs * 6144);
-        size_t off = 0, o_blk, o_tx[4], o_itx, o_coef;
-        o_blk = off;  off += (size_t)g.blk_cap * sizeof(Vp9CudaInterBlock);
-        for (int t = 0; t < 4; t++) { o_tx[t] = off; off += (size_t)g.tx_cap[t] * sizeof(Vp9CudaTx); }
-        o_itx = off;  off += (size_t)g.itx_cap * sizeof(Vp9CudaIntraTx);
-        off = (off + 63) & ~(size_t)63;
-        o_coef = off; off += (size_t)g.coef_cap * cb;
-        if (r->mem[l].reserve(off))
-            return -ENOMEM;
-        char *base = (char *)r->mem[l].p;
-        g.blk = (Vp9CudaInterBlock *)(base + o_blk);
-        for (int t = 0; t < 4; t++) g.tx[t] = (Vp9CudaTx *)(base + o_tx[t]);
-        g.itx = (Vp9CudaIntraTx *)(base + o_itx);
-        g.coef = base + o_coef;
-        g.coef_base = coef_base;
-        g.reserved = 0;
-        coef_base += g.coef_cap;
-        memset(&r->counts[l], 0, sizeof(r->counts[l]));
-    }
-    if (r->sb_index.reserve(n_sb * sizeof(Vp9CudaSbIndex)) || r->lf.reserve(n_sb * sizeof(Vp9CudaLoopFilterSb)))
-        return -ENOMEM;
-    memset(r->sb_index.p, 0, n_sb * sizeof(Vp9CudaSbIndex));
-    memset(r->lf.p, 0, n_sb * sizeof(Vp9CudaLoopFilterSb));
+    auto pick = [&]() {
+        for (size_t i = 0; i < c->rings.size(); i++) {
+            RingSet *q = c->rings[(c->ring_rr + i) % c->rings.size()];
+            if (!q->busy) { r = q; c->ring_rr = (c->ring_rr + i + 1) % c->rings.size(); return true; }
+        }
+        return false;
+    };
+    /* all sets in use: another thread's finish_frame / abort_frame frees one (frame threading);
+     * a caller that never finishes its frames gets -EBUSY instead of a hang */
+    if (!c->cv.wait_for(lk, std::chrono::seconds(20), pick))
+        return -EBUSY;
+    r->busy = true;
+    r->frame_id = c->next_frame_id++;
+    if (!c->next_frame_id) c->next_frame_id = 1;
+    r->seq = c->next_begin_seq++;
     r->hdr = *hdr;
     r->n_sb = n_sb;
-    r->frame_id = c->next_frame_id++;
-    r->busy = true;
+    auto fail = [&](int e) { abort_set(c, r); return e; };
+    /* the previous user's H2D must be over before the producer scribbles on the pinned slab */
+    if (cudaEventSynchronize(r->consumed) != cudaSuccess)
+        return fail(-EIO);
+    const int ceb = coef_entry_bytes(hdr->bpp);
+    const int cols = (hdr->w + 7) >> 3, rows = (hdr->h + 7) >> 3, sb_rows = (hdr->h + 63) >> 6;
+    if (ringset_reserve(c, r, n_sb, cols, rows, sb_rows, ceb) < 0)
+        return fail(-ENOMEM);
+    DevRecords &d = r->dev;
+    if (d.has_free) {                       /* the kernels of this landing zone's previous frame */
+        if (cudaStreamWaitEvent(c->s_up, d.dev_free, 0) != cudaSuccess)
+            return fail(-EIO);
+        d.has_free = false;
+    }
+    uint32_t sb0 = 0;
+    for (int l = 0; l < hdr->n_lanes; l++) {
+        const uint32_t sbs = hdr->lane_sbs[l];
+        Vp9CudaLaneRing &g = r->ring[l];
+        char *base = (char *)r->mem.p + (size_t)sb0 * ring_bytes_per_sb(ceb);
+        g.blk_cap = sbs * CAP_BLK; g.tx_cap = sbs * CAP_TX; g.itx_cap = sbs * CAP_ITX; g.coef_cap = sbs * CAP_COEF;
+        g.blk = (Vp9CudaInterBlock *)base;              base += (size_t)g.blk_cap * sizeof(Vp9CudaInterBlock);
+        g.tx = (Vp9CudaTx *)base;                       base += (size_t)g.tx_cap * sizeof(Vp9CudaTx);
+        g.itx = (Vp9CudaIntraTx *)base;                 base += (size_t)g.itx_cap * sizeof(Vp9CudaIntraTx);
+        g.coef = base;
+        g.coef_base = sb0 * CAP_COEF;
+        g.reserved = 0;
+        d.lane_blk_base[l] = sb0 * CAP_BLK; d.lane_tx_base[l] = sb0 * CAP_TX; d.lane_itx_base[l] = sb0 * CAP_ITX;
+        memset(&r->counts[l], 0, sizeof(r->counts[l]));
+        memset(&r->sent[l], 0, sizeof(r->sent[l]));
+        sb0 += sbs;
+    }
+    memset(r->sb_index.p, 0, (size_t)n_sb * sizeof(Vp9CudaSbIndex));
+    memset(r->lf.p, 0, (size_t)n_sb * sizeof(Vp9CudaLoopFilterSb));
     ring->sb_index = (Vp9CudaSbIndex *)r->sb_index.p;
     ring->lf = (Vp9CudaLoopFilterSb *)r->lf.p;
     ring->n_sb = n_sb;
@@ -938,17 +1103,48 @@ extern "C" int vp9cuda_submit_tile(Vp9CudaCtx *c, uint32_t frame_id, int lane, c
 {
     if (!c || !counts)
         return -EINVAL;
-    std::lock_guard<std::mutex> lk(c->mu);
-    RingSet *r = ring_of(c, frame_id);
+    RingSet *r;
+    {
+        std::lock_guard<std::mutex> lk(c->mu);
+        r = ring_of(c, frame_id);
+    }
     if (!r || lane < 0 || lane >= r->hdr.n_lanes)
         return -EINVAL;
+    std::lock_guard<std::mutex> lk(r->mu);
     const Vp9CudaLaneRing &g = r->ring[lane];
-    if (counts->blk > g.blk_cap || counts->itx > g.itx_cap || counts->coef > g.coef_cap)
+    const Vp9CudaLaneCounts &was = r->counts[lane];
+    if (counts->blk > g.blk_cap || counts->tx > g.tx_cap || counts->itx > g.itx_cap || counts->coef > g.coef_cap ||
+        counts->blk < was.blk || counts->tx < was.tx || counts->itx < was.itx || counts->coef < was.coef)
         return -EINVAL;
-    for (int t = 0; t < 4; t++)
-        if (counts->tx[t] > g.tx_cap[t])
-            return -EINVAL;
     r->counts[lane] = *counts;
+    /* start the copy of what is new; small increments are left to ride with the next call */
+    const uint64_t fresh = (uint64_t)(counts->blk - r->sent[lane].blk) * sizeof(Vp9CudaInterBlock) +
+                           (uint64_t)(counts->tx - r->sent[lane].tx) * sizeof(Vp9CudaTx) +
+                           (uint64_t)(counts->itx - r->sent[lane].itx) * sizeof(Vp9CudaIntraTx) +
+                           (uint64_t)(counts->coef - r->sent[lane].coef) * coef_entry_bytes(r->hdr.bpp);
+    if (fresh < 64 * 1024)
+        return 0;
+    cudaSetDevice(c->device);
+    uint64_t bytes = 0;
+    int ret = copy_lane_range(c, r->dev, g, lane, r->sent[lane], *counts, coef_entry_bytes(r->hdr.bpp), &bytes);
+    if (ret < 0)
+        return ret;
+    r->sent[lane] = *counts;
+    c->h2d_bytes += bytes;
+    c->early_h2d_bytes += bytes;
+    return 0;
+}
+
+extern "C" int vp9cuda_abort_frame(Vp9CudaCtx *c, uint32_t frame_id)
+{
+    if (!c)
+        return -EINVAL;
+    cudaSetDevice(c->device);
+    std::lock_guard<std::mutex> lk(c->mu);
+    RingSet *r = ring_of(c, frame_id);
+    if (!r)
+        return -EINVAL;
+    abort_set(c, r);
     return 0;
 }
 
@@ -958,22 +1154,45 @@ extern "C" int vp9cuda_finish_frame(Vp9CudaCtx *c, uint32_t frame_id, uint8_t *c
     if (!c)
         return -EINVAL;
     cudaSetDevice(c->device);
+    RingSet *r;
+    {
+        std::unique_lock<std::mutex> lk(c->mu);
+        r = ring_of(c, frame_id);
+        if (!r)
+            return -EINVAL;
+        /* decode order: every frame begun before this one has been finished or aborted */
+        const uint64_t seq = r->seq;
+        c->cv.wait(lk, [&]() { return c->next_finish_seq == seq || !r->busy || r->seq != seq; });
+        if (!r->busy || r->seq != seq)
+            return -EINVAL;      /* flushed / aborted while it waited for its turn */
+    }
+    int ret;
+    {
+        std::lock_guard<std::mutex> gk(c->gpu_mu);
+        {
+            std::lock_guard<std::mutex> rk(r->mu);
+            const int ceb = coef_entry_bytes(r->hdr.bpp);
+            uint64_t bytes = 0;
+            ret = 0;
+            kstat_begin(c, c->s_up);
+            for (int l = 0; l < r->hdr.n_lanes && ret == 0; l++) {
+                ret = copy_lane_range(c, r->dev, r->ring[l], l, r->sent[l], r->counts[l], ceb, &bytes);
+                r->sent[l] = r->counts[l];
+            }
+            if (ret == 0)
+                ret = upload_frame_tail(c, r->dev, &r->hdr, r->n_sb, r->counts, (const Vp9CudaSbIndex *)r->sb_index.p,
+                                        (const Vp9CudaLoopFilterSb *)r->lf.p, &bytes);
+            kstat_end(c, KS_H2D, 0, bytes, c->s_up);
+            c->h2d_bytes += bytes;
+            cudaEventRecord(r->consumed, c->s_up);
+        }
+        if (ret == 0)
+            ret = reconstruct(c, r->dev, out_planes, out_strides, ticket);
+    }
     std::lock_guard<std::mutex> lk(c->mu);
-    RingSet *r = ring_of(c, frame_id);
-    if (!r)
-        return -EINVAL;
-    Vp9CudaFrameRecords recs;
-    recs.lanes = r->ring;
-    recs.counts = r->counts;
-    recs.sb_index = (const Vp9CudaSbIndex *)r->sb_index.p;
-    recs.lf = (const Vp9CudaLoopFilterSb *)r->lf.p;
-    int ret = upload_records(c, r->dev, &r->hdr, &recs);
-    if (ret == 0)
-        CK(cudaEventRecord(r->consumed, c->s_up));
     r->busy = false;
-    if (ret < 0)
-        return ret;
-    return reconstruct(c, r->dev, out_planes, out_strides, ticket);
+    advance_turn(c);
+    return ret;
 }
 
 extern "C" int vp9cuda_wait(Vp9CudaCtx *c, uint64_t ticket)
@@ -1008,10 +1227,12 @@ extern "C" int vp9cuda_wait(Vp9CudaCtx *c, uint64_t ticket)
 extern "C" int vp9cuda_show_existing(Vp9CudaCtx *c, int slot, uint8_t *const out_planes[3],
                                      const ptrdiff_t out_strides[3], uint64_t *ticket)
 {
-    if (!c || slot < 0 || slot > 7 || !c->ref[slot] || !out_planes)
+    if (!c || slot < 0 || slot > 7 || !out_planes)
         return -EINVAL;
     cudaSetDevice(c->device);
-    std::lock_guard<std::mutex> lk(c->mu);
+    std::lock_guard<std::mutex> lk(c->gpu_mu);
+    if (!c->ref[slot])
+        return -EINVAL;
     int r = copy_out(c, c->ref[slot], out_planes, out_strides);
     return r < 0 ? r : make_ticket(c, ticket, c->s_down);
 }
@@ -1023,7 +1244,7 @@ extern "C" int vp9cuda_map_frame(Vp9CudaCtx *c, int slot, Vp9CudaMappedFrame *ou
     cudaSetDevice(c->device);
     Surface *s;
     {
-        std::lock_guard<std::mutex> lk(c->mu);
+        std::lock_guard<std::mutex> lk(c->gpu_mu);
         s = slot < 0 ? c->last : c->ref[slot];
         if (!s)
             return -EINVAL;
@@ -1044,7 +1265,7 @@ extern "C" int vp9cuda_unmap_frame(Vp9CudaCtx *c, const void *plane0)
 {
     if (!c || !plane0)
         return -EINVAL;
-    std::lock_guard<std::mutex> lk(c->mu);
+    std::lock_guard<std::mutex> lk(c->gpu_mu);
     for (Surface *s : c->pool)
         if (s->pl[0] == plane0 && s->refs > 0) {
             s->refs--;
@@ -1059,13 +1280,25 @@ extern "C" int vp9cuda_decode_frame(Vp9CudaCtx *c, const Vp9CudaFrameHeader *hdr
     if (!c || !hdr || !recs)
         return -EINVAL;
     cudaSetDevice(c->device);
-    std::lock_guard<std::mutex> lk(c->mu);
-    /* use the device records of ring set (frame_id round robin) as the landing zone */
-    RingSet *r = c->rings[c->next_frame_id++ % c->rings.size()];
-    int ret = upload_records(c, r->dev, hdr, recs);
+    {
+        /* one-shot frames take their place in decode order at once: no begun frame may be open */
+        std::lock_guard<std::mutex> lk(c->mu);
+        for (RingSet *r : c->rings)
+            if (r->busy)
+                return -EBUSY;
+    }
+    std::lock_guard<std::mutex> gk(c->gpu_mu);
+    /* landing zones of their own (three, round robin), so that the upload of one frame runs beside
+     * the kernels of the one before */
+    if (c->oneshot.empty())
+        c->oneshot.assign(3, nullptr);
+    DevRecords *&d = c->oneshot[c->oneshot_rr++ % c->oneshot.size()];
+    if (!d)
+        d = new DevRecords;
+    int ret = upload_records(c, *d, hdr, recs);
     if (ret < 0)
         return ret;
-    return reconstruct(c, r->dev, out_planes, out_strides, ticket);
+    return reconstruct(c, *d, out_planes, out_strides, ticket);
 }
 
 extern "C" int vp9cuda_stage_frame(Vp9CudaCtx *c, const Vp9CudaFrameHeader *hdr, const Vp9CudaFrameRecords *recs,
@@ -1074,7 +1307,7 @@ extern "C" int vp9cuda_stage_frame(Vp9CudaCtx *c, const Vp9CudaFrameHeader *hdr,
     if (!c || !hdr || !recs || !handle)
         return -EINVAL;
     cudaSetDevice(c->device);
-    std::lock_guard<std::mutex> lk(c->mu);
+    std::lock_guard<std::mutex> gk(c->gpu_mu);
     DevRecords *d = new DevRecords;
     int ret = upload_records(c, *d, hdr, recs);
     if (ret < 0) {
@@ -1095,7 +1328,7 @@ extern "C" int vp9cuda_run_staged(Vp9CudaCtx *c, int handle, uint8_t *const out_
     if (!c || handle < 0 || handle >= (int)c->staged.size() || !c->staged[handle])
         return -EINVAL;
     cudaSetDevice(c->device);
-    std::lock_guard<std::mutex> lk(c->mu);
+    std::lock_guard<std::mutex> gk(c->gpu_mu);
     return reconstruct(c, *c->staged[handle], out_planes, out_strides, ticket);
 }
 
@@ -1104,12 +1337,27 @@ extern "C" int vp9cuda_free_staged(Vp9CudaCtx *c, int handle)
     if (!c || handle < 0 || handle >= (int)c->staged.size() || !c->staged[handle])
         return -EINVAL;
     cudaSetDevice(c->device);
+    std::lock_guard<std::mutex> gk(c->gpu_mu);
     sync_all(c);
     if (c->prev_dev == c->staged[handle])
         c->prev_dev = nullptr;
     c->staged[handle]->release();
     delete c->staged[handle];
     c->staged[handle] = nullptr;
+    return 0;
+}
+
+extern "C" int vp9cuda_get_stat(Vp9CudaCtx *c, const char *key, uint64_t *value)
+{
+    if (!c || !key || !value)
+        return -EINVAL;
+    if (!strcmp(key, "allocs")) *value = c->n_allocs;
+    else if (!strcmp(key, "frames")) *value = c->n_frames;
+    else if (!strcmp(key, "aborted")) *value = c->n_aborted;
+    else if (!strcmp(key, "h2d_bytes")) *value = c->h2d_bytes;
+    else if (!strcmp(key, "early_h2d_bytes")) *value = c->early_h2d_bytes;
+    else if (!strcmp(key, "d2h_bytes")) *value = c->d2h_bytes;
+    else return -EINVAL;
     return 0;
 }
 
@@ -1170,7 +1418,7 @@ extern "C" int vp9cuda_set_option(Vp9CudaCtx *c, const char *key, int value)
     }
     if (!strcmp(key, "phase_clk")) {       /* profiling: accumulate per-phase clocks inside k_lf */
         cudaSetDevice(c->device);
-        if (c->phase_clk.reserve(64 * 8))
+        if (c->phase_clk.reserve(64 * 8, c->n_allocs))
             return -ENOMEM;
         CK(cudaStreamSynchronize(c->stream));
         CK(cudaMemset(c->phase_clk.p, 0, 64 * 8));
@@ -1234,11 +1482,11 @@ extern "C" int vp9cuda_frame_checksum(Vp9CudaCtx *c, int slot, uint64_t *sum)
     if (!c || !sum || slot > 7)
         return -EINVAL;
     cudaSetDevice(c->device);
-    std::lock_guard<std::mutex> lk(c->mu);
+    std::lock_guard<std::mutex> lk(c->gpu_mu);
     Surface *s = slot < 0 ? c->last : c->ref[slot];
     if (!s)
         return -EINVAL;
-    if (c->sum_buf.reserve(8))
+    if (c->sum_buf.reserve(8, c->n_allocs))
         return -ENOMEM;
     CK(cudaMemsetAsync(c->sum_buf.p, 0, 8, c->stream));
     for (int p = 0; p < 3; p++) {

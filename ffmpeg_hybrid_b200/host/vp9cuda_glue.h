@@ -22,12 +22,25 @@ typedef struct VP9CudaGlue VP9CudaGlue;
 /* vp9_decode_init: attach the back end.  Fails (negative AVERROR) when libvp9cuda.so or a
  * B200 is missing -- there is deliberately no software fallback. */
 int  ff_vp9cuda_init(struct AVCodecContext *avctx);
-/* vp9_decode_free */
+/* vp9_decode_free: first wait for every copy-out that may still write into a picture about to be
+ * unreferenced (quiesce, before the frames are dropped), then detach (uninit) */
+void ff_vp9cuda_quiesce(struct AVCodecContext *avctx);
 void ff_vp9cuda_uninit(struct AVCodecContext *avctx);
+/* vp9_decode_update_thread_context (frame threading, vp9.c:1923-1962): all workers share one back end */
+int  ff_vp9cuda_update_thread_context(struct AVCodecContext *dst, const struct AVCodecContext *src);
 /* vp9_decode_flush */
 void ff_vp9cuda_flush(struct AVCodecContext *avctx);
-/* vp9_decode_frame, after the header is parsed and CUR_FRAME allocated, before the tile loop */
+/* vp9_decode_frame, after decode_frame_header and before vp9_frame_alloc: back end exists, CUR_FRAME
+ * will come from the pinned pool */
+int  ff_vp9cuda_prepare_frame(struct AVCodecContext *avctx);
+/* vp9_decode_frame, after the header is parsed and CUR_FRAME allocated, before the tile loop and
+ * before ff_thread_finish_setup: fixes the frame's place in decode order */
 int  ff_vp9cuda_begin_frame(struct AVCodecContext *avctx);
+/* vp9_decode_frame returned an error after begin_frame: give the frame's ring set back */
+void ff_vp9cuda_abort_frame(struct AVCodecContext *avctx);
+/* decode_tiles / decode_tiles_mt, after each superblock row of a tile column: its records may
+ * start their way to the GPU */
+void ff_vp9cuda_row_done(struct VP9TileData *td);
 /* ff_vp9_decode_block, in place of ff_vp9_{intra,inter}_recon_{8,16}bpp + overhang copies */
 void ff_vp9cuda_emit_block(struct VP9TileData *td);
 /* ff_vp9_loopfilter_sb, in place of filter_plane_cols/rows */

@@ -1,8 +1,9 @@
 """Reader for the .v9r record-stream dumps written by the libavcodec glue ($VP9CUDA_DUMP).
 
-Layout (ffmpeg_hybrid_b200/host/vp9cuda_glue.c, dump sink): "V9R2", 8 x u32 struct sizes, then per
-frame "FRAM", Vp9CudaFrameHeader, n_sb, per lane {Vp9CudaLaneCounts, coef_base, blk[], tx[0..3][],
-itx[], coef[]}, sb_index[n_sb], lf[n_sb].  Struct layouts mirror include/vp9cuda.h.
+Layout (ffmpeg_hybrid_b200/host/vp9cuda_glue.c, dump sink): "V9R3", 8 x u32 struct sizes, then per
+frame "FRAM", Vp9CudaFrameHeader, n_sb, per lane {Vp9CudaLaneCounts, coef_base, blk[], tx[], itx[],
+coef[] (Vp9CudaCoef16 / Vp9CudaCoef32 entries)}, sb_index[n_sb], lf[n_sb].  Struct layouts mirror
+include/vp9cuda.h.
 """
 from __future__ import annotations
 
@@ -19,10 +20,21 @@ HDR_DTYPE = np.dtype([
     ("keyframe", "u1"), ("intraonly", "u1"), ("lossless", "u1"), ("invisible", "u1"),
     ("lf_level", "u1"), ("refreshrefmask", "u1"), ("ref_slot", "u1", (3,)),
     ("mvscale", "<u2", (3, 2)), ("mvstep", "u1", (3, 2)), ("n_lanes", "u1"), ("pad", "u1", (3,)),
-    ("lane_sbs", "<u2", (MAX_LANES,)), ("lim_lut", "u1", (64,)), ("mblim_lut", "u1", (64,)),
+    ("lane_sbs", "<u4", (MAX_LANES,)), ("lim_lut", "u1", (64,)), ("mblim_lut", "u1", (64,)),
 ], align=True)
-COUNTS_DTYPE = np.dtype([("blk", "<u4"), ("tx", "<u4", (4,)), ("itx", "<u4"), ("coef", "<u4")])
-BLK_SIZE, TX_SIZE, ITX_SIZE, SBI_SIZE, LF_SIZE = 48, 12, 20, 8, 192
+COUNTS_DTYPE = np.dtype([("blk", "<u4"), ("tx", "<u4"), ("itx", "<u4"), ("coef", "<u4")])
+BLK_SIZE, TX_SIZE, ITX_SIZE, SBI_SIZE, LF_SIZE = 48, 16, 20, 16, 192
+BLK_DTYPE = np.dtype([("col", "<u2"), ("row", "<u2"), ("bs", "u1"), ("filter", "u1"), ("comp", "u1"), ("ref", "u1", (2,)),
+                      ("pad", "u1", (3,)), ("mv", "<i2", (4, 2, 2)), ("reserved", "<u4")])
+TX_DTYPE = np.dtype([("x4", "<u2"), ("y4", "<u2"), ("eob", "<u2"), ("ncoef", "<u2"), ("plane", "u1"), ("tx", "u1"),
+                     ("txtp", "u1"), ("pad", "u1"), ("coef_off", "<u4")])
+ITX_DTYPE = np.dtype([("x4", "<u2"), ("y4", "<u2"), ("eob", "<u2"), ("level", "<u2"), ("plane", "u1"), ("tx", "u1"),
+                      ("mode", "u1"), ("txtp", "u1"), ("flags", "u1"), ("pad", "u1"), ("ncoef", "<u2"), ("coef_off", "<u4")])
+SBI_DTYPE = np.dtype([("itx_start", "<u4"), ("tx_start", "<u4"), ("itx_count", "<u2"), ("tx_count", "<u2"),
+                      ("lane", "u1"), ("pad", "u1", (3,))])
+COEF16_DTYPE = np.dtype([("val", "<i2"), ("pos", "<u2")])
+COEF32_DTYPE = np.dtype([("val", "<i4"), ("pos", "<u4")])
+assert (BLK_DTYPE.itemsize, TX_DTYPE.itemsize, ITX_DTYPE.itemsize, SBI_DTYPE.itemsize) == (48, 16, 20, 16)
 
 
 @dataclass
@@ -30,7 +42,7 @@ class Lane:
     counts: np.ndarray
     coef_base: int
     blk: bytes
-    tx: List[bytes]
+    tx: bytes
     itx: bytes
     coef: bytes
 
@@ -47,14 +59,14 @@ class Frame:
     def record_bytes(self) -> int:
         n = len(self.sb_index) + len(self.lf)
         for l in self.lanes:
-            n += len(l.blk) + sum(len(t) for t in l.tx) + len(l.itx) + len(l.coef)
+            n += len(l.blk) + len(l.tx) + len(l.itx) + len(l.coef)
         return n
 
 
 def read_v9r(path: Path) -> List[Frame]:
     data = Path(path).read_bytes()
-    if data[:4] != b"V9R2":
-        raise ValueError("not a V9R2 file")
+    if data[:4] != b"V9R3":
+        raise ValueError("not a V9R3 file")
     sizes = struct.unpack("<8I", data[4:36])
     if sizes[0] != HDR_DTYPE.itemsize or sizes[1] != COUNTS_DTYPE.itemsize or sizes[2:7] != (
             BLK_SIZE, TX_SIZE, ITX_SIZE, SBI_SIZE, LF_SIZE):
@@ -70,7 +82,7 @@ def read_v9r(path: Path) -> List[Frame]:
         (n_sb,) = struct.unpack_from("<I", data, pos)
         pos += 4
         fr = Frame(hdr=hdr, n_sb=n_sb)
-        cb = 4 if hdr["bpp"] > 8 else 2
+        ceb = COEF32_DTYPE.itemsize if hdr["bpp"] > 8 else COEF16_DTYPE.itemsize
         for _ in range(int(hdr["n_lanes"])):
             cnt = np.frombuffer(data, COUNTS_DTYPE, 1, pos)[0]
             pos += COUNTS_DTYPE.itemsize
@@ -83,9 +95,9 @@ def read_v9r(path: Path) -> List[Frame]:
                 pos += n
                 return b
             blk = take(int(cnt["blk"]) * BLK_SIZE)
-            tx = [take(int(cnt["tx"][t]) * TX_SIZE) for t in range(4)]
+            tx = take(int(cnt["tx"]) * TX_SIZE)
             itx = take(int(cnt["itx"]) * ITX_SIZE)
-            coef = take(int(cnt["coef"]) * cb)
+            coef = take(int(cnt["coef"]) * ceb)
             fr.lanes.append(Lane(cnt, coef_base, blk, tx, itx, coef))
         fr.sb_index = data[pos:pos + n_sb * SBI_SIZE]
         pos += n_sb * SBI_SIZE

@@ -13,9 +13,10 @@
  * Nothing here ever falls back to a CPU implementation.
  *
  * Threading: one Vp9CudaCtx per decoder instance (= per stream), bound to one GPU and its own
- * CUDA streams.  begin_frame / finish_frame / wait / flush come from the decode thread.
- * A lane ring has exactly one producer thread; submit_tile may be called concurrently for
- * DIFFERENT lanes (libavcodec slice threading, vp9.c:1442-1520, runs one lane per tile column).
+ * CUDA streams.  begin_frame comes from one thread at a time in decode order; everything that
+ * names a frame_id may come from any thread (libavcodec frame threading, pthread_frame.c, runs
+ * one frame per worker).  A lane ring has exactly one producer thread; submit_tile may be called
+ * concurrently for DIFFERENT lanes (slice threading, vp9.c:1442-1520: one lane per tile column).
  */
 #ifndef VP9CUDA_H
 #define VP9CUDA_H
@@ -30,7 +31,7 @@ extern "C" {
 #pragma GCC visibility push(default)   /* the library is built with -fvisibility=hidden */
 #endif
 
-#define VP9CUDA_ABI_VERSION 2
+#define VP9CUDA_ABI_VERSION 3
 #define VP9CUDA_MAX_LANES   64   /* max tile columns, vp9.c:800-810 */
 
 typedef struct Vp9CudaCtx Vp9CudaCtx;
@@ -51,15 +52,19 @@ typedef struct Vp9CudaInterBlock {
 } Vp9CudaInterBlock;         /* 48 bytes */
 
 /* One per transform block with eob > 0 of an INTER block: the itxfm_add call of
- * inter_recon() (vp9recon.c:707-763).  Kept in four lists by transform size. */
+ * inter_recon() (vp9recon.c:707-763).  One list per lane, in coding order, so that the blocks of
+ * one superblock are contiguous (Vp9CudaSbIndex.tx_start / tx_count). */
 typedef struct Vp9CudaTx {
     uint16_t x4, y4;         /* position inside the plane, in 4-pixel units */
     uint16_t eob;
+    uint16_t ncoef;          /* coefficient entries of this block (non-zero values, <= eob) */
     uint8_t  plane;          /* 0 Y, 1 U, 2 V */
+    uint8_t  tx;             /* enum TxfmMode 0..3 */
     uint8_t  txtp;           /* enum TxfmType | 0x80 when lossless (WHT, slot index 4) */
-    uint32_t coef_off;       /* first coefficient in the frame's coefficient arena
+    uint8_t  pad;
+    uint32_t coef_off;       /* first entry in the frame's coefficient stream
                                 (= lane ring's coef_base + offset inside the lane) */
-} Vp9CudaTx;                 /* 12 bytes */
+} Vp9CudaTx;                 /* 16 bytes */
 
 /* One per transform block of an INTRA block, in the order intra_recon() walks them
  * (vp9recon.c:269-358): prediction (check_intra_mode, vp9recon.c:37-221) then itxfm_add. */
@@ -76,19 +81,32 @@ typedef struct Vp9CudaIntraTx {
     uint8_t  mode;           /* signalled IntraPredMode 0..9 (edge remap happens on the GPU) */
     uint8_t  txtp;           /* enum TxfmType | 0x80 when lossless */
     uint8_t  flags;          /* VP9CUDA_ITX_* */
-    uint8_t  pad[3];
+    uint8_t  pad;
+    uint16_t ncoef;          /* coefficient entries of this block */
     uint32_t coef_off;
 } Vp9CudaIntraTx;            /* 20 bytes */
 #define VP9CUDA_ITX_HAVE_LEFT  1   /* col > tile_col_start || x > 0  (vp9recon.c:46) */
 #define VP9CUDA_ITX_HAVE_RIGHT 2   /* x < w - 1 inside the coding block (vp9recon.c:47) */
 
-/* Per 64x64 superblock: where its intra transform blocks sit in the producing lane's list. */
+/* Coefficient stream: only the NON-ZERO dequantised coefficients of a coded transform block
+ * travel, each with its position in the column-major N x N block decode_coeffs fills
+ * (`coef[rc]`, vp9block.c:912-917; rc = x * N + y).  The reference ships nothing -- it keeps the
+ * dense block in td->block -- and checkasm bounds the block by eob (copy_subcoefs,
+ * tests/checkasm/vp9dsp.c:253-296); here the eob-long scan prefix is walked once on the host.
+ * 8-bit streams use Vp9CudaCoef16 (dctcoef = int16_t), 10/12-bit Vp9CudaCoef32 (int32_t,
+ * bit_depth_template.c:82). */
+typedef struct Vp9CudaCoef16 { int16_t val; uint16_t pos; } Vp9CudaCoef16;   /* 4 bytes */
+typedef struct Vp9CudaCoef32 { int32_t val; uint32_t pos; } Vp9CudaCoef32;   /* 8 bytes */
+
+/* Per 64x64 superblock: where its transform blocks sit in the producing lane's lists. */
 typedef struct Vp9CudaSbIndex {
-    uint32_t itx_start;
+    uint32_t itx_start;      /* intra transform blocks (Vp9CudaIntraTx) */
+    uint32_t tx_start;       /* residual blocks of inter blocks (Vp9CudaTx) */
     uint16_t itx_count;
+    uint16_t tx_count;
     uint8_t  lane;
-    uint8_t  pad;
-} Vp9CudaSbIndex;            /* 8 bytes */
+    uint8_t  pad[3];
+} Vp9CudaSbIndex;            /* 16 bytes */
 
 /* Byte-for-byte VP9Filter (vp9dec.h:83-87): level[64] then mask[2][2][8][4]. */
 typedef struct Vp9CudaLoopFilterSb {
@@ -112,24 +130,27 @@ typedef struct Vp9CudaFrameHeader {
     uint8_t  mvstep[3][2];       /* s->mvstep */
     uint8_t  n_lanes;            /* producer lanes this frame (1, or tile columns when slice-threaded) */
     uint8_t  pad[3];
-    uint16_t lane_sbs[VP9CUDA_MAX_LANES]; /* superblocks each lane will produce (sizes its ring) */
+    uint32_t lane_sbs[VP9CUDA_MAX_LANES]; /* superblocks each lane will produce (sizes its ring);
+                                             their sum must not exceed the frame's superblock count */
     uint8_t  lim_lut[64];        /* s->filter_lut (vp9.c:673-686) */
     uint8_t  mblim_lut[64];
 } Vp9CudaFrameHeader;
 
-/* Pinned host memory of one producer lane for the current frame. */
+/* Pinned host memory of one producer lane for the current frame.  Capacities per superblock
+ * of the lane: 64 blocks, 384 + 384 transform blocks, 6144 coefficient entries (= every
+ * coefficient of every block non-zero), so a legal stream can never overflow a ring. */
 typedef struct Vp9CudaLaneRing {
     Vp9CudaInterBlock *blk;  uint32_t blk_cap;
-    Vp9CudaTx *tx[4];        uint32_t tx_cap[4];   /* by transform size 4x4..32x32 */
+    Vp9CudaTx *tx;           uint32_t tx_cap;
     Vp9CudaIntraTx *itx;     uint32_t itx_cap;
-    void *coef;              uint32_t coef_cap;    /* int16_t (8-bit) or int32_t (10/12-bit) units */
-    uint32_t coef_base;      /* index of coef[0] in the frame's coefficient arena: every
+    void *coef;              uint32_t coef_cap;    /* Vp9CudaCoef16 (8-bit) or Vp9CudaCoef32 entries */
+    uint32_t coef_base;      /* index of coef[0] in the frame's coefficient stream: every
                                 coef_off the producer writes is coef_base + offset-in-lane */
     uint32_t reserved;
 } Vp9CudaLaneRing;
 
 typedef struct Vp9CudaLaneCounts {
-    uint32_t blk, tx[4], itx, coef;
+    uint32_t blk, tx, itx, coef;
 } Vp9CudaLaneCounts;
 
 /* Frame-level pinned arrays, one entry per superblock in raster order. */
@@ -144,33 +165,53 @@ typedef struct Vp9CudaFrameRing {
 /* ---- life cycle -------------------------------------------------------------------------- */
 
 /* Replaces ff_vp9_webgpu_init (vp9_webgpu.h:371; call site vp9.c:1905-1917).
- * max_w/max_h bound every frame of the stream (all sizes); frames_in_flight >= 1. */
+ * max_w x max_h at max_bpp (8, 10 or 12) bound every frame of the stream: all pinned rings and
+ * device record buffers of the frames_in_flight (1..32) ring sets are allocated here, so that no
+ * allocation happens on the frame path (vp9cuda_get_stat "allocs" stays constant).  With
+ * max_w == 0 or max_h == 0 the buffers grow on demand instead (a frame larger than any before
+ * reallocates; never in the steady state of a stream). */
 int  vp9cuda_create(Vp9CudaCtx **out, int device, int max_w, int max_h, int max_bpp,
                     int frames_in_flight);
 /* Replaces ff_vp9_webgpu_uninit (vp9_webgpu.h:374; call site vp9.c:1281-1292). */
 void vp9cuda_destroy(Vp9CudaCtx *ctx);
-/* Replaces vp9_decode_flush's reference drop (vp9.c:1865-1883). */
+/* Replaces vp9_decode_flush's reference drop (vp9.c:1865-1883).  Frames that were begun and
+ * not finished are aborted. */
 int  vp9cuda_flush(Vp9CudaCtx *ctx);
 
-/* ---- per frame ----------------------------------------------------------------------------- */
+/* ---- per frame -----------------------------------------------------------------------------
+ * Frames may overlap in time (libavcodec frame threading, pthread_frame.c: one vp9_decode_frame
+ * per worker, only the serial entropy decode runs on the host): begin_frame fixes the DECODE
+ * ORDER, every call after it names its frame by frame_id and may come from any thread, and
+ * finish_frame hands the frames to the GPU in begin_frame order whatever order the workers
+ * arrive in.  Every begun frame must end in finish_frame or abort_frame. */
 
 /* Call after decode_frame_header + vp9_frame_alloc (vp9.c:1657-1692), before the tile loop, in
- * DECODE ORDER (reference slots are resolved here).  Blocks only if all frames_in_flight ring
- * sets are still in use.  Fills *ring. */
+ * DECODE ORDER (one thread at a time; under frame threading: before ff_thread_finish_setup).
+ * Blocks while all frames_in_flight ring sets are in use.  Fills *ring.
+ * -EINVAL for a frame the back end cannot take (size 0, more than 16384 pixels wide, a bit
+ * depth other than 8/10/12, chroma other than 4:2:0). */
 int  vp9cuda_begin_frame(Vp9CudaCtx *ctx, const Vp9CudaFrameHeader *hdr, Vp9CudaFrameRing *ring);
-/* Pinned ring of one lane of the current frame. */
+/* Pinned ring of one lane of frame frame_id. */
 int  vp9cuda_tile_ring(Vp9CudaCtx *ctx, uint32_t frame_id, int lane, Vp9CudaLaneRing *ring);
-/* Records [previous counts, counts) of this lane are final: start their host->device copy.
- * Called by the lane's producer at tile / superblock-row granularity (decode_tiles,
- * vp9.c:1325-1395; decode_tiles_mt, vp9.c:1465-1518).  Counts are cumulative for the frame. */
+/* Records [previous counts, counts) of this lane are final: their host->device copy is enqueued
+ * now, beside the entropy decode of the rest of the frame.  Called by the lane's producer at
+ * tile / superblock-row granularity (decode_tiles, vp9.c:1325-1395; decode_tiles_mt,
+ * vp9.c:1465-1518), any number of times.  Counts are cumulative for the frame and never
+ * decrease; records below a submitted count must not be written again. */
 int  vp9cuda_submit_tile(Vp9CudaCtx *ctx, uint32_t frame_id, int lane,
                          const Vp9CudaLaneCounts *counts);
-/* All lanes submitted: enqueue inter prediction -> residual -> intra wavefront -> loop filter
- * -> reference refresh and, when out_planes != NULL, the async copy of the visible w x h crop
- * (framemd5 layout: packed rows, 10-bit as little-endian 16-bit).  Replaces the reconstruction
- * half of decode_tiles + ff_vp9_webgpu_end_frame (vp9.c:1839-1857).  Returns a ticket. */
+/* All lanes submitted: copy what submit_tile has not yet sent plus the per-superblock arrays,
+ * then enqueue inter prediction + residual -> intra wavefront -> loop filter -> reference
+ * refresh and, when out_planes != NULL, the async copy of the visible w x h crop (framemd5
+ * layout: packed rows, 10-bit as little-endian 16-bit).  Replaces the reconstruction half of
+ * decode_tiles + ff_vp9_webgpu_end_frame (vp9.c:1839-1857).  Blocks until every frame begun
+ * before this one has been finished or aborted.  Returns a ticket. */
 int  vp9cuda_finish_frame(Vp9CudaCtx *ctx, uint32_t frame_id, uint8_t *const out_planes[3],
                           const ptrdiff_t out_strides[3], uint64_t *ticket);
+/* The frame will not be finished (the host found the packet damaged between begin_frame and
+ * finish_frame: vp9.c:1340-1346, 1389-1391, 1827-1832): give its ring set back and let the
+ * frames behind it proceed.  Reference slots stay as they were (vp9.c:1860-1862 `fail:`). */
+int  vp9cuda_abort_frame(Vp9CudaCtx *ctx, uint32_t frame_id);
 /* Block until the frame behind `ticket` is complete (pixels in out_planes valid). */
 int  vp9cuda_wait(Vp9CudaCtx *ctx, uint64_t ticket);
 /* Device-resident output (the output site is vp9.c:1853-1857): hand the finished
@@ -238,6 +279,11 @@ int  vp9cuda_set_option(Vp9CudaCtx *ctx, const char *key, int value);
 int  vp9cuda_phase_clocks(Vp9CudaCtx *ctx, uint64_t *out, int n);
 /* device time between two marks (waits for mark_b) */
 int  vp9cuda_elapsed_ms(Vp9CudaCtx *ctx, int mark_a, int mark_b, double *ms);
+/* counters: "allocs" = device / pinned allocations made so far (constant once the stream is in
+ * its steady state), "frames" = frames reconstructed, "aborted" = frames given back unfinished,
+ * "h2d_bytes" / "d2h_bytes" = record bytes copied in / picture bytes copied out so far,
+ * "early_h2d_bytes" = the part of h2d_bytes that submit_tile sent before finish_frame */
+int  vp9cuda_get_stat(Vp9CudaCtx *ctx, const char *key, uint64_t *value);
 const char *vp9cuda_version(void);
 
 /* ---- slot-level entry points: the batched equivalent of one VP9DSPContext slot -------------

@@ -172,9 +172,9 @@ struct Lane {
     Vp9CudaLaneCounts n;
     uint32_t coef_base;
     std::vector<Vp9CudaInterBlock> blk;
-    std::vector<Vp9CudaTx> tx[4];
+    std::vector<Vp9CudaTx> tx;
     std::vector<Vp9CudaIntraTx> itx;
-    std::vector<uint8_t> coef;
+    std::vector<uint8_t> coef;            /* Vp9CudaCoef16 / Vp9CudaCoef32 entries */
 };
 
 struct Model {
@@ -182,12 +182,31 @@ struct Model {
     std::shared_ptr<Surf> cur;
 };
 
-static const void *coef_ptr(const std::vector<Lane> &lanes, uint32_t off, int cb)
+/* The coefficient stream carries the non-zero coefficients of a block with their positions in
+ * the column-major N x N block (include/vp9cuda.h: Vp9CudaCoef16/32).  Rebuilds the dense block
+ * the itxfm_add slot takes; checks what the producer promises (positions inside the block, values
+ * non-zero, at most eob of them, an eob == 1 block holds the DC). */
+static const void *coef_block(const std::vector<Lane> &lanes, uint32_t off, int ncoef, int eob, int tx, bool hbd,
+                              std::vector<int32_t> &dense)
 {
-    for (const Lane &l : lanes)
-        if (off >= l.coef_base && off < l.coef_base + l.n.coef)
-            return l.coef.data() + (size_t)(off - l.coef_base) * cb;
-    fprintf(stderr, "coef_off %u outside every lane\n", off);
+    const int nn = 16 << (2 * tx);
+    dense.assign(nn, 0);
+    if (ncoef > eob || eob > nn) { fprintf(stderr, "ncoef %d / eob %d out of range\n", ncoef, eob); exit(3); }
+    if (!ncoef)
+        return dense.data();
+    for (const Lane &l : lanes) {
+        if (off < l.coef_base || (uint64_t)off + ncoef > (uint64_t)l.coef_base + l.n.coef)
+            continue;
+        for (int i = 0; i < ncoef; i++) {
+            int32_t val; uint32_t pos;
+            if (hbd) { const Vp9CudaCoef32 &e = ((const Vp9CudaCoef32 *)l.coef.data())[off - l.coef_base + i]; val = e.val; pos = e.pos; }
+            else     { const Vp9CudaCoef16 &e = ((const Vp9CudaCoef16 *)l.coef.data())[off - l.coef_base + i]; val = e.val; pos = e.pos; }
+            if (pos >= (uint32_t)nn || !val || (eob == 1 && pos)) { fprintf(stderr, "bad coefficient entry pos %u val %d\n", pos, val); exit(3); }
+            if (hbd) dense[pos] = val; else ((int16_t *)dense.data())[pos] = (int16_t)val;
+        }
+        return dense.data();
+    }
+    fprintf(stderr, "coef_off %u (+%d) outside every lane\n", off, ncoef);
     exit(3);
 }
 
@@ -252,7 +271,8 @@ static void inter_block(Model &m, const Vp9CudaFrameHeader &h, const Vp9CudaInte
 static void decode_frame(Model &m, const Vp9CudaFrameHeader &h, const std::vector<Lane> &lanes,
                          const std::vector<Vp9CudaSbIndex> &sbi, const std::vector<Vp9CudaLoopFilterSb> &lf)
 {
-    const int cb = h.bpp > 8 ? 4 : 2;
+    const bool hbd = h.bpp > 8;
+    std::vector<int32_t> dense;
     const int cols = (h.w + 7) >> 3, rows = (h.h + 7) >> 3;
     const int sb_cols = (h.w + 63) >> 6, sb_rows = (h.h + 63) >> 6;
     m.cur = std::make_shared<Surf>();
@@ -263,10 +283,25 @@ static void decode_frame(Model &m, const Vp9CudaFrameHeader &h, const std::vecto
         for (const auto &b : l.blk)
             inter_block(m, h, b);
     for (const Lane &l : lanes)
-        for (int t = 0; t < 4; t++)
-            for (const auto &r : l.tx[t])
-                itx_add(&c.p[r.plane][(size_t)r.y4 * 4 * c.stride[r.plane] + r.x4 * 4], c.stride[r.plane],
-                        coef_ptr(lanes, r.coef_off, cb), t, r.txtp, r.eob, h.bpp);
+        for (const auto &r : l.tx)
+            itx_add(&c.p[r.plane][(size_t)r.y4 * 4 * c.stride[r.plane] + r.x4 * 4], c.stride[r.plane],
+                    coef_block(lanes, r.coef_off, r.ncoef, r.eob, r.tx, hbd, dense), r.tx, r.txtp, r.eob, h.bpp);
+    /* the per-superblock index must name exactly the lane's residual blocks that lie inside it */
+    {
+        std::vector<size_t> seen(lanes.size(), 0);
+        for (int s = 0; s < sb_rows * sb_cols; s++) {
+            if (!sbi[s].tx_count) continue;
+            const Lane &l = lanes[sbi[s].lane];
+            for (unsigned k = 0; k < sbi[s].tx_count; k++) {
+                const Vp9CudaTx &r = l.tx[sbi[s].tx_start + k];
+                const int ch = r.plane > 0, sx = (r.x4 * 4) >> (ch ? 5 : 6), sy = (r.y4 * 4) >> (ch ? 5 : 6);
+                if (sy * sb_cols + sx != s) { fprintf(stderr, "superblock %d lists a residual block of superblock %d\n", s, sy * sb_cols + sx); exit(4); }
+            }
+            seen[sbi[s].lane] += sbi[s].tx_count;
+        }
+        for (size_t i = 0; i < lanes.size(); i++)
+            if (seen[i] != lanes[i].tx.size()) { fprintf(stderr, "lane %zu: %zu residual blocks indexed, %zu recorded\n", i, seen[i], lanes[i].tx.size()); exit(4); }
+    }
     /* phase 3: intra blocks, superblocks in raster order, coding order inside.  Along the way
      * the records' dependency levels are re-derived and checked (exactly 1 + max over the intra
      * neighbours the block may read), which is what the GPU's level-ordered dispatch relies on. */
@@ -306,7 +341,7 @@ static void decode_frame(Model &m, const Vp9CudaFrameHeader &h, const std::vecto
                         avail_w, avail_h, h.bpp);
             if (r.eob)
                 itx_add(&c.p[pl][(size_t)by * c.stride[pl] + bx], c.stride[pl],
-                        coef_ptr(lanes, r.coef_off, cb), r.tx, r.txtp, r.eob, h.bpp);
+                        coef_block(lanes, r.coef_off, r.ncoef, r.eob, r.tx, hbd, dense), r.tx, r.txtp, r.eob, h.bpp);
         }
     }
     /* phase 4: loop filter, superblocks in raster order */
@@ -344,7 +379,7 @@ int main(int argc, char **argv)
     if (!fp || !out) { perror("open"); return 2; }
     char magic[4]; uint32_t sz[8];
     rd(fp, magic, 4); rd(fp, sz, 32);
-    if (memcmp(magic, "V9R2", 4) || sz[0] != sizeof(Vp9CudaFrameHeader) || sz[2] != sizeof(Vp9CudaInterBlock) ||
+    if (memcmp(magic, "V9R3", 4) || sz[0] != sizeof(Vp9CudaFrameHeader) || sz[2] != sizeof(Vp9CudaInterBlock) ||
         sz[3] != sizeof(Vp9CudaTx) || sz[4] != sizeof(Vp9CudaIntraTx) || sz[7] != VP9CUDA_ABI_VERSION) {
         fprintf(stderr, "bad .v9r header\n"); return 2;
     }
@@ -354,14 +389,14 @@ int main(int argc, char **argv)
         if (memcmp(magic, "FRAM", 4)) { fprintf(stderr, "bad frame tag\n"); return 2; }
         Vp9CudaFrameHeader h; uint32_t n_sb;
         rd(fp, &h, sizeof(h)); rd(fp, &n_sb, 4);
-        const int cb = h.bpp > 8 ? 4 : 2;
+        const int ceb = h.bpp > 8 ? sizeof(Vp9CudaCoef32) : sizeof(Vp9CudaCoef16);
         std::vector<Lane> lanes(h.n_lanes);
         for (Lane &l : lanes) {
             rd(fp, &l.n, sizeof(l.n)); rd(fp, &l.coef_base, 4);
             l.blk.resize(l.n.blk); rd(fp, l.blk.data(), l.n.blk * sizeof(Vp9CudaInterBlock));
-            for (int t = 0; t < 4; t++) { l.tx[t].resize(l.n.tx[t]); rd(fp, l.tx[t].data(), l.n.tx[t] * sizeof(Vp9CudaTx)); }
+            l.tx.resize(l.n.tx); rd(fp, l.tx.data(), l.n.tx * sizeof(Vp9CudaTx));
             l.itx.resize(l.n.itx); rd(fp, l.itx.data(), l.n.itx * sizeof(Vp9CudaIntraTx));
-            l.coef.resize((size_t)l.n.coef * cb); rd(fp, l.coef.data(), l.coef.size());
+            l.coef.resize((size_t)l.n.coef * ceb); rd(fp, l.coef.data(), l.coef.size());
         }
         std::vector<Vp9CudaSbIndex> sbi(n_sb); rd(fp, sbi.data(), n_sb * sizeof(Vp9CudaSbIndex));
         std::vector<Vp9CudaLoopFilterSb> lf(n_sb); rd(fp, lf.data(), n_sb * sizeof(Vp9CudaLoopFilterSb));

@@ -26,18 +26,21 @@ def test_every_declared_symbol_is_exported():
 
 
 def test_struct_sizes_match_header():
-    assert v9r.BLK_SIZE == 48 and v9r.TX_SIZE == 12 and v9r.ITX_SIZE == 20
-    assert v9r.SBI_SIZE == 8 and v9r.LF_SIZE == 192
+    assert v9r.BLK_SIZE == 48 and v9r.TX_SIZE == 16 and v9r.ITX_SIZE == 20
+    assert v9r.SBI_SIZE == 16 and v9r.LF_SIZE == 192
     # header comments state the sizes; the dump writer stores sizeof() and the reader checks them
-    for n, sz in (("Vp9CudaInterBlock", 48), ("Vp9CudaTx", 12), ("Vp9CudaIntraTx", 20), ("Vp9CudaSbIndex", 8),
-                  ("Vp9CudaLoopFilterSb", 192)):
+    for n, sz in (("Vp9CudaInterBlock", 48), ("Vp9CudaTx", 16), ("Vp9CudaIntraTx", 20), ("Vp9CudaSbIndex", 16),
+                  ("Vp9CudaLoopFilterSb", 192), ("Vp9CudaCoef16", 4), ("Vp9CudaCoef32", 8)):
         assert re.search(r"}\s*%s;\s*/\*\s*%d bytes" % (n, sz), HEADER), n
-    assert C.sizeof(binding.LaneCounts) == v9r.COUNTS_DTYPE.itemsize == 28
-    assert C.sizeof(binding.LaneRing) == 104
+    assert C.sizeof(binding.LaneCounts) == v9r.COUNTS_DTYPE.itemsize == 16
+    assert C.sizeof(binding.LaneRing) == 72
 
 
 def test_version_string():
-    assert b"sm_100a" in binding.load().vp9cuda_version()
+    v = binding.load().vp9cuda_version()
+    assert b"sm_100a" in v
+    abi = int(re.search(r"#define VP9CUDA_ABI_VERSION\s+(\d+)", HEADER).group(1))
+    assert v.endswith(b"abi %d" % abi), v
 
 
 def test_no_cpu_fallback_without_gpu():

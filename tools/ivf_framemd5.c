@@ -11,7 +11,10 @@
  * 10-bit samples as little-endian 16-bit -- the byte string libavcodec/rawenc.c:52-60
  * hands to the framemd5 muxer.  IVF parsing follows libavformat/ivfdec.c:29-57.
  *
- * usage: ffvp9_ref [-threads N] [-thread_type frame|slice] [-null] [-raw out.yuv] in.ivf
+ * usage: ffvp9_ref [-threads N] [-thread_type frame|slice] [-null] [-raw out.yuv] [-loop K] in.ivf
+ *   -loop K feeds the packet list K times to the one decoder instance (the stream starts with a
+ *   key frame, so this is a K times longer stream); with K > 1 the first pass is the warm-up
+ *   and "fps=" is the rate of the K - 1 passes after it (bench.py: steady-state decode rate).
  */
 #include <stdio.h>
 #include <stdlib.h>
@@ -66,13 +69,14 @@ static void emit(AVFrame *f)
 
 int main(int argc, char **argv)
 {
-    int threads = 1, ttype = 0;
+    int threads = 1, ttype = 0, loops = 1;
     const char *in = NULL;
     for (int i = 1; i < argc; i++) {
         if (!strcmp(argv[i], "-threads") && i + 1 < argc) threads = atoi(argv[++i]);
         else if (!strcmp(argv[i], "-thread_type") && i + 1 < argc)
             ttype = !strcmp(argv[++i], "slice") ? FF_THREAD_SLICE : FF_THREAD_FRAME;
         else if (!strcmp(argv[i], "-null")) do_hash = 0;
+        else if (!strcmp(argv[i], "-loop") && i + 1 < argc) loops = atoi(argv[++i]);
         else if (!strcmp(argv[i], "-raw") && i + 1 < argc) raw = fopen(argv[++i], "wb");
         else in = argv[i];
     }
@@ -102,34 +106,53 @@ int main(int argc, char **argv)
 
     AVPacket *pkt = av_packet_alloc();
     AVFrame *fr = av_frame_alloc();
-    long pos = rl32(buf + 4) >> 16 ? 32 : 32; /* header length field is 16-bit at +6; always 32 */
     int rc = 0, npkt = 0;
-    double t0 = now_s();
-    while (pos + 12 <= sz) {
-        unsigned fsz = rl32(buf + pos);
-        if (pos + 12 + fsz > sz) { fprintf(stderr, "truncated IVF\n"); rc = 1; break; }
-        /* the packet payload must be padded: copy into an av_new_packet */
-        if (av_new_packet(pkt, fsz) < 0) return 2;
-        memcpy(pkt->data, buf + pos + 12, fsz);
-        pkt->pts = pkt->dts = rl32(buf + pos + 4);
-        pos += 12 + fsz;
-        int r = avcodec_send_packet(c, pkt);
-        av_packet_unref(pkt);
-        /* a damaged packet is reported and skipped, the following packets are still decoded and the
-         * decoder is drained at the end (what fftools does): the exit code says that something failed */
-        if (r < 0) { fprintf(stderr, "decode error %d at packet %d\n", r, npkt); rc = 1; }
-        npkt++;
-        while ((r = avcodec_receive_frame(c, fr)) >= 0) { emit(fr); av_frame_unref(fr); }
-        if (r != AVERROR(EAGAIN) && r != AVERROR_EOF) { fprintf(stderr, "decode error %d\n", r); rc = 1; }
+    double t0 = now_s(), t1 = t0;
+    int frames_warm = 0;
+    for (int pass = 0; pass < (loops < 1 ? 1 : loops); pass++) {
+        long pos = 32;                  /* IVF file header */
+        if (pass == 1) {                /* the timed region starts with the second pass */
+            t1 = now_s();
+            frames_warm = nframes;
+        }
+        while (pos + 12 <= sz) {
+            unsigned fsz = rl32(buf + pos);
+            if (pos + 12 + fsz > sz) { fprintf(stderr, "truncated IVF\n"); rc = 1; break; }
+            /* the packet payload must be padded: copy into an av_new_packet */
+            if (av_new_packet(pkt, fsz) < 0) return 2;
+            memcpy(pkt->data, buf + pos + 12, fsz);
+            pkt->pts = pkt->dts = rl32(buf + pos + 4);
+            pos += 12 + fsz;
+            int r = avcodec_send_packet(c, pkt);
+            av_packet_unref(pkt);
+            /* a damaged packet is reported and skipped, the following packets are still decoded and the
+             * decoder is drained at the end (what fftools does): the exit code says that something failed */
+            if (r < 0) { fprintf(stderr, "decode error %d at packet %d\n", r, npkt); rc = 1; }
+            npkt++;
+            /* under frame threading a packet's error surfaces here, some packets later: report it and go on */
+            for (;;) {
+                r = avcodec_receive_frame(c, fr);
+                if (r >= 0) { emit(fr); av_frame_unref(fr); continue; }
+                if (r == AVERROR(EAGAIN) || r == AVERROR_EOF) break;
+                fprintf(stderr, "decode error %d\n", r); rc = 1;
+            }
+        }
     }
     {
         avcodec_send_packet(c, NULL);
-        int r;
-        while ((r = avcodec_receive_frame(c, fr)) >= 0) { emit(fr); av_frame_unref(fr); }
-        if (r != AVERROR_EOF && r != AVERROR(EAGAIN)) { fprintf(stderr, "decode error %d at drain\n", r); rc = 1; }
+        for (int guard = 0; guard < 1000; guard++) {
+            int r = avcodec_receive_frame(c, fr);
+            if (r >= 0) { emit(fr); av_frame_unref(fr); continue; }
+            if (r == AVERROR_EOF || r == AVERROR(EAGAIN)) break;
+            fprintf(stderr, "decode error %d at drain\n", r); rc = 1;
+        }
     }
-    double dt = now_s() - t0;
-    fprintf(stderr, "frames=%d seconds=%.6f fps=%.3f threads=%d\n", nframes, dt, nframes / dt, threads);
+    double t2 = now_s();
+    if (loops > 1)   /* frames still inside the decoder at t1 are counted with the timed passes: a steady-state rate */
+        fprintf(stderr, "frames=%d seconds=%.6f fps=%.3f threads=%d first_pass_fps=%.3f loops=%d\n", nframes - frames_warm,
+                t2 - t1, (nframes - frames_warm) / (t2 - t1), threads, frames_warm / (t1 - t0), loops);
+    else
+        fprintf(stderr, "frames=%d seconds=%.6f fps=%.3f threads=%d\n", nframes, t2 - t0, nframes / (t2 - t0), threads);
     if (raw) fclose(raw);
     av_frame_free(&fr);
     av_packet_free(&pkt);
