@@ -60,9 +60,11 @@ def load() -> C.CDLL:
     """dlopen libvp9cuda.so; raises if it is not built (no CPU fallback exists)."""
     global _lib
     if _lib is None:
-        if not LIB_PATH.exists():
-            raise RuntimeError(f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'`")
-        lib = C.CDLL(str(LIB_PATH))
+        import os
+        path = Path(os.environ.get("VP9CUDA_LIB", LIB_PATH))      # instrumented builds for the profiling tools
+        if not path.exists():
+            raise RuntimeError(f"{path} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'`")
+        lib = C.CDLL(str(path))
         lib.vp9cuda_version.restype = C.c_char_p
         lib.vp9cuda_host_alloc.restype = C.c_void_p
         lib.vp9cuda_host_alloc.argtypes = [C.c_size_t]

@@ -42,6 +42,25 @@ struct IntraRec {
     uint32_t coef_off;               /* first entry in the frame's coefficient stream */
 };
 
+/* What the intra wavefront needs per transform block, with every address that does not depend on
+ * pixel values worked out by the pre-pass (k_intra_prep): byte offsets into the wavefront CTA's
+ * shared memory (pixel rings, IntraSmem) and limits of the edge rules of check_intra_mode
+ * (vp9recon.c:72-221).  The dependent chain of the wavefront then is: this record -> edge samples ->
+ * predictor taps -> store. */
+struct IntraBlk {
+    uint32_t dst;                    /* pixel (0,0) of the block */
+    uint32_t top;                    /* sample 0 of the row above it */
+    uint32_t tl;                     /* the top-left sample (may wrap to the ring's last column) */
+    uint32_t left;                   /* the sample left of row 0 */
+    uint16_t res;                    /* the block's first residual in the superblock's residual tile */
+    uint8_t mode;                    /* edge-converted prediction mode */
+    uint8_t lg;                      /* log2 of the block size: 2..5 */
+    uint8_t klim;                    /* last sample of the row above the block may read (replicated beyond) */
+    uint8_t hlim;                    /* last row whose left sample exists */
+    uint8_t flags;                   /* 1 left, 2 top, 4 has residual, 8 real top-left, 16 chroma */
+    uint8_t pad[9];
+};                                   /* 32 bytes */
+
 /* Everything a kernel needs to know about the frame being reconstructed. */
 struct FrameDesc {
     SurfDesc cur;
@@ -65,6 +84,7 @@ struct FrameDesc {
     int32_t *cellmap;              /* cols*rows: index into blk, -1 = not inter */
     IntraSb *isb;                  /* [sb] intra work of each superblock */
     IntraRec *irec;                /* n_itx records regrouped per superblock, sorted by depth */
+    IntraBlk *iblk;                /* the same blocks as the wavefront reads them */
     int *iprogress;                /* [2][sb_rows] intra wavefront counters: border row stored, superblock stored */
     int lf_follow;                 /* the loop filter runs beside the intra wavefront (k_wave) */
     uint16_t *itab;                /* [sb][768] per-step chunk tables (k_intra_prep) */

@@ -47,6 +47,7 @@ namespace vp9 {
 #define INTRA_SB_RECS 384                   /* 256 luma + 2 x 64 chroma 4x4 blocks */
 #define INTRA_SB_RES 6144                   /* residual tile: 64*64 + 2 * 32*32 int16 */
 #define INTRA_SB_TAB 768                    /* work table: <= 384 chunk entries + <= 384 step headers */
+#define INTRA_EDGE_N 104                    /* per compute warp: top[0..64] (0 = top-left) at 0, left[0..31] at 72 */
 
 __device__ __forceinline__ void cp16(void *smem, const void *gmem)
 {
@@ -55,6 +56,9 @@ __device__ __forceinline__ void cp16(void *smem, const void *gmem)
 }
 __device__ __forceinline__ void cp_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
 template <int N> __device__ __forceinline__ void cp_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
+
+/* residual tile of one superblock: luma 64x64 row-major, then U 32x32, then V 32x32 (int16) */
+__device__ __forceinline__ int res_plane_off(int pl) { return pl == 0 ? 0 : pl == 1 ? 4096 : 5120; }
 
 /* 32-pixel chunks a block is dealt out in (a 4x4 block is one half-filled chunk) */
 __device__ __forceinline__ int intra_chunks(int tx) { return tx == 0 ? 1 : 2 << (2 * (tx - 1)); }
@@ -202,6 +206,32 @@ __global__ void __launch_bounds__(128) k_intra_prep(const __grid_constant__ Fram
         o.ncoef = r.ncoef;
         o.coef_off = r.coef_off;
         f.irec[g0 + k] = o;
+        /* the wavefront's view of the block: addresses in its shared-memory rings (layout: IntraSmem) */
+        {
+            const int ps = f.bpp > 8 ? 2 : 1, rsby = 256 * ps + 16, rsbc = 128 * ps + 16;
+            const int pl = r.plane, ch = pl > 0, S = 64 >> ch, N = 4 << r.tx, rsb = ch ? rsbc : rsby;
+            const int o_pl = pl == 0 ? 0 : pl == 1 ? 65 * rsby : 65 * rsby + 33 * rsbc;
+            const int bx = (sbx & 3) * S + o.lx * 4, by = 1 + o.ly * 4, xmask = 4 * S - 1;
+            const bool have_left = o.flags & 1, have_right = o.flags & 2, have_top = o.flags & 4;
+            const int avail_w = ((f.cols * 8) >> ch) - (sbx * S + o.lx * 4);
+            const int avail_h = ((f.rows * 8) >> ch) - (sby * S + o.ly * 4);
+            const int needs = intra_mode_needs(o.mode);
+            IntraBlk b;
+            b.dst = o_pl + by * rsb + bx * ps;
+            b.top = o_pl + (by - 1) * rsb + bx * ps;
+            b.tl = o_pl + (by - 1) * rsb + ((bx - 1) & xmask) * ps;
+            b.left = o_pl + by * rsb + ((bx - 1) & xmask) * ps;
+            b.res = (uint16_t)(res_plane_off(pl) + o.ly * 4 * S + o.lx * 4);
+            b.mode = o.mode;
+            b.lg = (uint8_t)(2 + r.tx);
+            /* beyond the block: the real top-right only for 4x4 blocks that may read it, else replicate */
+            b.klim = (uint8_t)min((N == 4 && (needs & 8) && have_right && avail_w >= 8) ? 7 : N - 1, avail_w - 1);
+            b.hlim = (uint8_t)min(N - 1, avail_h - 1);
+            b.flags = (uint8_t)((have_left ? 1 : 0) | (have_top ? 2 : 0) | (r.eob ? 4 : 0) | ((have_left && have_top) ? 8 : 0) |
+                                (ch ? 16 : 0));
+            for (int q = 0; q < 9; q++) b.pad[q] = 0;
+            f.iblk[g0 + k] = b;
+        }
     }
     /* work table: thread t owns sorted records 4t .. 4t+3; two block-wide exclusive scans give every
      * record the chunks and the step headers in front of it */
@@ -267,8 +297,6 @@ __global__ void __launch_bounds__(128) k_intra_prep(const __grid_constant__ Fram
 }
 
 /* ---------------------------------------------------------------------------------------------- */
-/* residual tile of one superblock: luma 64x64 row-major, then U 32x32, then V 32x32 (int16) */
-__device__ __forceinline__ int res_plane_off(int pl) { return pl == 0 ? 0 : pl == 1 ? 4096 : 5120; }
 
 struct ResBlk {
     int16_t *p; int stride;
@@ -323,18 +351,6 @@ template <class P> struct TilePx {
     __device__ __forceinline__ int operator()(int x, int y) const { return *(const P *)(t + y * rsb + (x & mask) * (int)sizeof(P)); }
 };
 
-/* edge samples evaluated on the fly from the ring (same rules as intra_edges, vp9_pred.h) */
-template <class P> struct TileEdges {
-    TilePx<P> px;
-    int bx, by, N, needs, avail_w, avail_h, bpp;
-    bool have_top, have_left, have_right;
-    __device__ __forceinline__ int top(int i) const
-    {
-        return intra_edge_top(px, i, bx, by, N, needs, have_top, have_left, have_right, avail_w, bpp);
-    }
-    __device__ __forceinline__ int left(int y) const { return intra_edge_left(px, y, bx, by, have_left, avail_h, bpp); }
-};
-
 template <class P> struct IntraSmem {
     static constexpr int RSBY = 4 * 64 * (int)sizeof(P) + 16;      /* luma ring row stride, bytes */
     static constexpr int RSBC = 4 * 32 * (int)sizeof(P) + 16;
@@ -342,10 +358,11 @@ template <class P> struct IntraSmem {
     static constexpr int O_U = O_Y + 65 * RSBY;
     static constexpr int O_V = O_U + 33 * RSBC;
     static constexpr int O_RES = O_V + 33 * RSBC;                  /* [4][INTRA_SB_RES] int16 */
-    static constexpr int O_REC = O_RES + 4 * INTRA_SB_RES * 2;     /* [4][INTRA_SB_RECS] IntraRec */
-    static constexpr int O_TAB = O_REC + 4 * INTRA_SB_RECS * (int)sizeof(IntraRec);   /* [4][INTRA_SB_TAB] u16 */
+    static constexpr int O_REC = O_RES + 4 * INTRA_SB_RES * 2;     /* [4][INTRA_SB_RECS] IntraBlk */
+    static constexpr int O_TAB = O_REC + 4 * INTRA_SB_RECS * (int)sizeof(IntraBlk);   /* [4][INTRA_SB_TAB] u16 */
     static constexpr int O_INFO = O_TAB + 4 * INTRA_SB_TAB * 2;
-    static constexpr int BYTES = O_INFO + INTRA_MAX_SB_COLS * (int)sizeof(IntraSb);
+    static constexpr int O_EDGE = O_INFO + INTRA_MAX_SB_COLS * (int)sizeof(IntraSb);   /* [INTRA_CW][INTRA_EDGE_N] int */
+    static constexpr int BYTES = O_EDGE + INTRA_CW * INTRA_EDGE_N * 4;
 };
 
 #define ICLK(k) do { if (f.phase_clk) { long long c_ = clock64(); \
@@ -358,7 +375,7 @@ __device__ __forceinline__ void intra_row(const FrameDesc &f, const int row, uns
     typedef IntraSmem<P> L;
     auto tile = [&](int pl) -> unsigned char * { return sm + (pl == 0 ? L::O_Y : pl == 1 ? L::O_U : L::O_V); };
     int16_t *const resbuf = (int16_t *)(sm + L::O_RES);
-    IntraRec *const recbuf = (IntraRec *)(sm + L::O_REC);
+    IntraBlk *const recbuf = (IntraBlk *)(sm + L::O_REC);
     uint16_t *const tabbuf = (uint16_t *)(sm + L::O_TAB);
     const IntraSb *const info = (const IntraSb *)(sm + L::O_INFO);
     const int ncol = f.sb_cols;
@@ -394,51 +411,63 @@ __device__ __forceinline__ void intra_row(const FrameDesc &f, const int row, uns
 #ifdef VP9CUDA_STEPSTATS   /* counters for tools/prof_frames.py; the chain is so tight that they cost ~4 % of the wavefront */
             int nsteps = 0, nrounds = 0, nchunks = 0, ntop = info[c].needs_top;
 #endif
-            const IntraRec *rec = recbuf + (c & 3) * INTRA_SB_RECS;
+            const IntraBlk *rec = recbuf + (c & 3) * INTRA_SB_RECS;
             const int16_t *res = resbuf + (c & 3) * INTRA_SB_RES;
             const uint16_t *tab = tabbuf + (c & 3) * INTRA_SB_TAB;
             const int ntab = info[c].ntab;
+            const int base = 128 << (f.bpp - 8);
+            int *const T = (int *)(sm + L::O_EDGE) + warp * INTRA_EDGE_N, *const Lf = T + 72;
             for (int pos = 0; pos < ntab;) {
                 const int cnt = tab[pos] & 0x7fff;
                 for (int i = warp; i < cnt; i += INTRA_CW) {
                     const unsigned ent = tab[pos + 1 + i];
-                    const IntraRec r = rec[ent & 511];
+                    const uint4 w0 = *(const uint4 *)&rec[ent & 511];                       /* dst, top, tl, left */
+                    const uint2 w1 = *(const uint2 *)((const unsigned char *)&rec[ent & 511] + 16);
                     const int q = ent >> 9 & 31;
-                    const int pl = r.plane, ch = pl > 0;
-                    const int N = 4 << r.tx, S = 64 >> ch;
-                    const int rsb = ch ? L::RSBC : L::RSBY;
-                    unsigned char *tl = tile(pl);
-                    TileEdges<P> e;
-                    e.px.t = tl; e.px.rsb = rsb; e.px.mask = 4 * S - 1;
-                    e.bx = (c & 3) * S + r.lx * 4; e.by = 1 + r.ly * 4;            /* ring coordinates */
-                    e.N = N; e.bpp = f.bpp;
-                    e.have_left = r.flags & 1; e.have_right = r.flags & 2; e.have_top = r.flags & 4;
-                    const int mode = r.mode;                                        /* already edge-converted */
-                    e.needs = intra_mode_needs(mode);
-                    e.avail_w = ((f.cols * 8) >> ch) - (c * S + r.lx * 4);
-                    e.avail_h = ((f.rows * 8) >> ch) - (row * S + r.ly * 4);
+                    const int mode = w1.x >> 16 & 0xff, lg = w1.x >> 24, N = 1 << lg;
+                    const int klim = w1.y & 0xff, hlim = w1.y >> 8 & 0xff, flags = w1.y >> 16 & 0xff;
+                    const int rsb = (flags & 16) ? L::RSBC : L::RSBY;
+                    /* Edge samples once per chunk (rules of check_intra_mode, vp9recon.c:72-221, already turned
+                     * into limits by the pre-pass; same values as intra_edges, vp9_pred.h): lane l fetches top[l]
+                     * (0 = top-left, 1 + k = sample k above) and left[l] into the warp's own arrays, then the
+                     * predictor indexes them freely. */
+                    int tv = base - 1, lv = base + 1;
+                    if (flags & 2)
+                        tv = *(const P *)(sm + w0.y + min(lane - 1, klim) * (int)sizeof(P));
+                    if (lane == 0)
+                        tv = (flags & 8) ? (int)*(const P *)(sm + w0.z) : base + ((flags & 2) ? 1 : -1);
+                    if (flags & 1)
+                        lv = *(const P *)(sm + w0.w + min(lane, hlim) * rsb);
+                    T[lane] = tv;
+                    Lf[lane] = lv;
+                    if (N >= 16) {                       /* top[32 ..]: all of them the last sample the block may read */
+                        const int rep = (flags & 2) ? (int)*(const P *)(sm + w0.y + klim * (int)sizeof(P)) : base - 1;
+                        if (N == 32) T[32 + lane] = rep;
+                        if (lane == 0) T[N == 32 ? 64 : 32] = rep;
+                    }
                     int dc = 0;
                     if (mode == DC_PRED || mode == LEFT_DC_PRED || mode == TOP_DC_PRED) {
-                        /* intra_dc's sums (vp9_pred.h), lane-parallel */
+                        /* intra_dc's sums (vp9_pred.h), lane-parallel: lane l holds top[l] and left[l] */
                         int sum = 0;
-                        if (lane < N) {
-                            if (mode != LEFT_DC_PRED) sum += e.top(1 + lane);
-                            if (mode != TOP_DC_PRED) sum += e.left(lane);
-                        }
+                        if (mode != LEFT_DC_PRED && lane >= 1 && lane <= min(N, 31)) sum += tv;
+                        if (mode != TOP_DC_PRED && lane < N) sum += lv;
                         sum = __reduce_add_sync(0xffffffffu, sum);
-                        const int lg = 2 + r.tx;
+                        if (N == 32 && mode != LEFT_DC_PRED)
+                            sum += (flags & 2) ? (int)*(const P *)(sm + w0.y + min(31, klim) * (int)sizeof(P)) : base - 1;
                         dc = mode == DC_PRED ? (sum + N) >> (lg + 1) : (sum + (N >> 1)) >> lg;
                     } else if (mode >= DC_128_PRED) {
-                        dc = (128 << (f.bpp - 8)) + (mode == DC_127_PRED ? -1 : mode == DC_129_PRED ? 1 : 0);
+                        dc = base + (mode == DC_127_PRED ? -1 : mode == DC_129_PRED ? 1 : 0);
                     }
+                    __syncwarp();
                     const int p = q * 32 + lane;
                     if (p < N * N) {
-                        const int x = p & (N - 1), y = p >> (2 + r.tx);
-                        int v = intra_pixel_e(mode, N, x, y, e, dc, f.bpp);
-                        if (r.eob)
-                            v = clip_pixel(v + res[res_plane_off(pl) + (r.ly * 4 + y) * S + r.lx * 4 + x], f.bpp);
-                        *((P *)(tl + (e.by + y) * rsb) + e.bx + x) = (P)v;
+                        const int x = p & (N - 1), y = p >> lg;
+                        int v = intra_pixel(mode, N, x, y, T, Lf, dc, f.bpp);
+                        if (flags & 4)
+                            v = clip_pixel(v + res[(w1.x & 0xffff) + (y << ((flags & 16) ? 5 : 6)) + x], f.bpp);
+                        *(P *)(sm + w0.x + y * rsb + x * (int)sizeof(P)) = (P)v;
                     }
+                    __syncwarp();                        /* the arrays are rewritten by this warp's next chunk */
                 }
                 asm volatile("bar.sync 1, %0;\n" ::"n"(INTRA_CT) : "memory");
                 pos += cnt + 1;
@@ -501,9 +530,9 @@ __device__ __forceinline__ void intra_row(const FrameDesc &f, const int row, uns
                 }
             }
             if (sj.count > 0) {
-                const unsigned char *rs = (const unsigned char *)(f.irec + sj.start);
+                const unsigned char *rs = (const unsigned char *)(f.iblk + sj.start);
                 unsigned char *rd = (unsigned char *)(recbuf + (j & 3) * INTRA_SB_RECS);
-                for (int i = lane; i < sj.count; i += 32)
+                for (int i = lane; i < 2 * sj.count; i += 32)
                     cp16(rd + 16 * i, rs + 16 * i);
                 const unsigned char *ts = (const unsigned char *)(f.itab + (size_t)(row * ncol + j) * INTRA_SB_TAB);
                 unsigned char *td = (unsigned char *)(tabbuf + (j & 3) * INTRA_SB_TAB);

@@ -144,7 +144,7 @@ struct HBuf {
  * staged path: lanes packed back to back). */
 struct DevRecords {
     DBuf blk, tx, itx, coef, sb_index, lf;
-    DBuf cellmap, isb, irec, ires, itab, iprogress, lfops, progress, misc;
+    DBuf cellmap, isb, irec, iblk, ires, itab, iprogress, lfops, progress, misc;
     uint32_t lane_blk_base[VP9CUDA_MAX_LANES] = { 0 }, lane_tx_base[VP9CUDA_MAX_LANES] = { 0 },
              lane_itx_base[VP9CUDA_MAX_LANES] = { 0 };
     uint32_t lane_blk_cnt[VP9CUDA_MAX_LANES] = { 0 }, lane_tx_cnt[VP9CUDA_MAX_LANES] = { 0 };
@@ -184,6 +184,7 @@ struct DevRecords {
         r |= cellmap.reserve((size_t)cols * rows * 4, allocs);
         r |= isb.reserve((size_t)n_sb * sizeof(IntraSb), allocs);
         r |= irec.reserve(cap_itx * sizeof(IntraRec), allocs);
+        r |= iblk.reserve(cap_itx * sizeof(IntraBlk), allocs);
         if (intra) r |= ires.reserve((size_t)n_sb * INTRA_SB_RES * 2, allocs);
         if (intra) r |= itab.reserve((size_t)n_sb * INTRA_SB_TAB * 2, allocs);
         r |= iprogress.reserve((size_t)2 * sb_rows * 4, allocs);
@@ -201,7 +202,7 @@ struct DevRecords {
         if (inter_done) cudaEventDestroy(inter_done);
         uploaded = dev_free = prepped = cellmapped = inter_done = nullptr;
         blk.release(); tx.release(); itx.release(); coef.release(); sb_index.release(); lf.release();
-        misc.release(); cellmap.release(); isb.release(); irec.release(); ires.release(); itab.release(); iprogress.release(); lfops.release();
+        misc.release(); cellmap.release(); isb.release(); irec.release(); iblk.release(); ires.release(); itab.release(); iprogress.release(); lfops.release();
         progress.release();
     }
 };
@@ -762,6 +763,7 @@ static int reconstruct(Vp9CudaCtx *c, DevRecords &d, uint8_t *const out_planes[3
     f.cellmap = (int32_t *)d.cellmap.p;
     f.isb = (IntraSb *)d.isb.p;
     f.irec = (IntraRec *)d.irec.p;
+    f.iblk = (IntraBlk *)d.iblk.p;
     f.iprogress = (int *)d.iprogress.p;
     f.ires = (int16_t *)d.ires.p;
     f.itab = (uint16_t *)d.itab.p;

@@ -359,6 +359,10 @@ static int dump_abort_frame(Vp9CudaCtx *c, uint32_t id)
 }
 
 static int dump_wait(Vp9CudaCtx *c, uint64_t t) { return 0; }
+/* output pictures come from the same size-stable pool as with the back end (plain memory here), so
+ * that the entropy-only decoder differs from the real one in the missing reconstruction only */
+static void *dump_host_alloc(size_t n) { return av_malloc(n); }
+static void dump_host_free(void *p) { av_free(p); }
 
 /* ------------------------------------------------------------------------------------------ */
 
@@ -464,7 +468,8 @@ static int shared_create(AVCodecContext *avctx, VP9CudaGlue *g)
     pthread_mutex_init(&sh->pool_mu, NULL);
     if (getenv("VP9CUDA_DUMP")) {
         sh->api = (SinkApi){ dump_create, dump_destroy, dump_flush, dump_begin_frame, dump_tile_ring,
-                             dump_submit_tile, dump_finish_frame, dump_abort_frame, dump_wait };
+                             dump_submit_tile, dump_finish_frame, dump_abort_frame, dump_wait,
+                             dump_host_alloc, dump_host_free };
     } else {
         const char *lib = getenv("VP9CUDA_LIB");
         sh->dl = dlopen(lib ? lib : "libvp9cuda.so", RTLD_NOW | RTLD_LOCAL);

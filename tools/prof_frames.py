@@ -32,7 +32,7 @@ def main():
         ctx.option("reset_stats")
         ctx.wait(ctx.run_staged(h))
         st = ctx.kernel_stats()
-        itx = np.frombuffer(b"".join(l.itx for l in raw[i].lanes), dtype=np.dtype([("x4", "<u2"), ("y4", "<u2"), ("eob", "<u2"), ("level", "<u2"), ("p", "u1"), ("tx", "u1"), ("m", "u1"), ("tt", "u1"), ("f", "u1"), ("pad", "u1", (3,)), ("c", "<u4")]))
+        itx = np.frombuffer(b"".join(l.itx for l in raw[i].lanes), dtype=v9r.ITX_DTYPE)
         nlv = int(itx["level"].max()) + 1 if len(itx) else 0
         if names is None:
             names = [k for k in st]
