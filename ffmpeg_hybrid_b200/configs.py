@@ -192,6 +192,26 @@ def small_variants() -> Dict[str, StreamSpec]:
         FrameSpec(refreshrefmask=0x80, refidx=(7, 3, 1), size_from_ref=2, signbias=(1, 0, 0), **kw),
     ]
     out["keyresize"] = st
+    st = StreamSpec(640, 384, seed=25)                       # fixed bilinear filter at 1/16-pel precision with
+    st.frames = _ippp(9, compound=True)                      # compound prediction on 64-wide blocks: the bilinear
+    for f in st.frames[1:]:                                  # mc slots the switchable streams rarely reach
+        f.filtermode = 3
+    out["bilinear"] = st
+    st = StreamSpec(640, 384, seed=26)                       # scaled references (2:1 down and up) under every fixed
+    kw = dict(txfmmode=TX_SWITCHABLE)                        # filter, single and compound: the smc slots
+    st.frames = [FrameSpec(keyframe=True, refreshrefmask=0xFF),
+                 FrameSpec(show=False, width=320, height=192, refreshrefmask=1 << 3, refidx=(0, 1, 2),
+                           signbias=(0, 0, 1), filtermode=3, **kw)]
+    for i, fm in enumerate((3, 0, 2, 1, 3, 0, FILTER_SWITCHABLE, 0)):
+        st.frames.append(FrameSpec(refreshrefmask=1 << (i % 3), refidx=(3, 0, 3) if i % 2 else (0, 3, 3),
+                                   signbias=(0, 0, 1), filtermode=fm, **kw))
+    out["scale_filters"] = st
+    st = StreamSpec(1024, 576, seed=27)                      # many 64- and 32-wide compound blocks under each fixed
+    st.frames = _ippp(11, tile_cols=1, compound=True)        # 8-tap filter with quarter-pel vectors (integer phase in
+    for i, f in enumerate(st.frames[1:]):                    # one direction only is common then)
+        f.filtermode = (0, 2, 0, 2, 1, 0, 2, 3, 0, 2)[i]
+        f.highprecisionmvs = False
+    out["wide64"] = st
     st = StreamSpec(72, 40, seed=11)                         # tiny, single superblock column
     st.frames = _ippp(4, compound=True)
     out["tiny"] = st
