@@ -5,7 +5,12 @@
 #ifndef VP9CUDA_DEV_COMMON_CUH
 #define VP9CUDA_DEV_COMMON_CUH
 
+#ifdef VP9_EMU                      /* host emulation of a kernel inside the CPU tests (oracle/cuda_emu.h) */
+#include "cuda_emu.h"
+#else
 #include <cuda_runtime.h>
+#define VP9_DYN_SMEM(name) extern __shared__ __align__(16) unsigned char name[]
+#endif
 #include <stdint.h>
 #include <stdio.h>
 
@@ -94,6 +99,8 @@ struct FrameDesc {
     int *mv_reach;                 /* max vertical motion vector component of this frame, 1/8 pel (k_cellmap) */
     int tile_y0;                   /* k_inter: first 32-row tile row of this launch (the frame may be launched in bands) */
     unsigned long long *phase_clk; /* optional: per-phase clock accumulation (profiling), or NULL */
+    int *err;                      /* context error word (device memory): non-zero = a wavefront wait gave up */
+    int *err_host;                 /* the same, host-mapped: what vp9cuda_wait reads */
     uint8_t lim_lut[64], mblim_lut[64];
 };
 
@@ -136,7 +143,23 @@ __device__ int *g_wd_buf;
     q_[1] = (int)(a); q_[2] = (int)(b); q_[0] = __LINE__; \
     while (cond) { if ((ns) > 0) __nanosleep(ns); } q_[0] = -__LINE__; } while (0)
 #else
-#define VP9_SPIN(cond, ns, tag, a, b) do { while (cond) { if ((ns) > 0) __nanosleep(ns); } } while (0)
+/* Production build: a wait that lasts longer than VP9_SPIN_BUDGET clock cycles (~4 s) is a broken
+ * dependency (the wavefronts rely on CTAs being dispatched in block-index order, which CUDA does not
+ * promise).  The waiter then sets the context's error word -- f.err[0] in device memory, polled by
+ * every other wait of the context once per 1024 polls, and f.err_host[0] in host-mapped memory, read
+ * by vp9cuda_wait -- and gives up; every other wait gives up as soon as it sees the word, the launch
+ * drains, and the host reports -EIO for the frame instead of sitting on a hung GPU. */
+#ifndef VP9_SPIN_BUDGET
+#define VP9_SPIN_BUDGET (8ll << 30)
+#endif
+#define VP9_SPIN(cond, ns, tag, a, b) do { unsigned n_ = 0; long long t0_ = 0; \
+    while (cond) { if ((ns) > 0) __nanosleep(ns); \
+        if ((++n_ & 1023u) == 0 && f.err) { \
+            if (*(volatile int *)f.err) break; \
+            const long long now_ = clock64(); \
+            if (!t0_) t0_ = now_; \
+            else if (now_ - t0_ > VP9_SPIN_BUDGET) { \
+                atomicExch(f.err, __LINE__); *(volatile int *)f.err_host = __LINE__; __threadfence_system(); break; } } } } while (0)
 #endif
 
 template <class P> __device__ __forceinline__ P ld_cg(const P *p);

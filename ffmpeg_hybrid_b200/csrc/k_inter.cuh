@@ -224,8 +224,11 @@ __device__ __forceinline__ void inter_strip(const FrameDesc &f, const Vp9CudaInt
  * luma-scale row Y is final with loop-filter row (Y + 16) >> 6 at the latest; rows finish top
  * down.  Reach below the band's last row: integer motion (k_cellmap's maximum) + 4 taps, with
  * slack for the rounding of the chroma / sub-8x8 average vectors. */
-__global__ void k_inter_gate(const int *dep_done, int dep_rows, int dep_whole, const int *mv_reach, int y_last)
+__global__ void k_inter_gate(const int *dep_done, int dep_rows, int dep_whole, const int *mv_reach, int y_last,
+                             int *err, int *err_host)
 {
+    struct { int *err, *err_host; } f = { err, err_host };      /* what VP9_SPIN reports to */
+    (void)f;
     if (threadIdx.x == 0) {
         int need = dep_rows - 1;
         if (!dep_whole)

@@ -55,8 +55,10 @@ __device__ __forceinline__ void itx_entries(const typename ItxTypes<HBD>::E *__r
 /* RES = true: instead of adding to the picture, put() receives the rounded residual clamped to
  * [-2^bpp, 2^bpp] -- clip_pixel(pred + r) is the same for every pred in [0, 2^bpp) whether or not
  * r was clamped to that range, so a later `clip_pixel(pred + residual)` is bit-exact. */
+/* `tmp` may be the same memory as `blk` (the fused inter kernel has room for one block per warp):
+ * every lane has its inputs in registers before any lane writes an intermediate. */
 template <bool HBD, int N, class Pix, bool RES = false>
-__device__ __forceinline__ void itx_block(const typename ItxTypes<HBD>::C *__restrict__ blk,
+__device__ __forceinline__ void itx_block(const typename ItxTypes<HBD>::C *blk,
                                           typename ItxTypes<HBD>::C *tmp, int lane, int txtp, int eob,
                                           int bpp, Pix &pix, unsigned syncmask)
 {
@@ -78,6 +80,7 @@ __device__ __forceinline__ void itx_block(const typename ItxTypes<HBD>::C *__res
 #pragma unroll
         for (int x = 0; x < 4; x++) in[x] = W32((int64_t)blk[lane + x * 4]);
         iwht4(in, 1, out, 0);
+        __syncwarp(syncmask);
 #pragma unroll
         for (int x = 0; x < 4; x++) tmp[lane * 5 + x] = (C)out[x].v;
         __syncwarp(syncmask);
@@ -95,6 +98,7 @@ __device__ __forceinline__ void itx_block(const typename ItxTypes<HBD>::C *__res
 #pragma unroll
         for (int x = 0; x < N; x++) in[x] = T((int64_t)blk[lane + x * N]);
         itx_1d<T, N>(in, out, (txtp & 1) && N < 32);
+        __syncwarp(syncmask);
 #pragma unroll
         for (int x = 0; x < N; x++) tmp[lane * (N + 1) + x] = (C)out[x].v;
         __syncwarp(syncmask);

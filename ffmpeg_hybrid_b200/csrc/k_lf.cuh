@@ -461,6 +461,10 @@ __global__ void __launch_bounds__(INTRA_THREADS, VP9_WAVE_CTAS_PER_SM) k_wave(co
     extern __shared__ __align__(16) unsigned char sm[];
     __shared__ IntraSig isig;
     __shared__ LfSig lsig;
+    /* test hook (set_option "inject_stall"): CTA 0 waits for something that never happens, so that the
+     * budget of VP9_SPIN, the error word and the draining of the launch can be exercised */
+    if ((f.lf_follow & 4) && blockIdx.x == 0 && threadIdx.x == 0)
+        VP9_SPIN(true, 100, "injected stall", 0, 0);
     if ((int)blockIdx.x < f.sb_rows)
         intra_row<P>(f, blockIdx.x, sm, isig);
     else

@@ -33,6 +33,7 @@
 #include "dev_common.cuh"
 #include "k_inter.cuh"
 #include "k_itx.cuh"
+#include "k_inter_sb.cuh"
 #include "k_intra.cuh"
 #include "k_lf.cuh"
 
@@ -254,6 +255,9 @@ struct Vp9CudaCtx {
     int follow_mask = 3;                   /* debugging: 1 = wait for intra write-back, 2 = wait for the intra row below */
     bool trace = false;                    /* VP9CUDA_TRACE: one stderr line per submitted / finished frame */
     bool fuse_wave = true;                 /* set_option "fuse_wave": loop filter beside the intra wavefront */
+    bool inject_stall = false;             /* set_option "inject_stall": the next wavefront launch never satisfies one wait (test) */
+    bool inter_sb = true;                  /* set_option "inter_sb": k_inter_sb (shared-memory windows + fused residual);
+                                              0 = the strip kernel k_inter + k_itx of round 1 */
     std::vector<Surface *> pool;           /* every surface ever allocated */
     Surface *ref[8] = { nullptr };
     Surface *last = nullptr;               /* most recently reconstructed frame */
@@ -281,6 +285,8 @@ struct Vp9CudaCtx {
     cudaEvent_t marks[16] = { nullptr };
     cudaEvent_t join_ev[4] = { nullptr, nullptr, nullptr, nullptr };
     DBuf sum_buf;
+    DBuf err_dev;                          /* error word of the wavefront waits (dev_common.cuh: VP9_SPIN) */
+    int *err_host = nullptr, *err_host_dev = nullptr;   /* its host-mapped twin */
     DBuf phase_clk;                        /* optional profiling counters (set_option "phase_clk") */
     bool phase_on = false;
 };
@@ -552,6 +558,10 @@ static int launch_frame(Vp9CudaCtx *c, FrameDesc &f, DevRecords &d)
     const uint64_t P_bytes = (uint64_t)f.w * f.h * 3 / 2 * sizeof(P);
     const bool fused = c->fuse_wave && f.n_itx && f.lf_level;
     f.lf_follow = fused ? c->follow_mask : 0;
+    if (fused && c->inject_stall) {
+        f.lf_follow |= 4;
+        c->inject_stall = false;
+    }
     /* ---- prep stream: everything that depends on the records only (sorting the intra blocks
      * into dependency steps, their residuals, the loop-filter edge schedule).  Runs beside the
      * inter stage of this frame and the wavefronts of the previous one. ---- */
@@ -585,6 +595,7 @@ static int launch_frame(Vp9CudaCtx *c, FrameDesc &f, DevRecords &d)
         CK(cudaEventRecord(d.prepped, sp));
     }
     const bool had_upload = d.wait_upload;
+    bool residual_done = false;
     if (d.wait_upload) {
         CK(cudaStreamWaitEvent(s, d.uploaded, 0));
         d.wait_upload = false;
@@ -621,12 +632,17 @@ static int launch_frame(Vp9CudaCtx *c, FrameDesc &f, DevRecords &d)
             const int band = dep_whole ? gy : std::max(4, (gy + c->inter_bands - 1) / c->inter_bands);
             for (int y0 = 0; y0 < gy; y0 += band) {
                 const int n = std::min(band, gy - y0);
-                k_inter_gate<<<1, 32, 0, si>>>(dep_done, dep_rows, dep_whole, f.mv_reach, (y0 + n) * 32 - 1);
+                k_inter_gate<<<1, 32, 0, si>>>(dep_done, dep_rows, dep_whole, f.mv_reach, (y0 + n) * 32 - 1, f.err, f.err_host);
                 f.tile_y0 = y0;
                 k_inter<P><<<dim3(gx, n), 256, 0, si>>>(f);
             }
             f.tile_y0 = 0;
             kstat_end(c, KS_INTER, 2 * ((gy + band - 1) / band), 2 * P_bytes, si);
+        } else if (c->inter_sb) {
+            /* one CTA per superblock: windows staged in shared memory, residual added in the tile */
+            k_inter_sb<P, HBD><<<dim3(f.sb_cols, f.sb_rows), ISB_THREADS, IsbSmem<P>::BYTES, si>>>(f, 1);
+            kstat_end(c, KS_INTER, 1, 2 * P_bytes + d.n_coef * sizeof(typename ItxTypes<HBD>::E), si);
+            residual_done = true;
         } else {
             k_inter<P><<<dim3(gx, gy), 256, 0, si>>>(f);
             kstat_end(c, KS_INTER, 1, 2 * P_bytes, si);
@@ -638,7 +654,7 @@ static int launch_frame(Vp9CudaCtx *c, FrameDesc &f, DevRecords &d)
             CK(cudaEventRecord(c->prev_dev->dev_free, s));
         }
     }
-    if (f.n_tx) {
+    if (f.n_tx && !residual_done) {
         kstat_begin(c);
         k_itx<P, HBD><<<dim3((d.max_tx + 3) / 4, f.n_lanes), 128, 0, s>>>(f);
         /* bytes: the coefficient entries of the frame (intra blocks included: the stream is shared) */
@@ -772,6 +788,8 @@ static int reconstruct(Vp9CudaCtx *c, DevRecords &d, uint8_t *const out_planes[3
     f.progress = (int *)d.progress.p;
     f.mv_reach = (int *)d.misc.p;
     f.phase_clk = c->phase_on ? (unsigned long long *)c->phase_clk.p : nullptr;
+    f.err = (int *)c->err_dev.p;
+    f.err_host = c->err_host_dev;
     memcpy(f.lim_lut, h.lim_lut, 64);
     memcpy(f.mblim_lut, h.mblim_lut, 64);
 
@@ -845,6 +863,16 @@ static int create_impl(Vp9CudaCtx *c, int device, int max_w, int max_h, int max_
     CK(cudaFuncSetAttribute(k_wave<uint16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, WaveSmem<uint16_t>::BYTES));
     CK(cudaFuncSetAttribute(k_intra<uint8_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, IntraSmem<uint8_t>::BYTES));
     CK(cudaFuncSetAttribute(k_intra<uint16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, IntraSmem<uint16_t>::BYTES));
+    CK(cudaFuncSetAttribute(k_inter_sb<uint8_t, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, IsbSmem<uint8_t>::BYTES));
+    CK(cudaFuncSetAttribute(k_inter_sb<uint16_t, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, IsbSmem<uint16_t>::BYTES));
+    if (const char *e = getenv("VP9CUDA_INTER_SB"))
+        c->inter_sb = atoi(e) != 0;
+    if (c->err_dev.reserve(64, c->n_allocs))
+        return -ENOMEM;
+    CK(cudaMemset(c->err_dev.p, 0, 64));
+    CK(cudaHostAlloc((void **)&c->err_host, 64, cudaHostAllocMapped));
+    memset(c->err_host, 0, 64);
+    CK(cudaHostGetDevicePointer((void **)&c->err_host_dev, c->err_host, 0));
     c->ticket_ev.assign(256, nullptr);
     for (auto &e : c->ticket_ev)
         CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
@@ -951,6 +979,10 @@ extern "C" int vp9cuda_flush(Vp9CudaCtx *c)
     }
     std::lock_guard<std::mutex> gk(c->gpu_mu);
     sync_all(c);
+    if (c->err_host && *(volatile int *)c->err_host) {
+        cudaMemset(c->err_dev.p, 0, 64);
+        memset(c->err_host, 0, 64);
+    }
     for (int i = 0; i < 8; i++) {
         surface_unref(c->ref[i]);
         c->ref[i] = nullptr;
@@ -990,6 +1022,8 @@ extern "C" void vp9cuda_destroy(Vp9CudaCtx *c)
     for (auto &e : c->join_ev) if (e) cudaEventDestroy(e);
     for (auto &e : c->tpool) cudaEventDestroy(e);
     c->sum_buf.release();
+    c->err_dev.release();
+    if (c->err_host) cudaFreeHost(c->err_host);
     c->phase_clk.release();
     if (c->stream) cudaStreamDestroy(c->stream);
     if (c->s_up) cudaStreamDestroy(c->s_up);
@@ -1221,6 +1255,13 @@ extern "C" int vp9cuda_wait(Vp9CudaCtx *c, uint64_t ticket)
 #endif
     CK(cudaEventSynchronize(c->ticket_ev[ticket % c->ticket_ev.size()]));
     CK(cudaGetLastError());
+    if (c->err_host && *(volatile int *)c->err_host) {
+        /* a wavefront wait ran out of its budget (dev_common.cuh: VP9_SPIN): the pictures from here on are not
+         * valid; the context stays in error until vp9cuda_flush */
+        fprintf(stderr, "vp9cuda: a wavefront dependency was never satisfied (the wait at source line %d gave up)\n",
+                *(volatile int *)c->err_host);
+        return -EIO;
+    }
     if (c->trace)
         fprintf(stderr, "vp9cuda: ticket %llu done\n", (unsigned long long)ticket);
     return 0;
@@ -1398,6 +1439,14 @@ extern "C" int vp9cuda_set_option(Vp9CudaCtx *c, const char *key, int value)
         c->overlap_inter = value != 0;
         return 0;
     }
+    if (!strcmp(key, "inject_stall")) {
+        c->inject_stall = value != 0;
+        return 0;
+    }
+    if (!strcmp(key, "inter_sb")) {        /* 1 (default): k_inter_sb; 0: k_inter + k_itx */
+        c->inter_sb = value != 0;
+        return 0;
+    }
     if (!strcmp(key, "fuse_wave")) {       /* 1 (default): k_wave; 0: separate k_intra / k_lf launches */
         c->fuse_wave = value != 0;
         return 0;
@@ -1556,22 +1605,41 @@ __global__ void k_slot_intra(int n, const uint8_t *tx, const uint8_t *mode, P *p
         pix[(size_t)i * 4096 + (k / N) * 64 + k % N] = (P)intra_pixel(m, N, k % N, k / N, T, L, dc, bpp);
 }
 
+/* the frame kernel's own staging / filtering code (mc_batch, mc_batch_scaled of k_inter_sb.cuh), one warp per item */
 template <class P>
 __global__ void k_slot_mc(int n, const uint8_t *w, const uint8_t *h, const uint8_t *filter, const uint8_t *avg,
                           const uint8_t *mx, const uint8_t *my, const uint8_t *dx, const uint8_t *dy, P *pix,
                           const P *ref, int bpp)
 {
+    __shared__ __align__(16) unsigned char arena[ISB_ARENA];
+    __shared__ UGeom geom[1];
     const int i = blockIdx.x;
     if (i >= n)
         return;
-    RefPlane<P> rp = { ref + (size_t)i * 160 * 160, 160, 160, 160 };
-    McPos pos = { 8, 8, mx[i], my[i], dx[i] ? dx[i] : 16, dy[i] ? dy[i] : 16 };
-    for (int k = threadIdx.x; k < w[i] * h[i]; k += blockDim.x) {
-        int ox = k % w[i], oy = k / w[i];
-        int v = mc_pixel(rp, pos, ox, oy, filter[i], bpp);
-        P *d = pix + (size_t)i * 4096 + oy * 64 + ox;
-        *d = (P)(avg[i] ? (*d + v + 1) >> 1 : v);
-    }
+    const int W = w[i], H = h[i], pw = min(W, 32), ph = min(H, 16);
+    const int wl = pw == 4 ? 0 : pw == 8 ? 1 : pw == 16 ? 2 : 3, hl = ph == 4 ? 0 : ph == 8 ? 1 : 2;
+    const bool scaled = dx[i] != 0;
+    for (int py = 0; py < H; py += ph)
+        for (int px = 0; px < W; px += pw) {
+            if (threadIdx.x == 0) {
+                UGeom &g = geom[0];
+                g.src = ref + (size_t)i * 160 * 160; g.stride = 160; g.rw = g.rh = 160;
+                g.filter = filter[i];
+                g.dst = (uint16_t)(py * 64 + px); g.dpitch = 64;
+                g.pos.x0 = 8; g.pos.y0 = 8; g.pos.fx = mx[i]; g.pos.fy = my[i];
+                g.pos.dx = scaled ? dx[i] : 16; g.pos.dy = scaled ? dy[i] : 16;
+                g.sox = px; g.soy = py;
+                g.fx = mx[i]; g.fy = my[i];
+                g.wx = 8 + px - 3; g.wy = 8 + py - 3;
+                g.interior = 1;
+                g.a = (uint8_t)(g.wx & (IsbGeo<P>::APX - 1));
+            }
+            __syncwarp();
+            if (scaled)
+                mc_batch_scaled<P>(geom, 1, wl, hl, pix + (size_t)i * 4096, avg[i] != 0, bpp);
+            else
+                mc_batch<P>(geom, 1, wl, hl, arena, pix + (size_t)i * 4096, avg[i] != 0, bpp);
+        }
 }
 
 template <class P>
@@ -1660,8 +1728,8 @@ extern "C" int vp9cuda_slot_mc(int device, int bpp, int n, const uint8_t *w, con
     uint8_t *dp = b.up((const uint8_t *)pix, (size_t)n * 4096 * pb);
     uint8_t *dr = b.up((const uint8_t *)ref, (size_t)n * 160 * 160 * pb);
     if (!dw || !dh || !df || !da || !dmx || !dmy || !ddx || !ddy || !dp || !dr) return -ENOMEM;
-    if (bpp > 8) k_slot_mc<uint16_t><<<n, 256>>>(n, dw, dh, df, da, dmx, dmy, ddx, ddy, (uint16_t *)dp, (const uint16_t *)dr, bpp);
-    else         k_slot_mc<uint8_t><<<n, 256>>>(n, dw, dh, df, da, dmx, dmy, ddx, ddy, dp, dr, bpp);
+    if (bpp > 8) k_slot_mc<uint16_t><<<n, 32>>>(n, dw, dh, df, da, dmx, dmy, ddx, ddy, (uint16_t *)dp, (const uint16_t *)dr, bpp);
+    else         k_slot_mc<uint8_t><<<n, 32>>>(n, dw, dh, df, da, dmx, dmy, ddx, ddy, dp, dr, bpp);
     CK(cudaMemcpy(pix, dp, (size_t)n * 4096 * pb, cudaMemcpyDeviceToHost));
     CK(cudaGetLastError());
     return 0;

@@ -217,3 +217,64 @@ def test_many_broken_frames_in_one_stream(threads, ttype, workdir):
         assert pics(out) == pics(want) and len(out) == len(want)
     else:
         assert out == want
+
+
+INTER_AB = ["c2_small", "c3_small", "hbd12", "odd", "scale_mix", "filters_tx", "bilinear", "scale_filters", "tiny", "lossless"]
+
+
+@pytest.mark.parametrize("name", INTER_AB)
+def test_inter_kernels_agree(name, workdir):
+    """k_inter_sb (shared-memory windows + fused residual, the default) against the strip kernel k_inter +
+    k_itx of round 1 (set_option inter_sb 0): same checksums frame by frame, both equal to the reference"""
+    from ffmpeg_hybrid_b200 import binding
+    lib = binding.load()
+    ivf = parity.write_stream(configs.small_variants()[name], workdir / f"{name}_ab.ivf")
+    parity.dump_records(ivf, workdir / f"{name}_ab.v9r")
+    frames = binding.load_stream(lib, workdir / f"{name}_ab.v9r", pinned=True)
+    sums = []
+    for mode in (1, 0):
+        ctx = binding.Context(0)
+        ctx.option("inter_sb", mode)
+        s = []
+        for f in frames:
+            ctx.wait(ctx.decode(f, None))
+            s.append(ctx.checksum(-1))
+        sums.append(s)
+        ctx.close()
+    assert sums[0] == sums[1]
+    for f in frames:
+        f.free()
+
+
+def test_unsatisfied_dependency_is_an_error_not_a_hang(workdir):
+    """set_option inject_stall: one wait of the next wavefront launch is never satisfied.  The waits run out
+    of their clock budget, the launch drains, vp9cuda_wait returns an error, and after vp9cuda_flush the
+    context decodes the stream correctly again."""
+    import time
+    from ffmpeg_hybrid_b200 import binding
+    lib = binding.load()
+    name = "c1_small"
+    ivf = parity.write_stream(configs.small_variants()[name], workdir / "stall.ivf")
+    parity.dump_records(ivf, workdir / "stall.v9r")
+    frames = binding.load_stream(lib, workdir / "stall.v9r", pinned=True)
+    ctx = binding.Context(0)
+    good = []
+    for f in frames:
+        ctx.wait(ctx.decode(f, None))
+        good.append(ctx.checksum(-1))
+    assert lib.vp9cuda_flush(ctx.ctx) == 0
+    ctx.option("inject_stall", 1)
+    t0 = time.time()
+    t = ctx.decode(frames[0], None)            # key frame: intra + loop filter wavefront
+    rc = lib.vp9cuda_wait(ctx.ctx, t)
+    assert rc < 0, "the stalled frame must be reported"
+    assert time.time() - t0 < 60
+    assert lib.vp9cuda_flush(ctx.ctx) == 0
+    again = []
+    for f in frames:
+        ctx.wait(ctx.decode(f, None))
+        again.append(ctx.checksum(-1))
+    assert again == good
+    ctx.close()
+    for f in frames:
+        f.free()
