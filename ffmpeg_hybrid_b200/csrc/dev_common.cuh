@@ -126,7 +126,9 @@ __device__ __forceinline__ int rounded_div(int a, int b)
 #ifndef VP9_TIGHT_NS
 #define VP9_TIGHT_NS 0      /* sleep (ns) inside the compute warps' waits for their loader warps */
 #endif
-#ifdef VP9CUDA_WATCHDOG
+#ifdef VP9_EMU
+#define VP9_SPIN(cond, ns, tag, a, b) do { while (cond) std::this_thread::yield(); } while (0)
+#elif defined(VP9CUDA_WATCHDOG)
 __device__ int *g_wd_buf;            /* host-mapped: [0] = count, then {line, id, at, block} per report */
 #define VP9_SPIN(cond, ns, tag, a, b) do { long long t0_ = clock64(); bool rep_ = false; while (cond) { if ((ns) > 0) __nanosleep(ns); \
     const long long dt_ = clock64() - t0_; \
@@ -160,6 +162,24 @@ __device__ int *g_wd_buf;
             if (!t0_) t0_ = now_; \
             else if (now_ - t0_ > VP9_SPIN_BUDGET) { \
                 atomicExch(f.err, __LINE__); *(volatile int *)f.err_host = __LINE__; __threadfence_system(); break; } } } } while (0)
+#endif
+
+/* 16-byte asynchronous global -> shared copies (LDGSTS.128) and named barriers, with host stand-ins for
+ * the emulation build (oracle/cuda_emu.h) */
+#ifdef VP9_EMU
+__device__ __forceinline__ void cp16(void *smem, const void *gmem) { memcpy(smem, gmem, 16); }
+__device__ __forceinline__ void cp_commit() {}
+template <int N> __device__ __forceinline__ void cp_wait() {}
+template <int ID, int N> __device__ __forceinline__ void bar_named() { emu::named_barrier(ID, N); }
+#else
+__device__ __forceinline__ void cp16(void *smem, const void *gmem)
+{
+    unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(sa), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
+template <int ID, int N> __device__ __forceinline__ void bar_named() { asm volatile("bar.sync %0, %1;\n" ::"n"(ID), "n"(N) : "memory"); }
 #endif
 
 template <class P> __device__ __forceinline__ P ld_cg(const P *p);

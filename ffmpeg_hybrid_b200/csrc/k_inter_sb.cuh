@@ -62,19 +62,9 @@ struct UGeom {
     uint8_t fx, fy, filter, interior;
 };
 
-#ifdef VP9_EMU
-__device__ __forceinline__ void isb_cp16(void *smem, const void *gmem) { memcpy(smem, gmem, 16); }
-__device__ __forceinline__ void isb_cp_commit() {}
-__device__ __forceinline__ void isb_cp_wait_all() {}
-#else
-__device__ __forceinline__ void isb_cp16(void *smem, const void *gmem)
-{
-    unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(sa), "l"(gmem) : "memory");
-}
-__device__ __forceinline__ void isb_cp_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
-__device__ __forceinline__ void isb_cp_wait_all() { asm volatile("cp.async.wait_group 0;\n" ::: "memory"); }
-#endif
+__device__ __forceinline__ void isb_cp16(void *smem, const void *gmem) { cp16(smem, gmem); }
+__device__ __forceinline__ void isb_cp_commit() { cp_commit(); }
+__device__ __forceinline__ void isb_cp_wait_all() { cp_wait<0>(); }
 
 template <class P> struct IsbGeo {
     static constexpr int PS = (int)sizeof(P);

@@ -49,14 +49,6 @@ namespace vp9 {
 #define INTRA_SB_TAB 768                    /* work table: <= 384 chunk entries + <= 384 step headers */
 #define INTRA_EDGE_N 104                    /* per compute warp: top[0..64] (0 = top-left) at 0, left[0..31] at 72 */
 
-__device__ __forceinline__ void cp16(void *smem, const void *gmem)
-{
-    unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(sa), "l"(gmem) : "memory");
-}
-__device__ __forceinline__ void cp_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
-template <int N> __device__ __forceinline__ void cp_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
-
 /* residual tile of one superblock: luma 64x64 row-major, then U 32x32, then V 32x32 (int16) */
 __device__ __forceinline__ int res_plane_off(int pl) { return pl == 0 ? 0 : pl == 1 ? 4096 : 5120; }
 
@@ -407,7 +399,7 @@ __device__ __forceinline__ void intra_row(const FrameDesc &f, const int row, uns
                 ICLK(11);
                 __threadfence_block();
             }
-            asm volatile("bar.sync 1, %0;\n" ::"n"(INTRA_CT) : "memory");
+            bar_named<1, INTRA_CT>();
 #ifdef VP9CUDA_STEPSTATS   /* counters for tools/prof_frames.py; the chain is so tight that they cost ~4 % of the wavefront */
             int nsteps = 0, nrounds = 0, nchunks = 0, ntop = info[c].needs_top;
 #endif
@@ -469,7 +461,7 @@ __device__ __forceinline__ void intra_row(const FrameDesc &f, const int row, uns
                     }
                     __syncwarp();                        /* the arrays are rewritten by this warp's next chunk */
                 }
-                asm volatile("bar.sync 1, %0;\n" ::"n"(INTRA_CT) : "memory");
+                bar_named<1, INTRA_CT>();
                 pos += cnt + 1;
 #ifdef VP9CUDA_STEPSTATS
                 nsteps++;
@@ -636,7 +628,7 @@ __device__ __forceinline__ void intra_row(const FrameDesc &f, const int row, uns
 template <class P>
 __global__ void __launch_bounds__(INTRA_THREADS) k_intra(const __grid_constant__ FrameDesc f)
 {
-    extern __shared__ __align__(16) unsigned char sm[];
+    VP9_DYN_SMEM(sm);
     __shared__ IntraSig sig;
     intra_row<P>(f, blockIdx.x, sm, sig);
 }

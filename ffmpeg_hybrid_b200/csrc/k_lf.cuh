@@ -144,14 +144,10 @@ __global__ void __launch_bounds__(LF_SCHED_THREADS) k_lf_sched(const __grid_cons
     }
 }
 
-__device__ __forceinline__ void lf_cp16(void *smem, const void *gmem)
-{
-    unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(sa), "l"(gmem) : "memory");
-}
-__device__ __forceinline__ void lf_cp_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
-template <int N> __device__ __forceinline__ void lf_cp_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
-__device__ __forceinline__ void lf_bar_compute() { asm volatile("bar.sync 1, %0;\n" ::"n"(LF_CT) : "memory"); }
+__device__ __forceinline__ void lf_cp16(void *smem, const void *gmem) { cp16(smem, gmem); }
+__device__ __forceinline__ void lf_cp_commit() { cp_commit(); }
+template <int N> __device__ __forceinline__ void lf_cp_wait() { cp_wait<N>(); }
+__device__ __forceinline__ void lf_bar_compute() { bar_named<1, LF_CT>(); }
 
 /* signals between the warps of one CTA (shared memory, monotonically increasing counts) */
 struct LfSig {
@@ -458,7 +454,7 @@ template <class P> struct WaveSmem {
 template <class P>
 __global__ void __launch_bounds__(INTRA_THREADS, VP9_WAVE_CTAS_PER_SM) k_wave(const __grid_constant__ FrameDesc f)
 {
-    extern __shared__ __align__(16) unsigned char sm[];
+    VP9_DYN_SMEM(sm);
     __shared__ IntraSig isig;
     __shared__ LfSig lsig;
     /* test hook (set_option "inject_stall"): CTA 0 waits for something that never happens, so that the

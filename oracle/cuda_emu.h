@@ -123,7 +123,52 @@ static inline void __threadfence_block() { __atomic_thread_fence(__ATOMIC_SEQ_CS
 static inline long long clock64() { return 0; }
 static inline void __nanosleep(unsigned) { std::this_thread::yield(); }
 template <class T> static inline T __ldcg(const T *p) { return *p; }
-static inline int __reduce_max_sync(unsigned, int v) { return v; }     /* only used for statistics */
+static inline int __shfl_up_sync(unsigned mask, int v, int delta)
+{
+    emu::Cta *c = emu::g_cta;
+    c->shfl[threadIdx.x] = (uint32_t)v;
+    __syncwarp(mask);
+    const int lane = threadIdx.x & 31;
+    const int r = lane >= delta ? (int)c->shfl[threadIdx.x - delta] : v;
+    __syncwarp(mask);
+    return r;
+}
+static inline int __reduce_add_sync(unsigned mask, int v)
+{
+    emu::Cta *c = emu::g_cta;
+    c->shfl[threadIdx.x] = (uint32_t)v;
+    __syncwarp(mask);
+    int s = 0;
+    for (int l = 0; l < 32; l++)
+        if (mask >> l & 1) s += (int)c->shfl[(threadIdx.x & ~31u) + l];
+    __syncwarp(mask);
+    return s;
+}
+static inline int __reduce_max_sync(unsigned mask, int v)
+{
+    emu::Cta *c = emu::g_cta;
+    c->shfl[threadIdx.x] = (uint32_t)v;
+    __syncwarp(mask);
+    int s = v;
+    for (int l = 0; l < 32; l++)
+        if ((mask >> l & 1) && (int)c->shfl[(threadIdx.x & ~31u) + l] > s) s = (int)c->shfl[(threadIdx.x & ~31u) + l];
+    __syncwarp(mask);
+    return s;
+}
+static inline unsigned long long atomicAdd(unsigned long long *p, unsigned long long v) { return __atomic_fetch_add(p, v, __ATOMIC_SEQ_CST); }
+namespace emu {
+static inline void named_barrier(int id, int n)
+{
+    Barrier *b;
+    {
+        std::lock_guard<std::mutex> lk(g_cta->mu);
+        Barrier *&q = g_cta->warp_bar[(uint64_t)0xffff0000u << 32 | (unsigned)id];
+        if (!q) q = new Barrier(n);
+        b = q;
+    }
+    b->wait();
+}
+}
 
 namespace emu {
 

@@ -7,18 +7,85 @@
  * reference decoder).  This checks the kernel's indexing, staging, batching and synchronisation
  * before it ever runs on a GPU; the GPU parity tests then check the real thing.
  *
- * usage: emu_inter in.v9r [max_frames]      exit 0 = identical
+ * usage: emu_inter [-full] in.v9r [max_frames]      exit 0 = identical
+ *   -full: also k_intra_prep, k_intra_res, k_lf_sched and the intra / loop-filter wavefronts (k_wave), CTAs in
+ *          block-index order; the whole reconstructed frame is compared with the restatement
  */
 #define VP9_EMU_IMPL
 #include "cuda_emu.h"
 #define MODEL_NO_MAIN
 #include "replay_model.cc"
 #include "k_inter_sb.cuh"
+#include "k_intra.cuh"
+#include "k_lf.cuh"
+
+static bool g_full;          /* -full: also the pre-passes and the intra / loop-filter wavefronts, whole frame compared */
 
 static long g_compared;
 template <class P, bool HBD>
+static long run_wave(FrameDesc &f, const Vp9CudaFrameHeader &h, const std::vector<Lane> &lanes,
+                     const std::vector<Vp9CudaSbIndex> &sbi, const std::vector<Vp9CudaLoopFilterSb> &lf,
+                     std::vector<P> *cur, Model &m)
+{
+    /* the rest of launch_frame (csrc/vp9cuda.cu): pre-passes, then the wavefronts.  CTAs run one after the
+     * other in block-index order, which satisfies every cross-CTA wait of k_wave (they all point at lower
+     * block indices) */
+    const int n_sb = f.sb_cols * f.sb_rows;
+    std::vector<Vp9CudaIntraTx> itx;
+    for (size_t l = 0; l < lanes.size(); l++) {
+        f.lane_itx_base[l] = (uint32_t)itx.size();
+        itx.insert(itx.end(), lanes[l].itx.begin(), lanes[l].itx.end());
+    }
+    f.itx = itx.data(); f.n_itx = (uint32_t)itx.size();
+    f.lf = lf.data();
+    f.lossless = h.lossless; f.lf_level = h.lf_level;
+    memcpy(f.lim_lut, h.lim_lut, 64); memcpy(f.mblim_lut, h.mblim_lut, 64);
+    std::vector<IntraSb> isb(n_sb);
+    std::vector<IntraRec> irec(itx.size() + 1);
+    std::vector<IntraBlk> iblk(itx.size() + 1);
+    std::vector<int> iprogress(2 * f.sb_rows, 0), progress(6 * f.sb_rows, 0);
+    std::vector<uint16_t> itab((size_t)n_sb * INTRA_SB_TAB);
+    std::vector<int16_t> ires((size_t)n_sb * INTRA_SB_RES);
+    std::vector<LfSched> lfs((size_t)n_sb * 3);
+    f.isb = isb.data(); f.irec = irec.data(); f.iblk = iblk.data(); f.iprogress = iprogress.data();
+    f.itab = itab.data(); f.ires = ires.data(); f.lfsched = lfs.data(); f.progress = progress.data();
+    const bool fused = f.n_itx && f.lf_level && !getenv("EMU_NOFUSE");
+    f.lf_follow = fused ? 3 : 0;
+    if (f.n_itx) {
+        emu::launch(dim3(n_sb), 128, 0, [&] { k_intra_prep(f); });
+        emu::launch(dim3(n_sb), IRES_WARPS * 32, 0, [&] { k_intra_res<HBD>(f); });
+    }
+    if (getenv("EMU_NOLF")) f.lf_level = 0;
+    if (f.lf_level)
+        emu::launch(dim3(n_sb), LF_SCHED_THREADS, 0, [&] { k_lf_sched(f); });
+    if (fused) {
+        emu::launch(dim3(4 * f.sb_rows), INTRA_THREADS, WaveSmem<P>::BYTES, [&] { k_wave<P>(f); });
+    } else {
+        if (f.n_itx)
+            emu::launch(dim3(f.sb_rows), INTRA_THREADS, IntraSmem<P>::BYTES, [&] { k_intra<P>(f); });
+        if (f.lf_level)
+            emu::launch(dim3(3 * f.sb_rows), LF_THREADS, 0, [&] { k_lf<P>(f); });
+    }
+    /* the whole picture against the restatement's (all four phases) */
+    Model mf = m;
+    Vp9CudaFrameHeader h2 = h;
+    if (getenv("EMU_NOLF")) h2.lf_level = 0;
+    decode_frame(mf, h2, lanes, sbi, lf);
+    long bad = 0;
+    for (int pl = 0; pl < 3; pl++)
+        for (int y = 0; y < mf.cur->ph[pl]; y++)
+            for (int x = 0; x < mf.cur->pw[pl]; x++) {
+                g_compared++;
+                const int want = mf.cur->p[pl][(size_t)y * mf.cur->stride[pl] + x], got = cur[pl][(size_t)y * f.cur.stride[pl] + x];
+                if (want != got && bad++ < 12)
+                    fprintf(stderr, "  full frame, plane %d (%d, %d): kernels %d, restatement %d\n", pl, x, y, got, want);
+            }
+    return bad;
+}
+
+template <class P, bool HBD>
 static long run_frame(Model &m, const Vp9CudaFrameHeader &h, const std::vector<Lane> &lanes,
-                      const std::vector<Vp9CudaSbIndex> &sbi)
+                      const std::vector<Vp9CudaSbIndex> &sbi, const std::vector<Vp9CudaLoopFilterSb> &lf)
 {
     const int cols = (h.w + 7) >> 3, rows = (h.h + 7) >> 3;
     const int sb_cols = (h.w + 63) >> 6, sb_rows = (h.h + 63) >> 6;
@@ -82,11 +149,14 @@ static long run_frame(Model &m, const Vp9CudaFrameHeader &h, const std::vector<L
                 cellmap[(size_t)(blk[i].row + y) * cols + blk[i].col + x] = (int32_t)i;
     }
     f.cellmap = cellmap.data();
-    if (blk.empty())
+    if (blk.empty() && !g_full)
         return 0;
-    emu::launch(dim3(sb_cols, sb_rows), ISB_THREADS, IsbSmem<P>::BYTES, [&] { k_inter_sb<P, HBD>(f, 1); });
+    if (!blk.empty())
+        emu::launch(dim3(sb_cols, sb_rows), ISB_THREADS, IsbSmem<P>::BYTES, [&] { k_inter_sb<P, HBD>(f, 1); });
     long bad = 0;
-    for (int pl = 0; pl < 3; pl++) {
+    if (g_full)
+        bad += run_wave<P, HBD>(f, h, lanes, sbi, lf, cur, m);
+    for (int pl = 0; pl < 3 && !g_full; pl++) {
         const int ch = pl > 0, cs = 8 >> ch;
         for (int y = 0; y < (rows * 8) >> ch; y++)
             for (int x = 0; x < (cols * 8) >> ch; x++) {
@@ -104,6 +174,7 @@ static long run_frame(Model &m, const Vp9CudaFrameHeader &h, const std::vector<L
 int main(int argc, char **argv)
 {
     if (argc < 2) { fprintf(stderr, "usage: %s in.v9r [max_frames]\n", argv[0]); return 2; }
+    if (argc > 1 && !strcmp(argv[1], "-full")) { g_full = true; argv++; argc--; }
     const int max_frames = argc > 2 ? atoi(argv[2]) : 1 << 30;
     FILE *fp = fopen(argv[1], "rb");
     if (!fp) { perror("open"); return 2; }
@@ -131,8 +202,8 @@ int main(int argc, char **argv)
         std::vector<Vp9CudaLoopFilterSb> lf(n_sb); rd(fp, lf.data(), n_sb * sizeof(Vp9CudaLoopFilterSb));
         size_t nblk = 0;
         for (const Lane &l : lanes) nblk += l.blk.size();
-        if (nblk) {
-            const long b = h.bpp > 8 ? run_frame<uint16_t, true>(m, h, lanes, sbi) : run_frame<uint8_t, false>(m, h, lanes, sbi);
+        if (nblk || g_full) {
+            const long b = h.bpp > 8 ? run_frame<uint16_t, true>(m, h, lanes, sbi, lf) : run_frame<uint8_t, false>(m, h, lanes, sbi, lf);
             if (b) fprintf(stderr, "frame %d: %ld differing pixels\n", nf, b);
             bad += b;
             ninter++;

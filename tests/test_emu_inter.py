@@ -45,3 +45,17 @@ def test_tile_threaded_records(workdir):
                    capture_output=True, env=dict(os.environ, VP9CUDA_DUMP=str(v9r)))
     p = subprocess.run([str(EMU), str(v9r)], capture_output=True, text=True, timeout=900)
     assert p.returncode == 0, p.stderr[-1500:]
+
+
+@pytest.mark.parametrize("name,frames", [("tiny", 4), ("hbd12", 3), ("lossless", 2), ("intraonly", 3), ("c4_small", 1)])
+def test_whole_gpu_pipeline_emulated(name, frames, workdir):
+    """-full: every kernel of a frame (k_inter_sb, k_intra_prep, k_intra_res, k_lf_sched and the intra /
+    loop-filter wavefronts of k_wave, CTAs in block-index order) on the host; the finished picture must equal
+    the restatement's.  This is the functional check of the wavefront kernels' indexing and hand-overs that
+    needs no GPU; the races between concurrently running CTAs are what the GPU tests add."""
+    ivf = parity.write_stream(configs.small_variants()[name], workdir / f"emuf_{name}.ivf")
+    v9r = workdir / f"emuf_{name}.v9r"
+    parity.dump_records(ivf, v9r)
+    p = subprocess.run([str(EMU), "-full", str(v9r), str(frames)], capture_output=True, text=True, timeout=900)
+    assert p.returncode == 0, p.stderr[-1500:]
+    assert " 0 differing" in p.stderr
