@@ -73,6 +73,34 @@ def c3p(frames: int = 30, seed: int = 3, w: int = 3840, h: int = 2160) -> Stream
     return st
 
 
+def natural_stats(st: StreamSpec) -> StreamSpec:
+    """Give a stream the statistics of encoded video instead of the default model's: every frame's header raises
+    the end-of-block / zero-token / skip probabilities (sparse coefficients) and, on inter frames, lowers the
+    intra probability and raises the no-split partition probabilities (large blocks, a few per cent of intra
+    blocks).  The updates are differential, coded against the context the generator tracks (streamgen.ProbTracker).  The payload is still a seeded random sample -- of this model."""
+    part = [0] * 48
+    none = {0: (235, 210, 210, 180), 1: (225, 200, 200, 160), 2: (215, 180, 180, 140), 3: (230, 200, 200, 170)}
+    from .streamgen import default_probs
+    d = default_probs()["partition"]
+    for lvl in range(4):
+        for ctx in range(4):
+            part[(lvl * 4 + ctx) * 3:(lvl * 4 + ctx) * 3 + 3] = [none[lvl][ctx], d[(lvl * 4 + ctx) * 3 + 1], d[(lvl * 4 + ctx) * 3 + 2]]
+    for f in st.frames:
+        if f.show_existing >= 0:
+            continue
+        f.prob_update = {"coef": (1.25, 1.1, 1.0), "skip": [200, 140, 80]}
+        if not f.keyframe and not f.intraonly:
+            f.prob_update.update({"intra": [3, 8, 24, 60], "partition": part})
+    return st
+
+
+def c3n(frames: int = 30, seed: int = 3, w: int = 3840, h: int = 2160) -> StreamSpec:
+    """C3 with natural statistics (natural_stats): the same 4K 10-bit profile 2 structure -- 32x32 transforms,
+    hidden half-size frames, scaled references, 4 tile columns, backward adaptation -- but inter frames made
+    of large, mostly skipped inter blocks with sparse residuals and only a few per cent of intra blocks."""
+    return natural_stats(c3(frames=frames, seed=seed, w=w, h=h))
+
+
 def c4(frames: int = 8, seed: int = 4, w: int = 7680, h: int = 4320) -> StreamSpec:
     """8K 8-bit, all key frames (intra + loop-filter wavefront bound); second half at max LF level."""
     st = StreamSpec(w, h, seed=seed)
@@ -212,6 +240,7 @@ def small_variants() -> Dict[str, StreamSpec]:
         f.filtermode = (0, 2, 0, 2, 1, 0, 2, 3, 0, 2)[i]
         f.highprecisionmvs = False
     out["wide64"] = st
+    out["c3n_small"] = c3n(frames=8, w=784, h=464)           # natural statistics through forward probability updates
     st = StreamSpec(72, 40, seed=11)                         # tiny, single superblock column
     st.frames = _ippp(4, compound=True)
     out["tiny"] = st

@@ -38,7 +38,9 @@
 
 namespace vp9 {
 
+#ifndef LF_CW
 #define LF_CW 8                       /* compute warps */
+#endif
 #define LF_CT (LF_CW * 32)
 #define LF_THREADS (LF_CT + 3 * 32)   /* + body loader, top loader, storer */
 

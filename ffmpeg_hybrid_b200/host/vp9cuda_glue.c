@@ -64,6 +64,8 @@ typedef struct VP9CudaShared {
 struct VP9CudaGlue {
     VP9CudaShared *sh;
     int frame_mt;                /* libavcodec frame threading: one frame per worker, several in flight */
+    int device;                  /* GPU of this decoder: $VP9CUDA_DEVICE as it was when the decoder was opened, so that
+                                    one process can open decoders on several GPUs (tools/vp9multi.c) */
     Vp9CudaFrameHeader hdr;
     Vp9CudaFrameRing fring;
     Vp9CudaLaneRing ring[VP9CUDA_MAX_LANES];
@@ -485,8 +487,7 @@ static int shared_create(AVCodecContext *avctx, VP9CudaGlue *g)
         SYM(finish_frame); SYM(abort_frame); SYM(wait); SYM(host_alloc); SYM(host_free);
 #undef SYM
     }
-    if (getenv("VP9CUDA_DEVICE"))
-        dev = atoi(getenv("VP9CUDA_DEVICE"));
+    dev = g->device;
     /* ring sets: one per frame a worker may hold between begin_frame and finish_frame, plus one */
     nfl = g->frame_mt ? FFMIN(avctx->thread_count + 1, 32) : 2;
     ret = sh->api.create(&sh->ctx, dev, s->w, s->h, s->s.h.bpp, nfl);
@@ -515,6 +516,7 @@ int ff_vp9cuda_init(AVCodecContext *avctx)
     if (!g)
         return AVERROR(ENOMEM);
     g->frame_mt = !!(avctx->active_thread_type & FF_THREAD_FRAME);
+    g->device = getenv("VP9CUDA_DEVICE") ? atoi(getenv("VP9CUDA_DEVICE")) : 0;
     atomic_init(&g->overflow, 0);
     /* one worker per frame already keeps many frames in flight; otherwise hold one picture back */
     g->pipeline = !g->frame_mt && (!getenv("VP9CUDA_PIPELINE") || atoi(getenv("VP9CUDA_PIPELINE")));

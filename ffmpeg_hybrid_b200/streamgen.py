@@ -158,6 +158,13 @@ class FrameSpec:
     # (vp9.c:1345 -> AVERROR_INVALIDDATA in the middle of the frame), "tilesize" writes a tile size
     # beyond the packet (vp9.c:1336-1341), "sync" breaks a key frame's sync code (vp9.c:552)
     damage: Optional[str] = None
+    # forward probability updates in the compressed header (vp9.c:956-1110), coded against the context the
+    # generator tracks (ProbTracker): "skip" (3 targets), "coef" ((eob, zero, one) factors f: default p ->
+    # 255 - (255 - p) / f, all bands / contexts / planes), and on inter frames "intra" (4 targets) and
+    # "partition" (48 targets, 64x64 level first).
+    # The random payload then samples THIS model: the way to give a stream natural statistics (few intra blocks
+    # in inter frames, large skipped blocks, sparse coefficients) without a syntax-level encoder.
+    prob_update: Optional[dict] = None
     superframe: bool = False              # packed into one packet with the NEXT frame (superframe index,
                                           # split again by bsf/vp9_superframe_split.c:41-137)
 
@@ -200,8 +207,98 @@ def _color_config(bw: BitWriter, st: StreamSpec) -> None:
     assert st.profile in (0, 2), "4:2:0 profiles only"
 
 
-def _compressed_header(fs: FrameSpec, inter: bool, allowcomp: bool, lossless: bool) -> bytes:
+_INV_MAP = [7 + 13 * k for k in range(20)]
+_INV_MAP += [v for v in range(1, 254) if v not in _INV_MAP] + [253]      # inv_map_table, vp9.c:401-421
+_DEFAULTS: Optional[dict] = None
+
+
+def default_probs() -> dict:
+    """The decoder's default probability tables (VP9 specification; reference libavcodec/vp9data.c), asked
+    from the decoder front end itself (`ffvp9_cuda -tables`) rather than copied."""
+    global _DEFAULTS
+    if _DEFAULTS is None:
+        import json
+        import subprocess
+        from .parity import CUDA_BIN
+        _DEFAULTS = json.loads(subprocess.run([str(CUDA_BIN), "-tables"], capture_output=True, text=True, check=True).stdout)
+    return _DEFAULTS
+
+
+def _inv_recenter_nonneg(v: int, m: int) -> int:
+    if v > 2 * m:
+        return v
+    return m - ((v + 1) >> 1) if v & 1 else m + (v >> 1)
+
+
+def _updated(d: int, p: int) -> int:
+    """update_prob's result for delta index d on current probability p (vp9.c:453-454)"""
+    v = _INV_MAP[d]
+    return 1 + _inv_recenter_nonneg(v, p - 1) if p <= 128 else 255 - _inv_recenter_nonneg(v, 255 - p)
+
+
+def _put_update(be: "BoolEncoder", p: int, target: int) -> int:
+    """update flag + differential update that brings p as close to target as the code allows; returns the new value"""
+    target = min(255, max(1, int(target)))
+    if target == p:
+        be.put(0, 252)
+        return p
+    d = min(range(254), key=lambda k: (abs(_updated(k, p) - target), k))
+    be.put(1, 252)
+    if d < 16:
+        be.put_eq(0); be.put_uint(4, d)
+    elif d < 32:
+        be.put_eq(1); be.put_eq(0); be.put_uint(4, d - 16)
+    elif d < 64:
+        be.put_eq(1); be.put_eq(1); be.put_eq(0); be.put_uint(5, d - 32)
+    else:
+        be.put_eq(1); be.put_eq(1); be.put_eq(1)
+        v = d - 64
+        if v < 65:
+            be.put_uint(7, v)
+        else:
+            be.put_uint(7, (v + 65) >> 1)
+            be.put_eq((v + 65) & 1)
+    return _updated(d, p)
+
+
+class ProbTracker:
+    """The decoder's saved probability context (context 0) for the elements the generator updates: skip, intra,
+    partition and coefficient probabilities.  Differential updates (vp9.c:399-455) are relative to it, and with
+    backward adaptation (vp9prob.c) it depends on what the previous frames decoded to, so it is not guessed: the
+    decoder front end runs beside the generator (`ffvp9_cuda -probe`, entropy decode only, record sink /dev/null),
+    is fed every finished packet and answers with the context it now holds."""
+
+    def __init__(self) -> None:
+        import os
+        import subprocess
+        from .parity import CUDA_BIN
+        self.p = {k: list(v) for k, v in default_probs().items()}
+        env = dict(os.environ, VP9CUDA_DUMP="/dev/null")
+        self.proc = subprocess.Popen([str(CUDA_BIN), "-probe"], stdin=subprocess.PIPE, stdout=subprocess.PIPE, env=env)
+
+    def feed(self, data: bytes) -> None:
+        """IVF bytes: the file header (no answer), or one packet (the context after it)"""
+        import json
+        self.proc.stdin.write(data)
+        self.proc.stdin.flush()
+        if data[:4] == b"DKIF":
+            return
+        line = self.proc.stdout.readline()
+        if not line:
+            raise RuntimeError("the probing decoder gave up on the stream")
+        self.p = json.loads(line)
+
+    def close(self) -> None:
+        self.proc.stdin.close()
+        self.proc.wait()
+
+
+def _compressed_header(fs: FrameSpec, inter: bool, allowcomp: bool, lossless: bool,
+                       trk: Optional["ProbTracker"] = None) -> bytes:
     be = BoolEncoder()
+    upd = fs.prob_update or {}
+    assert not upd or trk is not None, "prob_update needs the tracked context (encode_stream)"
+    dflt = trk.p if trk is not None else {}
     be.put(0, 128)                       # marker, vp9.c:912
     txm = TX_4X4 if lossless else fs.txfmmode
     if not lossless:                     # vp9.c:936-954
@@ -212,18 +309,40 @@ def _compressed_header(fs: FrameSpec, inter: bool, allowcomp: bool, lossless: bo
             for _ in range(2 + 4 + 6):
                 be.put(0, 252)
     for i in range(4):                   # coef updates, vp9.c:958-992
-        be.put_eq(0)
+        if "coef" in upd:
+            be.put_eq(1)
+            fac = upd["coef"]
+            for j in range(2):
+                for k in range(2):
+                    for l in range(6):
+                        for m in range(6):
+                            if m >= 3 and l == 0:
+                                break
+                            base = ((((i * 2 + j) * 2 + k) * 6 + l) * 6 + m) * 3
+                            for n in range(3):
+                                p = dflt["coef"][base + n]
+                                p0 = default_probs()["coef"][base + n]
+                                _put_update(be, p, 255 - (255 - p0) / fac[n] if fac[n] != 1 else p)
+        else:
+            be.put_eq(0)
         if txm == i:
             break
-    for _ in range(3):                   # skip
-        be.put(0, 252)
+    for i in range(3):                   # skip
+        if "skip" in upd:
+            _put_update(be, dflt["skip"][i], upd["skip"][i])
+        else:
+            be.put(0, 252)
     if inter:
         n = 21                           # mv_mode
         if fs.filtermode == FILTER_SWITCHABLE:
             n += 8
-        n += 4                           # intra
         for _ in range(n):
             be.put(0, 252)
+        for i in range(4):               # intra
+            if "intra" in upd:
+                _put_update(be, dflt["intra"][i], upd["intra"][i])
+            else:
+                be.put(0, 252)
         cpm = PRED_SINGLEREF
         if allowcomp:                    # vp9.c:1016-1027
             cpm = fs.comppredmode
@@ -238,7 +357,18 @@ def _compressed_header(fs: FrameSpec, inter: bool, allowcomp: bool, lossless: bo
             n += 10
         if cpm != PRED_SINGLEREF:
             n += 5
-        n += 36 + 48 + 3 + 2 * 22 + 2 * 9
+        n += 36                          # y_mode
+        for _ in range(n):
+            be.put(0, 252)
+        for i in range(4):               # partition: coded 8x8 level first, stored 64x64 level first (vp9.c:1065-1072)
+            for j in range(4):
+                for k in range(3):
+                    if "partition" in upd:
+                        idx = ((3 - i) * 4 + j) * 3 + k
+                        _put_update(be, dflt["partition"][idx], upd["partition"][idx])
+                    else:
+                        be.put(0, 252)
+        n = 3 + 2 * 22 + 2 * 9           # motion vectors
         if fs.highprecisionmvs:
             n += 4
         for _ in range(n):
@@ -247,7 +377,7 @@ def _compressed_header(fs: FrameSpec, inter: bool, allowcomp: bool, lossless: bo
 
 
 def encode_frame(st: StreamSpec, fs: FrameSpec, cur_w: int, cur_h: int,
-                 rng: np.random.Generator) -> bytes:
+                 rng: np.random.Generator, trk: Optional["ProbTracker"] = None) -> bytes:
     """Returns one frame's bytes. cur_w/cur_h is the resolved coded size."""
     bw = BitWriter()
     bw.u(2, 2)
@@ -394,7 +524,7 @@ def encode_frame(st: StreamSpec, fs: FrameSpec, cur_w: int, cur_h: int,
     else:
         bw.u(1, 1)
         bw.u(1, l2r - 1)
-    comp = _compressed_header(fs, inter, allowcomp, lossless)
+    comp = _compressed_header(fs, inter, allowcomp, lossless, trk)
     bw.u(16, len(comp))
     out = bytearray(bw.bytes())
     out += comp
@@ -466,9 +596,13 @@ def encode_stream(st: StreamSpec) -> bytes:
     out += b"DKIF" + struct.pack("<HH4sHHIIII", 0, 32, b"VP90", st.width, st.height,
                                  30, 1, len(st.frames), 0)
     group: List[bytes] = []
+    trk = ProbTracker() if any(f.prob_update for f in st.frames) else None
+    if trk is not None:
+        trk.feed(bytes(out))
     for i, (fs, (w, h)) in enumerate(zip(st.frames, sizes)):
         rng = np.random.default_rng([st.seed, i])
-        group.append(encode_frame(st, fs, w, h, rng))
+        assert not (fs.prob_update and group), "no probability updates inside a superframe (the context is probed per packet)"
+        group.append(encode_frame(st, fs, w, h, rng, trk))
         if fs.superframe and i + 1 < len(st.frames) and len(group) < 8:
             continue
         if len(group) == 1:
@@ -478,7 +612,11 @@ def encode_stream(st: StreamSpec) -> bytes:
             mag = max(1, max((len(g).bit_length() + 7) // 8 for g in group))
             marker = bytes([0xC0 | (mag - 1) << 3 | (len(group) - 1)])
             pkt = b"".join(group) + marker + b"".join(len(g).to_bytes(mag, "little") for g in group) + marker
-        out += struct.pack("<IQ", len(pkt), i)
-        out += pkt
+        rec = struct.pack("<IQ", len(pkt), i) + pkt
+        out += rec
+        if trk is not None:
+            trk.feed(rec)
         group = []
+    if trk is not None:
+        trk.close()
     return bytes(out)

@@ -144,6 +144,22 @@ static inline int __reduce_add_sync(unsigned mask, int v)
     __syncwarp(mask);
     return s;
 }
+static inline int __all_sync(unsigned mask, int pred)
+{
+    emu::Cta *c = emu::g_cta;
+    c->shfl[threadIdx.x] = (uint32_t)(pred != 0);
+    __syncwarp(mask);
+    int r = 1;
+    for (int l = 0; l < 32; l++)
+        if ((mask >> l & 1) && !c->shfl[(threadIdx.x & ~31u) + l]) r = 0;
+    __syncwarp(mask);
+    return r;
+}
+static inline int atomicCAS(int *p, int cmp, int v)
+{
+    __atomic_compare_exchange_n(p, &cmp, v, false, __ATOMIC_SEQ_CST, __ATOMIC_SEQ_CST);
+    return cmp;
+}
 static inline int __reduce_max_sync(unsigned mask, int v)
 {
     emu::Cta *c = emu::g_cta;

@@ -23,7 +23,7 @@ from ffmpeg_hybrid_b200.streamgen import encode_stream  # noqa: E402
 def main():
     specs = dict(configs.small_variants())
     specs.update({"c1": configs.c1(), "c2": configs.c2(), "c3": configs.c3(), "c4": configs.c4(),
-                  "c3p": configs.c3p()})
+                  "c3p": configs.c3p(), "c3n": configs.c3n()})
     specs.update({f"c5_rank{r}": configs.c5(r) for r in range(8)})
     out = {}
     tmp = Path(tempfile.mkdtemp())

@@ -188,10 +188,10 @@ def test_frame_threaded_host_is_bit_exact(name, threads, workdir):
     assert parity.cuda_md5(ivf, threads=threads, thread_type="frame") == GOLDEN[name]["framemd5"]
 
 
-@pytest.mark.parametrize("name,full", [("c3", "c3"), ("c3p", "c3p"), ("c2", "c2")])
+@pytest.mark.parametrize("name,full", [("c3", "c3"), ("c3p", "c3p"), ("c3n", "c3n"), ("c2", "c2")])
 @pytest.mark.parametrize("threads,ttype", [(8, "frame"), (16, "frame"), (8, "slice"), (16, "slice")])
 def test_full_size_configs_threaded(name, full, threads, ttype, workdir):
-    spec = {"c2": configs.c2, "c3": configs.c3, "c3p": configs.c3p}[full]()
+    spec = {"c2": configs.c2, "c3": configs.c3, "c3p": configs.c3p, "c3n": configs.c3n}[full]()
     ivf = parity.write_stream(spec, workdir / f"{name}_mt.ivf")
     assert parity.cuda_md5(ivf, threads=threads, thread_type=ttype) == GOLDEN[name]["framemd5"]
     ivf.unlink()

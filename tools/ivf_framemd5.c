@@ -22,6 +22,7 @@
 #include <time.h>
 
 #include "libavcodec/avcodec.h"
+#include "libavcodec/vp9data.h"     /* -tables: the default probability tables of the VP9 specification */
 #include "libavutil/frame.h"
 #include "libavutil/md5.h"
 #include "libavutil/pixdesc.h"
@@ -35,8 +36,44 @@ static double now_s(void)
 
 static unsigned rl32(const unsigned char *p) { return p[0] | p[1] << 8 | p[2] << 16 | (unsigned)p[3] << 24; }
 
+static void print_tables(const ProbContext *d, const uint8_t *cf)
+{
+    printf("{\"skip\": [%d, %d, %d], \"intra\": [%d, %d, %d, %d], \"partition\": [", d->skip[0], d->skip[1], d->skip[2],
+           d->intra[0], d->intra[1], d->intra[2], d->intra[3]);
+    for (int k = 0; k < 48; k++)
+        printf("%s%d", k ? ", " : "", (&d->partition[0][0][0])[k]);
+    printf("], \"coef\": [");
+    for (int k = 0; k < 4 * 2 * 2 * 6 * 6 * 3; k++)
+        printf("%s%d", k ? ", " : "", cf[k]);
+    printf("]}\n");
+    fflush(stdout);
+}
+
+/* -probe: packets come in on stdin (IVF), one at a time; after each one is decoded the SAVED probability context 0
+ * of the decoder (VP9Context.prob_ctx[0], i.e. after backward adaptation, vp9prob.c) goes out as one JSON line.
+ * A stream generator that writes differential probability updates (vp9.c:399-455) for frame N+1 reads it to know
+ * exactly what the decoder holds (ffmpeg_hybrid_b200/streamgen.py). */
+static int probe(AVCodecContext *c)
+{
+    unsigned char hdr[32];
+    AVPacket *pkt = av_packet_alloc();
+    AVFrame *fr = av_frame_alloc();
+    if (fread(hdr, 1, 32, stdin) != 32 || memcmp(hdr, "DKIF", 4)) return 2;
+    while (fread(hdr, 1, 12, stdin) == 12) {
+        unsigned fsz = rl32(hdr);
+        if (av_new_packet(pkt, fsz) < 0 || fread(pkt->data, 1, fsz, stdin) != fsz) return 2;
+        if (avcodec_send_packet(c, pkt) < 0) { fprintf(stderr, "probe: decode error\n"); return 1; }
+        av_packet_unref(pkt);
+        while (avcodec_receive_frame(c, fr) >= 0) av_frame_unref(fr);
+        const VP9Context *s = c->priv_data;
+        /* coef[4][2][2][6][6][3] of the saved context is laid out like ff_vp9_default_coef_probs */
+        print_tables(&s->prob_ctx[0].p, &s->prob_ctx[0].coef[0][0][0][0][0][0]);
+    }
+    return 0;
+}
+
 static int nframes;
-static int do_hash = 1;
+static int do_hash = 1, do_probe;
 static FILE *raw;
 
 static void emit(AVFrame *f)
@@ -75,10 +112,26 @@ int main(int argc, char **argv)
         if (!strcmp(argv[i], "-threads") && i + 1 < argc) threads = atoi(argv[++i]);
         else if (!strcmp(argv[i], "-thread_type") && i + 1 < argc)
             ttype = !strcmp(argv[++i], "slice") ? FF_THREAD_SLICE : FF_THREAD_FRAME;
+        else if (!strcmp(argv[i], "-tables")) {
+            /* the decoder's default probabilities (ff_vp9_default_probs, ff_vp9_default_coef_probs, reference
+             * libavcodec/vp9data.c) as JSON: what a stream generator needs to write differential probability
+             * updates (vp9.c:399-455) that land on the values it wants */
+            print_tables(&ff_vp9_default_probs, &ff_vp9_default_coef_probs[0][0][0][0][0][0]);
+            return 0;
+        }
+        else if (!strcmp(argv[i], "-probe")) do_probe = 1;
         else if (!strcmp(argv[i], "-null")) do_hash = 0;
         else if (!strcmp(argv[i], "-loop") && i + 1 < argc) loops = atoi(argv[++i]);
         else if (!strcmp(argv[i], "-raw") && i + 1 < argc) raw = fopen(argv[++i], "wb");
         else in = argv[i];
+    }
+    if (do_probe) {
+        const AVCodec *codec = avcodec_find_decoder(AV_CODEC_ID_VP9);
+        AVCodecContext *c = avcodec_alloc_context3(codec);
+        c->thread_count = 1;
+        c->flags |= AV_CODEC_FLAG_BITEXACT;
+        if (avcodec_open2(c, codec, NULL) < 0) { fprintf(stderr, "open failed\n"); return 2; }
+        return probe(c);
     }
     if (!in) {
         fprintf(stderr, "usage: %s [-threads N] [-thread_type frame|slice] [-null] [-raw f] in.ivf\n", argv[0]);
