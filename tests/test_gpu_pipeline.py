@@ -278,3 +278,60 @@ def test_unsatisfied_dependency_is_an_error_not_a_hang(workdir):
     ctx.close()
     for f in frames:
         f.free()
+
+
+def test_oversubscribed_wavefronts_many_contexts(workdir):
+    """The wavefront kernels' no-deadlock argument: every cross-CTA wait points at a lower
+    block index of the same launch, and CTAs are dispatched in block-index order -- which CUDA does not promise, so
+    it is exercised where it could break: 8K key frames (272 CTAs of k_wave on 148 SMs, i.e. more CTAs than fit)
+    from two contexts while four more contexts decode other streams, all at once, 1000+ frames in total.  Every
+    frame's checksum must equal the one a context decoding alone produced, and no wait may run out of its budget
+    (vp9cuda_wait would return -EIO)."""
+    import threading
+    from ffmpeg_hybrid_b200 import binding
+    lib = binding.load()
+    specs = {"k8": configs.c4(frames=2), "c3s": configs.small_variants()["c3_small"], "c2s": configs.small_variants()["c2_small"],
+             "seg": configs.small_variants()["segment"]}
+    frames, alone = {}, {}
+    for name, spec in specs.items():
+        ivf = parity.write_stream(spec, workdir / f"stress_{name}.ivf")
+        parity.dump_records(ivf, workdir / f"stress_{name}.v9r")
+        frames[name] = binding.load_stream(lib, workdir / f"stress_{name}.v9r", pinned=True)
+        (workdir / f"stress_{name}.v9r").unlink()
+        ivf.unlink()
+        ctx = binding.Context(0)
+        alone[name] = []
+        for f in frames[name]:
+            ctx.wait(ctx.decode(f, None))
+            alone[name].append(ctx.checksum(-1))
+        ctx.close()
+    plan = [("k8", 12), ("k8", 12), ("c3s", 30), ("c2s", 50), ("seg", 40), ("c3s", 30)]     # (stream, passes)
+    total = sum(len(frames[n]) * p for n, p in plan)
+    assert total >= 1000
+    errs = []
+    start = threading.Barrier(len(plan))
+
+    def worker(name, passes):
+        try:
+            ctx = binding.Context(0, frames_in_flight=3)
+            hs = [ctx.stage(f) for f in frames[name]]
+            start.wait()
+            for _ in range(passes):
+                for k, h in enumerate(hs):
+                    ctx.wait(ctx.run_staged(h, None))
+                    if ctx.checksum(-1) != alone[name][k]:
+                        raise RuntimeError(f"{name}: frame {k} differs")
+            ctx.close()
+        except Exception as e:  # noqa: BLE001
+            errs.append((name, repr(e)))
+            start.abort()
+
+    ts = [threading.Thread(target=worker, args=p) for p in plan]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join()
+    assert not errs, errs
+    for fl in frames.values():
+        for f in fl:
+            f.free()

@@ -123,3 +123,44 @@ def test_slot_loop_filter(bpp):
     assert rc == 0
     bad = [cases[i] for i in range(n) if not np.array_equal(pix[i], want[i])]
     assert not bad, f"loop filter differs for {bad[:6]}"
+
+
+@pytest.mark.parametrize("bpp", BPPS)
+def test_slot_loop_filter_mix2(bpp):
+    """loop_filter_mix2[wd1][wd2][dir] (vp9dsp.h:96-104) against vp9cuda_slot_loop_filter: the second 8 lines of a
+    mix2 call are the first 8 lines of the tile moved by 8 lines"""
+    from ffmpeg_hybrid_b200 import binding
+    lib, ref = binding.load(), ref_lib()
+    rng = np.random.default_rng(850 + bpp)
+    bps = 2 if bpp > 8 else 1
+    off = (32 * 64 + 32) * bps
+    cases, tiles, want = [], [], []
+    for kind in range(4):
+        for rep in range(4):
+            for w1 in range(2):
+                for w2 in range(2):
+                    for d in range(2):
+                        E = [int(rng.integers(1, 255)) for _ in range(2)]
+                        I = [int(rng.integers(1, 64)) for _ in range(2)]
+                        H = [int(rng.integers(0, 4)) for _ in range(2)]
+                        t0 = lf_tile(rng, bpp, kind)
+                        a = t0.copy()
+                        ref.ref_loop_filter_mix2(bpp, w1, w2, d, ptr(a, off), C.c_ssize_t(64 * bps),
+                                                 E[0] | E[1] << 8, I[0] | I[1] << 8, H[0] | H[1] << 8)
+                        want.append(a)
+                        cases.append((4 << w1, d, 8, E[0], I[0], H[0]))
+                        tiles.append(t0.copy())
+                        cases.append((4 << w2, d, 8, E[1], I[1], H[1]))
+                        tiles.append(np.roll(t0, -8, axis=0 if d == 0 else 1).copy())
+    n = len(cases)
+    pix = np.stack(tiles)
+    a8 = [u8([c[k] for c in cases]) for k in (0, 1, 2)]
+    a32 = [np.ascontiguousarray(np.asarray([c[k] for c in cases], np.int32)) for k in (3, 4, 5)]
+    rc = lib.vp9cuda_slot_loop_filter(0, bpp, n, ptr(a8[0]), ptr(a8[1]), ptr(a8[2]), ptr(a32[0]), ptr(a32[1]),
+                                      ptr(a32[2]), ptr(pix))
+    assert rc == 0
+    for i, w in enumerate(want):
+        d = cases[2 * i][1]
+        sl0 = (slice(32, 40), slice(None)) if d == 0 else (slice(None), slice(32, 40))
+        sl1 = (slice(40, 48), slice(None)) if d == 0 else (slice(None), slice(40, 48))
+        assert np.array_equal(w[sl0], pix[2 * i][sl0]) and np.array_equal(w[sl1], pix[2 * i + 1][sl0]), cases[2 * i]

@@ -101,3 +101,36 @@ def test_loop_filter(bpp):
                         ref.ref_loop_filter_16(bpp, d, ptr(a, off), C.c_ssize_t(64 * bps), E, I, H)
                         mod.model_loop_filter(bpp, 16, d, 16, ptr(b, off), C.c_ssize_t(64 * bps), E, I, H)
                         assert np.array_equal(a, b), f"loop_filter_16 mismatch bpp={bpp} dir={d} kind={kind}"
+
+
+def _shift_lines(t, d, n):
+    """the tile moved by n lines against the line direction of an edge (dir 0: column edge, lines run down)"""
+    return np.roll(t, -n, axis=0 if d == 0 else 1)
+
+
+@pytest.mark.parametrize("bpp", BPPS)
+def test_loop_filter_mix2(bpp):
+    """loop_filter_mix2[wd1][wd2][dir] (vp9dsp.h:96-104): two adjacent 8-line filters of width 4 or 8 with their
+    own limits in one call -- the restatement runs it as two 8-line calls"""
+    rng = np.random.default_rng(450 + bpp)
+    ref, mod = ref_lib(), model_lib()
+    bps = 2 if bpp > 8 else 1
+    off = (32 * 64 + 32) * bps
+    for kind in range(4):
+        for rep in range(6):
+            for w1 in range(2):
+                for w2 in range(2):
+                    for d in range(2):
+                        E = [int(rng.integers(1, 255)) for _ in range(2)]
+                        I = [int(rng.integers(1, 64)) for _ in range(2)]
+                        H = [int(rng.integers(0, 4)) for _ in range(2)]
+                        t0 = lf_tile(rng, bpp, kind)
+                        a = t0.copy()
+                        ref.ref_loop_filter_mix2(bpp, w1, w2, d, ptr(a, off), C.c_ssize_t(64 * bps),
+                                                 E[0] | E[1] << 8, I[0] | I[1] << 8, H[0] | H[1] << 8)
+                        b0, b1 = t0.copy(), _shift_lines(t0, d, 8).copy()
+                        mod.model_loop_filter(bpp, 4 << w1, d, 8, ptr(b0, off), C.c_ssize_t(64 * bps), E[0], I[0], H[0])
+                        mod.model_loop_filter(bpp, 4 << w2, d, 8, ptr(b1, off), C.c_ssize_t(64 * bps), E[1], I[1], H[1])
+                        sl0 = (slice(32, 40), slice(None)) if d == 0 else (slice(None), slice(32, 40))
+                        sl1 = (slice(40, 48), slice(None)) if d == 0 else (slice(None), slice(40, 48))
+                        assert np.array_equal(a[sl0], b0[sl0]) and np.array_equal(a[sl1], b1[sl0]), (bpp, w1, w2, d, kind)
