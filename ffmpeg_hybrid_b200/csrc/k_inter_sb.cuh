@@ -85,6 +85,94 @@ template <class P> struct IsbGeo {
     }
 };
 
+/* ---- 16-bit pixels: two outputs per lane, 8-tap filters as four packed dot products ------------------------
+ * The 8-tap kernels fit signed bytes for every phase but 0 (which is never filtered: fx / fy == 0 copies), so an
+ * output is 64 + sum over four (pixel pair) x (tap pair) dp2a, with pixel pairs taken as 32-bit words from shared
+ * memory.  Same arithmetic as filt8 (vp9_pred.h): (sum + 64) >> 7, clipped. */
+__device__ __forceinline__ void taps_packed(int filter, int phase, int &t0, int &t1)
+{
+    const int16_t *F = subpel_taps(filter, phase);
+    t0 = (int)((unsigned)(F[0] & 0xff) | (unsigned)(F[1] & 0xff) << 8 | (unsigned)(F[2] & 0xff) << 16 | (unsigned)(F[3] & 0xff) << 24);
+    t1 = (int)((unsigned)(F[4] & 0xff) | (unsigned)(F[5] & 0xff) << 8 | (unsigned)(F[6] & 0xff) << 16 | (unsigned)(F[7] & 0xff) << 24);
+}
+__device__ __forceinline__ int filt8_pairs(unsigned p0, unsigned p1, unsigned p2, unsigned p3, int t0, int t1, int bpp)
+{
+    int acc = 64;
+    acc = __dp2a_lo((int)p0, t0, acc);
+    acc = __dp2a_hi((int)p1, t0, acc);
+    acc = __dp2a_lo((int)p2, t1, acc);
+    acc = __dp2a_hi((int)p3, t1, acc);
+    return clip_pixel(acc >> 7, bpp);
+}
+
+/* horizontal pass of one unit for the lane (row parity rp, output pair j): rows r0 + rp, r0 + rp + 2, ... < r1 */
+__device__ __forceinline__ void mc_h_pairs(const unsigned char *wb, int pitch, int a, int j, int rp, int r0, int r1, int w,
+                                           uint16_t *m, int filter, int fx, int bpp)
+{
+    const int q = a + 2 * j, wi = q >> 1, odd = q & 1;
+    unsigned *m32 = (unsigned *)m + j;
+    const int hw = w >> 1;
+    if (fx) {
+        int t0, t1;
+        taps_packed(filter, fx, t0, t1);
+        for (int r = r0 + rp; r < r1; r += 2) {
+            const unsigned *row = (const unsigned *)(wb + r * pitch) + wi;
+            const unsigned w0 = row[0], w1 = row[1], w2 = row[2], w3 = row[3], w4 = row[4];
+            const unsigned f0 = __funnelshift_r(w0, w1, 16), f1 = __funnelshift_r(w1, w2, 16),
+                           f2 = __funnelshift_r(w2, w3, 16), f3 = __funnelshift_r(w3, w4, 16);
+            /* output 2j starts at pixel q, output 2j + 1 at q + 1; an odd q sits in the high half of its word */
+            const int v0 = odd ? filt8_pairs(f0, f1, f2, f3, t0, t1, bpp) : filt8_pairs(w0, w1, w2, w3, t0, t1, bpp);
+            const int v1 = odd ? filt8_pairs(w1, w2, w3, w4, t0, t1, bpp) : filt8_pairs(f0, f1, f2, f3, t0, t1, bpp);
+            m32[r * hw] = (unsigned)v0 | (unsigned)v1 << 16;
+        }
+    } else {
+        for (int r = r0 + rp; r < r1; r += 2) {
+            const uint16_t *s = (const uint16_t *)(wb + r * pitch) + q;
+            m32[r * hw] = (unsigned)s[3] | (unsigned)s[4] << 16;
+        }
+    }
+}
+
+/* vertical pass: output rows rp, rp + 2, ... < h of columns 2j, 2j + 1, written (or averaged) into the tile */
+__device__ __forceinline__ void mc_v_pairs(const uint16_t *m, int j, int rp, int w, int h, uint16_t *dst, int dp, int filter,
+                                           int fy, bool avg, int bpp)
+{
+    const unsigned *m32 = (const unsigned *)m + j;
+    const int hw = w >> 1, dw = dp >> 1;
+    unsigned *d32 = (unsigned *)dst + j;
+    auto put = [&](int y, int v0, int v1) {
+        if (avg) {
+            const unsigned o = d32[y * dw];
+            v0 = ((int)(o & 0xffff) + v0 + 1) >> 1;
+            v1 = ((int)(o >> 16) + v1 + 1) >> 1;
+        }
+        d32[y * dw] = (unsigned)v0 | (unsigned)v1 << 16;
+    };
+    if (fy) {
+        int t0, t1;
+        taps_packed(filter, fy, t0, t1);
+        /* vertically adjacent samples packed into words: (row, row + 1) of the low column and of the high column */
+        int y = rp;
+        unsigned a0 = m32[(y + 0) * hw], a1 = m32[(y + 1) * hw], a2 = m32[(y + 2) * hw], a3 = m32[(y + 3) * hw],
+                 a4 = m32[(y + 4) * hw], a5 = m32[(y + 5) * hw];
+        unsigned l0 = __byte_perm(a0, a1, 0x5410), h0 = __byte_perm(a0, a1, 0x7632);
+        unsigned l1 = __byte_perm(a2, a3, 0x5410), h1 = __byte_perm(a2, a3, 0x7632);
+        unsigned l2 = __byte_perm(a4, a5, 0x5410), h2 = __byte_perm(a4, a5, 0x7632);
+        for (; y < h; y += 2) {
+            const unsigned b0 = m32[(y + 6) * hw], b1 = m32[(y + 7) * hw];
+            const unsigned l3 = __byte_perm(b0, b1, 0x5410), h3 = __byte_perm(b0, b1, 0x7632);
+            put(y, filt8_pairs(l0, l1, l2, l3, t0, t1, bpp), filt8_pairs(h0, h1, h2, h3, t0, t1, bpp));
+            l0 = l1; l1 = l2; l2 = l3;
+            h0 = h1; h1 = h2; h2 = h3;
+        }
+    } else {
+        for (int y = rp; y < h; y += 2) {
+            const unsigned v = m32[(y + 3) * hw];
+            put(y, (int)(v & 0xffff), (int)(v >> 16));
+        }
+    }
+}
+
 /* Unscaled prediction of `cnt` units of w x h samples (w = 4 << wl <= 32, h = 4 << hl <= 16) by one
  * warp.  geom[0 .. cnt): the units; arena: ISB_ARENA bytes, 16-byte aligned, owned by the warp;
  * tile: base of the output (any address space); avg: average into the tile instead of storing. */
@@ -133,10 +221,16 @@ __device__ __forceinline__ void mc_batch(const UGeom *geom, int cnt, int wl, int
         isb_cp_wait_all();
         __syncwarp();
     }
-    /* ---- lanes = (unit u, output column c) ---- */
+    /* ---- lanes = (unit u, output column c); 16-bit pixels under an 8-tap filter: (unit u, row parity, column pair) ---- */
     const int u = lane >> (2 + wl), c = lane & (w - 1);
     const bool act = u < cnt;
-    if (act) {
+    const bool pairs = sizeof(P) == 2 && act && geom[u].filter != FILTER_BILINEAR;
+    const int prp = c >> (1 + wl), pj = c & ((w >> 1) - 1);
+    if (pairs) {
+        const UGeom &g = geom[u];
+        mc_h_pairs(win + u * wbytes, pitch, g.a, pj, prp, g.fy ? 0 : 3, g.fy ? rows : h + 3, w,
+                   (uint16_t *)(mid + u * rows * w), g.filter, g.fx, bpp);
+    } else if (act) {
         const UGeom &g = geom[u];
         const unsigned char *wb = win + u * wbytes;
         P *m = mid + u * rows * w;
@@ -155,7 +249,10 @@ __device__ __forceinline__ void mc_batch(const UGeom *geom, int cnt, int wl, int
         }
     }
     __syncwarp();
-    if (act) {
+    if (pairs) {
+        const UGeom &g = geom[u];
+        mc_v_pairs((const uint16_t *)(mid + u * rows * w), pj, prp, w, h, (uint16_t *)(tile + g.dst), g.dpitch, g.filter, g.fy, avg, bpp);
+    } else if (act) {
         const UGeom &g = geom[u];
         const P *m = mid + u * rows * w + c;
         P *dst = tile + g.dst + c;

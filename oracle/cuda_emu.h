@@ -160,6 +160,17 @@ static inline int atomicCAS(int *p, int cmp, int v)
     __atomic_compare_exchange_n(p, &cmp, v, false, __ATOMIC_SEQ_CST, __ATOMIC_SEQ_CST);
     return cmp;
 }
+static inline int __dp2a_lo(int a, int b, int c) { return c + (int16_t)(a & 0xffff) * (int8_t)(b & 0xff) + (int16_t)(a >> 16) * (int8_t)(b >> 8 & 0xff); }
+static inline int __dp2a_hi(int a, int b, int c) { return c + (int16_t)(a & 0xffff) * (int8_t)(b >> 16 & 0xff) + (int16_t)(a >> 16) * (int8_t)(b >> 24 & 0xff); }
+static inline unsigned __funnelshift_r(unsigned lo, unsigned hi, unsigned s) { s &= 31; return s ? lo >> s | hi << (32 - s) : lo; }
+static inline unsigned __byte_perm(unsigned x, unsigned y, unsigned sel)
+{
+    const uint64_t v = (uint64_t)y << 32 | x;
+    unsigned r = 0;
+    for (int i = 0; i < 4; i++)
+        r |= (unsigned)(v >> (8 * (sel >> (4 * i) & 7)) & 0xff) << (8 * i);
+    return r;
+}
 static inline int __reduce_max_sync(unsigned mask, int v)
 {
     emu::Cta *c = emu::g_cta;
