@@ -21,7 +21,7 @@ def test_emulated_kernel_equals_restatement(name, workdir):
     ivf = parity.write_stream(configs.small_variants()[name], workdir / f"emu_{name}.ivf")
     v9r = workdir / f"emu_{name}.v9r"
     parity.dump_records(ivf, v9r)
-    cmd = [str(EMU), str(v9r)] + (["3"] if name in BIG else [])
+    cmd = [str(EMU), str(v9r), "3" if name in BIG else "5"]
     p = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
     assert p.returncode == 0, p.stderr[-1500:]
     assert " 0 differing" in p.stderr

@@ -55,5 +55,26 @@ def launches(path):
     print(f"{'total':60s} {sum(cnt.values()):8d} {s:10.3f}")
 
 
+def traffic(path, source="profiles/"):
+    """per-kernel-family mean DRAM bytes per launch of a `--set full` capture, as JSON for bench.py's roofline.traffic"""
+    import json
+    rows = [r for r in csv.reader(open(path)) if r]
+    while rows and "Kernel Name" not in rows[0]:
+        rows.pop(0)
+    hdr, units = rows[0], rows[1]
+    kn, rd, wr = hdr.index("Kernel Name"), hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
+    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    fam = {"k_wave": "intra_lf_wavefront", "k_inter": "inter_pred", "k_itx": "itxfm_add"}
+    acc = defaultdict(list)
+    for r in rows[2:]:
+        for k, name in fam.items():
+            if k in r[kn]:
+                acc[name].append(float(r[rd].replace(",", "")) * scale[units[rd]] + float(r[wr].replace(",", "")) * scale[units[wr]])
+    out = {n: {"dram_bytes_per_launch": sum(v) / len(v), "launches_captured": len(v),
+               "source": f"{source} (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum, mean over the captured "
+                         "launches of tools/ncu_frames.py c3 3: one key frame + two inter frames)"} for n, v in acc.items()}
+    print(json.dumps(out, indent=1))
+
+
 if __name__ == "__main__":
-    {"full": full, "launches": launches}[sys.argv[1]](sys.argv[2])
+    {"full": full, "launches": launches, "traffic": traffic}[sys.argv[1]](*sys.argv[2:])
