@@ -24,7 +24,7 @@ def built():
     pieces are compiled; on the GPU box they arrive prebuilt with the snapshot."""
     need = [ROOT / "ffmpeg_hybrid_b200" / "libvp9cuda.so", ROOT / "oracle" / "_ref" / "ffvp9_ref",
             ROOT / "oracle" / "_ref" / "libvp9dsp_ref.so", ROOT / "oracle" / "_ref" / "libreplay_model.so",
-            ROOT / "oracle" / "_ref" / "replay_model", ROOT / "ffmpeg_hybrid_b200" / "host" / "_build" / "ffvp9_cuda", ROOT / "oracle" / "_ref" / "emu_inter",
+            ROOT / "oracle" / "_ref" / "replay_model", ROOT / "ffmpeg_hybrid_b200" / "host" / "_build" / "ffvp9_cuda", ROOT / "oracle" / "_ref" / "emu_inter", ROOT / "oracle" / "_ref" / "author" / "ffvp9_author",
             ROOT / "oracle" / "_ref" / "ffvp9_multi_ref", ROOT / "ffmpeg_hybrid_b200" / "host" / "_build" / "ffvp9_multi"]
     if not all(p.exists() for p in need):
         if not _have_reference_tree() and not (ROOT / "oracle" / "_ref" / "ffvp9_ref").exists():
