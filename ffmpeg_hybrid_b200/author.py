@@ -46,4 +46,7 @@ def authored_variants() -> Dict[str, Tuple[StreamSpec, str]]:
     # vectors far beyond the frame: +-256 pixels on a 200x136 frame, 12 bit
     st = configs.small_variants()["hbd12"]
     out["authored_far"] = (st, "seed=44,mv_range=2048,newmv=80")
+    # large blocks (most partition trees forced to "none") under long compound vectors: the 64- and 32-wide mc slots
+    # with every phase, windows of up to 71 x 71 samples hanging over the frame's edges
+    out["authored_big"] = (configs.c2(frames=6, w=712, h=456, seed=45), "seed=45,mv_range=512,newmv=75,part_none=70")
     return out

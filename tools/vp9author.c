@@ -21,8 +21,9 @@
  *                      encodes joint / sign / class / bits / fraction / hp of (target - predictor),
  *                      the predictor being the one find_ref_mvs just computed (vp9mvs.c:297-360);
  *   inter mode       : newmv=<percent> of the inter-mode trees are forced to NEWMV;
+ *   partition        : part_none=<percent> of the partition trees are forced to PARTITION_NONE (large blocks);
  *   tile marker      : 0 (vp9.c:1345).
- * Policy: $VP9AUTHOR = "seed=7,mv_range=512,newmv=70".
+ * Policy: $VP9AUTHOR = "seed=7,mv_range=512,newmv=70,part_none=50".
  *
  * usage: ffvp9_author seed.ivf out.ivf        (single-frame packets; decoder runs on one thread)
  */
@@ -100,8 +101,8 @@ static struct {
     int script_len, script_pos;
     const VPXRangeCoder *script_c;
     uint64_t rng;
-    int mv_range, newmv_pct;
-} A = { .rng = 0x9E3779B97F4A7C15ull, .mv_range = 512, .newmv_pct = 0 };
+    int mv_range, newmv_pct, part_none_pct;
+} A = { .rng = 0x9E3779B97F4A7C15ull, .mv_range = 512, .newmv_pct = 0, .part_none_pct = 0 };
 
 static unsigned rnd(void)
 {
@@ -190,6 +191,11 @@ int ff_vp9author_tree(const VPXRangeCoder *c, const int8_t (*tree)[2], const uin
         A.script_c = c;
         script_tree(tree, NEWMV);
     }
+    if (tree == ff_vp9_partition_tree && !(A.script_pos < A.script_len) && (int)(rnd() % 100) < A.part_none_pct) {
+        A.script_len = A.script_pos = 0;
+        A.script_c = c;
+        script_tree(tree, PARTITION_NONE);
+    }
     do {
         i = tree[i][ff_vp9author_bit(c, probs[i])];
     } while (i > 0);
@@ -248,6 +254,7 @@ int main(int argc, char **argv)
             if (sscanf(tok, "seed=%d", &v) == 1) A.rng ^= (uint64_t)v * 0xD6E8FEB86659FD93ull;
             else if (sscanf(tok, "mv_range=%d", &v) == 1) A.mv_range = v;
             else if (sscanf(tok, "newmv=%d", &v) == 1) A.newmv_pct = v;
+            else if (sscanf(tok, "part_none=%d", &v) == 1) A.part_none_pct = v;
             else { fprintf(stderr, "vp9author: unknown policy item %s\n", tok); return 2; }
         }
         free(s);
