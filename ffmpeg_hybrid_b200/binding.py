@@ -159,10 +159,11 @@ class HostFrame:
 class OutFrame:
     """Pinned host planes for the visible crop of one picture (framemd5 layout)."""
 
-    def __init__(self, lib: C.CDLL, w: int, h: int, bpp: int):
+    def __init__(self, lib: C.CDLL, w: int, h: int, bpp: int, ss: int = 1):
         self.lib = lib
         bps = 2 if bpp > 8 else 1
-        self.shape = [(h, w), ((h + 1) // 2, (w + 1) // 2), ((h + 1) // 2, (w + 1) // 2)]
+        ch = ((h + ss) >> ss, (w + ss) >> ss)             # ss = 1: 4:2:0, ss = 0: 4:4:4
+        self.shape = [(h, w), ch, ch]
         self.bps = bps
         self.sizes = [r * c * bps for r, c in self.shape]
         self.base = lib.vp9cuda_host_alloc(sum(self.sizes))

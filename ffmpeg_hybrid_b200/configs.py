@@ -241,6 +241,18 @@ def small_variants() -> Dict[str, StreamSpec]:
         f.highprecisionmvs = False
     out["wide64"] = st
     out["c3n_small"] = c3n(frames=8, w=784, h=464)           # natural statistics through forward probability updates
+    # 4:4:4 (profiles 1 and 3): every plane predicted, transformed and filtered like luma
+    st = StreamSpec(328, 200, profile=1, bitdepth=8, seed=61, ss_h=0, ss_v=0)     # 8-bit, compound, 2 tile columns
+    st.frames = _ippp(5, tile_cols=1, compound=True)
+    out["p1_444"] = st
+    st = StreamSpec(400, 240, profile=3, bitdepth=10, seed=62, ss_h=0, ss_v=0)    # 10-bit with C3's hidden half-size
+    st.frames = c3(frames=6, w=400, h=240).frames                                   # frames and scaled references
+    out["p3_444_10"] = st
+    st = StreamSpec(200, 136, profile=3, bitdepth=12, seed=63, ss_h=0, ss_v=0)    # 12-bit, intra-only frame, lossless tail
+    st.frames = _ippp(5, compound=True)
+    st.frames[2] = FrameSpec(intraonly=True, show=False, refreshrefmask=0x06, resetctx=0)
+    st.frames[4].yac_qi = 0
+    out["p3_444_12"] = st
     st = StreamSpec(72, 40, seed=11)                         # tiny, single superblock column
     st.frames = _ippp(4, compound=True)
     out["tiny"] = st

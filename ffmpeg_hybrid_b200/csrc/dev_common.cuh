@@ -71,6 +71,11 @@ struct FrameDesc {
     SurfDesc cur;
     SurfDesc ref[3];                 /* by b->ref index (LAST, GOLDEN, ALTREF) */
     int w, h, cols, rows, sb_cols, sb_rows, bpp;
+    int mono;                        /* -1: a 4:2:0 frame, all three planes in one go.  0..2: one plane of a 4:4:4 frame.  There
+                                        every plane is predicted, transformed and filtered exactly like luma (full size, luma
+                                        vector units, own vectors per 4x4, luma loop-filter masks: vp9_mc_template.c:78-121,
+                                        vp9lpf.c:214 with ss_h == ss_v == 0), so the frame runs as three passes in which
+                                        cur / ref plane 0 are that plane and only its records count, as plane 0 */
     uint16_t mvscale[3][2];
     uint8_t mvstep[3][2];
     uint8_t lossless, lf_level;

@@ -354,7 +354,7 @@ __device__ __forceinline__ void isb_block_units(const FrameDesc &f, uint32_t bi,
     const int nref = b.comp ? 2 : 1;
     for (int i = 0; i < nref; i++) {
         const int sc = f.mvscale[b.ref[i]][0] ? 12 : 0;
-        for (int pl = 0; pl < 3; pl++) {
+        for (int pl = 0; pl < (f.mono >= 0 ? 1 : 3); pl++) {
             const int ch = pl > 0, S = 64 >> ch;
             const int lx = (cx * 8) >> ch, ly = (cy * 8) >> ch;
             IUnit un;
@@ -473,7 +473,12 @@ __global__ void __launch_bounds__(ISB_THREADS, 3) k_inter_sb(const __grid_consta
             const Vp9CudaTx *tx = f.tx + f.lane_tx_base[si.lane] + si.tx_start;
             C *buf = (C *)arena;
             for (int k = warp; k < si.tx_count; k += ISB_WARPS) {
-                const Vp9CudaTx r = tx[k];
+                Vp9CudaTx r = tx[k];
+                if (f.mono >= 0) {                 /* one plane of a 4:4:4 frame: its blocks only, as plane 0 */
+                    if (r.plane != f.mono)
+                        continue;
+                    r.plane = 0;
+                }
                 const int S = r.plane ? 32 : 64;
                 GlobalPix<P> pix;
                 pix.stride = S;
@@ -504,7 +509,7 @@ __global__ void __launch_bounds__(ISB_THREADS, 3) k_inter_sb(const __grid_consta
             if (PS == 2) *(uint4 *)d = *(const uint4 *)s;
             else         *(uint2 *)d = *(const uint2 *)s;
         }
-        for (int i = tid; i < 512; i += ISB_THREADS) {            /* chroma: 2 planes x 32 rows x 8 cells of 4 samples */
+        for (int i = tid; i < (f.mono >= 0 ? 0 : 512); i += ISB_THREADS) {   /* chroma: 2 planes x 32 rows x 8 cells of 4 samples */
             const int pl = 1 + (i >> 8), r = i >> 3 & 31, cxl = i & 7;
             if (s_cell[(r >> 2) * 8 + cxl] < 0)
                 continue;

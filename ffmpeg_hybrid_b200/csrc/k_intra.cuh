@@ -66,23 +66,27 @@ __device__ __forceinline__ int intra_chunks(int tx) { return tx == 0 ? 1 : 2 << 
  *     (0x8000 | chunk count) followed by one entry per 32-pixel chunk (record | chunk << 9). */
 __global__ void __launch_bounds__(128) k_intra_prep(const __grid_constant__ FrameDesc f)
 {
-    __shared__ uint32_t keys[512];
-    __shared__ uint32_t inf[512];
-    __shared__ uint8_t loc[512];
+    __shared__ uint32_t keys[1024];
+    __shared__ uint32_t inf[768];
+    __shared__ uint8_t loc[768];
+    __shared__ int n_match;
     __shared__ uint8_t lvl[3 * 256];
     __shared__ unsigned any_res, need_top;
     const int sb = blockIdx.x, tid = threadIdx.x;
     const Vp9CudaSbIndex si = f.sb_index[sb];
-    const int n = si.itx_count;
+    /* a pass over one plane of a 4:4:4 frame (f.mono) sees the records of all three planes (up to 768) and keeps
+     * its own (up to 256), as plane 0 */
+    const int ntot = si.itx_count;
+    int n = ntot;
     const uint32_t g0 = n ? f.lane_itx_base[si.lane] + si.itx_start : 0;
-    if (n == 0 || n > INTRA_SB_RECS) {
+    if (n == 0 || n > (f.mono >= 0 ? 2 * INTRA_SB_RECS : INTRA_SB_RECS)) {
         if (tid == 0) {
             IntraSb o = { g0, 0, 0, 0, 0, 0 };
             f.isb[sb] = o;
         }
         return;
     }
-    if (tid == 0) { any_res = 0; need_top = 0; }
+    if (tid == 0) { any_res = 0; need_top = 0; n_match = 0; }
     int m = 32;
     while (m < n) m <<= 1;
     const int sbx = sb % f.sb_cols, sby = sb / f.sb_cols;
@@ -90,8 +94,11 @@ __global__ void __launch_bounds__(128) k_intra_prep(const __grid_constant__ Fram
     __syncthreads();
     for (int i = tid; i < m; i += 128) {
         uint32_t key = 0xffffffffu;
-        if (i < n) {
-            const Vp9CudaIntraTx &r = f.itx[g0 + i];
+        if (i < n && (f.mono < 0 || f.itx[g0 + i].plane == f.mono)) {
+            Vp9CudaIntraTx r = f.itx[g0 + i];
+            if (f.mono >= 0)
+                r.plane = 0;
+            atomicAdd(&n_match, 1);
             key = (uint32_t)r.level << 10 | i;
             const int ch = r.plane > 0;
             const int lx = r.x4 - sbx * (16 >> ch), ly = r.y4 - sby * (16 >> ch);
@@ -134,6 +141,14 @@ __global__ void __launch_bounds__(128) k_intra_prep(const __grid_constant__ Fram
             }
     };
     sort_keys();
+    n = n_match;                               /* the records that are not this pass's sort behind them */
+    if (n == 0) {
+        if (tid == 0) {
+            IntraSb o = { g0, 0, 0, 0, 0, 0 };
+            f.isb[sb] = o;
+        }
+        return;
+    }
     /* local depth, one frame-wide depth value (= set of mutually independent blocks) at a time */
     for (int pos = 0; pos < n;) {
         const uint32_t L = keys[pos] >> 10;
@@ -188,7 +203,9 @@ __global__ void __launch_bounds__(128) k_intra_prep(const __grid_constant__ Fram
     for (int k = tid; k < n; k += 128) {
         const int i = keys[k] & 1023;
         const uint32_t v = inf[i];
-        const Vp9CudaIntraTx &r = f.itx[g0 + i];
+        Vp9CudaIntraTx r = f.itx[g0 + i];
+        if (f.mono >= 0)
+            r.plane = 0;
         IntraRec o;
         o.lx = v & 15; o.ly = v >> 4 & 15;
         o.plane = r.plane; o.tx = r.tx; o.mode = v >> 12 & 15; o.txtp = r.txtp;
@@ -510,6 +527,8 @@ __device__ __forceinline__ void intra_row(const FrameDesc &f, const int row, uns
             if (need_tile) {
 #pragma unroll
                 for (int pl = 0; pl < 3; pl++) {
+                    if (pl && f.mono >= 0)
+                        break;                       /* one plane of a 4:4:4 frame */
                     const int S = pl ? 32 : 64, rsb = pl ? L::RSBC : L::RSBY;
                     const int cpr = S * (int)sizeof(P) / 16;
                     const int stride = f.cur.stride[pl];
@@ -564,6 +583,8 @@ __device__ __forceinline__ void intra_row(const FrameDesc &f, const int row, uns
                 __syncwarp();
 #pragma unroll
                 for (int pl = 0; pl < 3; pl++) {
+                    if (pl && f.mono >= 0)
+                        break;
                     const int S = pl ? 32 : 64;
                     const int cpr = S * (int)sizeof(P) / 16;
                     const int stride = f.cur.stride[pl];
@@ -592,6 +613,8 @@ __device__ __forceinline__ void intra_row(const FrameDesc &f, const int row, uns
             __syncwarp();
             if (info[c].count > 0) {
                 auto store_rows = [&](int pl, int r0, int r1) {
+                    if (pl && f.mono >= 0)
+                        return;
                     const int S = pl ? 32 : 64, rsb = pl ? L::RSBC : L::RSBY;
                     const int cpr = S * (int)sizeof(P) / 16;
                     const int stride = f.cur.stride[pl];

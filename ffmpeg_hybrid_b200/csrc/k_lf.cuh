@@ -411,7 +411,7 @@ __device__ __forceinline__ void lf_cta(const FrameDesc &f, int idx, unsigned cha
     unsigned char *ring = sm + L::O_RING;
     LfSched *sched = (LfSched *)(sm + L::O_SCHED);
     uint8_t *lut = sm + L::O_LUT;
-    const int pl = idx % 3, row = idx / 3;
+    const int pl = f.mono >= 0 ? 0 : idx % 3, row = f.mono >= 0 ? idx : idx / 3;     /* 4:4:4: one plane per launch */
     if (threadIdx.x == 0) {
         sig.body = 0; sig.top = 0; sig.done = 0; sig.stored = 0;
     }

@@ -79,6 +79,7 @@ struct Surface {
     void *pl[3] = { nullptr, nullptr, nullptr };
     int stride[3] = { 0, 0, 0 };       /* pixels */
     int w = 0, h = 0, bpp = 0, aw = 0, ah = 0;
+    int ss = 1;                        /* chroma subsampling in both directions: 1 = 4:2:0, 0 = 4:4:4 */
     int refs = 0;                      /* reference slots + "current" holding this surface */
     cudaEvent_t ready = nullptr;       /* recorded on the compute stream when the picture is final */
     cudaEvent_t d2h_done = nullptr;    /* recorded on the download stream after the last copy-out */
@@ -88,10 +89,12 @@ struct Surface {
 /* per-superblock record capacities of a lane ring (include/vp9cuda.h, Vp9CudaLaneRing) */
 enum { CAP_BLK = 64, CAP_TX = 384, CAP_ITX = 384, CAP_COEF = 6144 };
 inline int coef_entry_bytes(int bpp) { return bpp > 8 ? (int)sizeof(Vp9CudaCoef32) : (int)sizeof(Vp9CudaCoef16); }
-inline size_t ring_bytes_per_sb(int ceb)
+/* k = cap_scale(): a 4:4:4 superblock carries twice the samples of a 4:2:0 one */
+inline int cap_scale(const Vp9CudaFrameHeader *h) { return (h->ss_h && h->ss_v) ? 1 : 2; }
+inline size_t ring_bytes_per_sb(int ceb, int k)
 {
-    return (size_t)CAP_BLK * sizeof(Vp9CudaInterBlock) + (size_t)CAP_TX * sizeof(Vp9CudaTx) +
-           (size_t)CAP_ITX * sizeof(Vp9CudaIntraTx) + (size_t)CAP_COEF * ceb;     /* a multiple of 64 */
+    return (size_t)CAP_BLK * sizeof(Vp9CudaInterBlock) + (size_t)k * CAP_TX * sizeof(Vp9CudaTx) +
+           (size_t)k * CAP_ITX * sizeof(Vp9CudaIntraTx) + (size_t)k * CAP_COEF * ceb;     /* a multiple of 64 */
 }
 
 /* device buffer that only ever grows; every (re)allocation is counted (vp9cuda_get_stat "allocs") */
@@ -291,10 +294,10 @@ struct Vp9CudaCtx {
     bool phase_on = false;
 };
 
-static Surface *surface_get(Vp9CudaCtx *c, int w, int h, int bpp)
+static Surface *surface_get(Vp9CudaCtx *c, int w, int h, int bpp, int ss)
 {
     for (Surface *s : c->pool)
-        if (!s->refs && s->w == w && s->h == h && s->bpp == bpp) {
+        if (!s->refs && s->w == w && s->h == h && s->bpp == bpp && s->ss == ss) {
             s->refs = 1;
             if (s->has_d2h) {               /* a copy-out of its previous picture may still be in flight */
                 cudaStreamWaitEvent(c->stream, s->d2h_done, 0);
@@ -312,7 +315,7 @@ static Surface *surface_get(Vp9CudaCtx *c, int w, int h, int bpp)
     for (Surface *s : c->pool) idle += !s->refs;
     for (size_t i = 0; idle > POOL_IDLE_MAX && i < c->pool.size();) {
         Surface *s = c->pool[i];
-        if (!s->refs && (s->w != w || s->h != h || s->bpp != bpp)) {
+        if (!s->refs && (s->w != w || s->h != h || s->bpp != bpp || s->ss != ss)) {
             if (s->has_d2h) cudaEventSynchronize(s->d2h_done);
             for (int p = 0; p < 3; p++) cudaFree(s->pl[p]);
             cudaEventDestroy(s->ready); cudaEventDestroy(s->d2h_done);
@@ -324,11 +327,11 @@ static Surface *surface_get(Vp9CudaCtx *c, int w, int h, int bpp)
         }
     }
     Surface *s = new Surface;
-    s->w = w; s->h = h; s->bpp = bpp;
+    s->w = w; s->h = h; s->bpp = bpp; s->ss = ss;
     s->aw = (w + 63) & ~63; s->ah = (h + 63) & ~63;
     const int bytes = bpp > 8 ? 2 : 1;
     for (int p = 0; p < 3; p++) {
-        int sh = p ? 1 : 0;
+        int sh = p ? ss : 0;
         s->stride[p] = s->aw >> sh;
         size_t n = (size_t)s->stride[p] * (s->ah >> sh) * bytes;
         if (cudaMalloc(&s->pl[p], n) != cudaSuccess) {
@@ -422,7 +425,7 @@ static void kstat_resolve(Vp9CudaCtx *c)
 static int check_header(const Vp9CudaFrameHeader *h, uint32_t *n_sb_out)
 {
     if (!h->w || !h->h || h->w > 64 * INTRA_MAX_SB_COLS || h->h > 65535 ||
-        (h->bpp != 8 && h->bpp != 10 && h->bpp != 12) || h->ss_h != 1 || h->ss_v != 1 ||
+        (h->bpp != 8 && h->bpp != 10 && h->bpp != 12) || h->ss_h > 1 || h->ss_h != h->ss_v ||   /* 4:2:0 and 4:4:4 */
         h->n_lanes < 1 || h->n_lanes > VP9CUDA_MAX_LANES)
         return -EINVAL;
     const uint32_t n_sb = ((h->w + 63) >> 6) * ((h->h + 63) >> 6);
@@ -538,14 +541,14 @@ static int upload_records(Vp9CudaCtx *c, DevRecords &d, const Vp9CudaFrameHeader
 }
 
 /* ring path: size one ring set (pinned slab + device records) for n_sb superblocks */
-static int ringset_reserve(Vp9CudaCtx *c, RingSet *r, uint32_t n_sb, int cols, int rows, int sb_rows, int ceb)
+static int ringset_reserve(Vp9CudaCtx *c, RingSet *r, uint32_t n_sb, int cols, int rows, int sb_rows, int ceb, int k = 1)
 {
-    if (r->mem.reserve((size_t)n_sb * ring_bytes_per_sb(ceb), c->n_allocs) ||
+    if (r->mem.reserve((size_t)n_sb * ring_bytes_per_sb(ceb, k), c->n_allocs) ||
         r->sb_index.reserve((size_t)n_sb * sizeof(Vp9CudaSbIndex), c->n_allocs) ||
         r->lf.reserve((size_t)n_sb * sizeof(Vp9CudaLoopFilterSb), c->n_allocs))
         return -ENOMEM;
-    return r->dev.reserve(c->n_allocs, n_sb, cols, rows, sb_rows, (uint64_t)n_sb * CAP_BLK, (uint64_t)n_sb * CAP_TX,
-                          (uint64_t)n_sb * CAP_ITX, (uint64_t)n_sb * CAP_COEF, ceb, true);
+    return r->dev.reserve(c->n_allocs, n_sb, cols, rows, sb_rows, (uint64_t)n_sb * CAP_BLK, (uint64_t)n_sb * k * CAP_TX,
+                          (uint64_t)n_sb * k * CAP_ITX, (uint64_t)n_sb * k * CAP_COEF, ceb, true);
 }
 
 /* ------------------------------------------------------------------------------------------
@@ -555,7 +558,7 @@ template <class P, bool HBD>
 static int launch_frame(Vp9CudaCtx *c, FrameDesc &f, DevRecords &d)
 {
     cudaStream_t s = c->stream, sp = c->s_prep;
-    const uint64_t P_bytes = (uint64_t)f.w * f.h * 3 / 2 * sizeof(P);
+    const uint64_t P_bytes = (uint64_t)f.w * f.h * (f.mono >= 0 ? 2 : 3) / 2 * sizeof(P);
     const bool fused = c->fuse_wave && f.n_itx && f.lf_level;
     f.lf_follow = fused ? c->follow_mask : 0;
     if (fused && c->inject_stall) {
@@ -604,7 +607,7 @@ static int launch_frame(Vp9CudaCtx *c, FrameDesc &f, DevRecords &d)
      * still in flight and all of its CTAs are resident -- on the inter stream right behind that
      * wavefront, each tile waiting for the superblock rows it can reach (k_inter, dep_done) ---- */
     if (f.n_blk) {
-        const bool overlap = c->overlap_inter && c->prev_dev && c->prev_dev != &d && c->prev_lf && !c->fresh_surface;
+        const bool overlap = c->overlap_inter && f.mono < 0 && c->prev_dev && c->prev_dev != &d && c->prev_lf && !c->fresh_surface;
         bool depends = false;
         for (int i = 0; i < 3; i++)
             depends |= c->prev_surf && f.ref[i].pl[0] == c->prev_surf->pl[0];
@@ -638,7 +641,7 @@ static int launch_frame(Vp9CudaCtx *c, FrameDesc &f, DevRecords &d)
             }
             f.tile_y0 = 0;
             kstat_end(c, KS_INTER, 2 * ((gy + band - 1) / band), 2 * P_bytes, si);
-        } else if (c->inter_sb) {
+        } else if (c->inter_sb || f.mono >= 0) {
             /* one CTA per superblock: windows staged in shared memory, residual added in the tile */
             k_inter_sb<P, HBD><<<dim3(f.sb_cols, f.sb_rows), ISB_THREADS, IsbSmem<P>::BYTES, si>>>(f, 1);
             kstat_end(c, KS_INTER, 1, 2 * P_bytes + d.n_coef * sizeof(typename ItxTypes<HBD>::E), si);
@@ -668,7 +671,7 @@ static int launch_frame(Vp9CudaCtx *c, FrameDesc &f, DevRecords &d)
     c->prev_sb_rows = f.sb_rows; c->prev_w = f.w; c->prev_h = f.h;
     if (fused) {
         kstat_begin(c);
-        k_wave<P><<<4 * f.sb_rows, INTRA_THREADS, WaveSmem<P>::BYTES, s>>>(f);
+        k_wave<P><<<(f.mono >= 0 ? 2 : 4) * f.sb_rows, INTRA_THREADS, WaveSmem<P>::BYTES, s>>>(f);
         kstat_end(c, KS_WAVE, 1, 3 * P_bytes);
     } else {
         if (f.n_itx) {
@@ -678,7 +681,7 @@ static int launch_frame(Vp9CudaCtx *c, FrameDesc &f, DevRecords &d)
         }
         if (f.lf_level) {
             kstat_begin(c);
-            k_lf<P><<<3 * f.sb_rows, LF_THREADS, 0, s>>>(f);
+            k_lf<P><<<(f.mono >= 0 ? 1 : 3) * f.sb_rows, LF_THREADS, 0, s>>>(f);
             kstat_end(c, KS_LF, 1, 2 * P_bytes);
         }
     }
@@ -693,7 +696,7 @@ static int copy_out(Vp9CudaCtx *c, Surface *s, uint8_t *const out_planes[3], con
     CK(cudaStreamWaitEvent(c->s_down, s->ready, 0));
     kstat_begin(c, c->s_down);
     for (int p = 0; p < 3; p++) {
-        int sh = p ? 1 : 0;
+        int sh = p ? s->ss : 0;
         int w = (s->w + sh) >> sh, h = (s->h + sh) >> sh;
         CK(cudaMemcpy2DAsync(out_planes[p], out_strides[p], s->pl[p], (size_t)s->stride[p] * bytes,
                              (size_t)w * bytes, h, cudaMemcpyDeviceToHost, c->s_down));
@@ -745,7 +748,7 @@ static int reconstruct(Vp9CudaCtx *c, DevRecords &d, uint8_t *const out_planes[3
     uint32_t n_sb_chk = 0;
     if (check_header(&h, &n_sb_chk) < 0)
         return -EINVAL;
-    Surface *cur = surface_get(c, h.w, h.h, h.bpp);
+    Surface *cur = surface_get(c, h.w, h.h, h.bpp, h.ss_h);
     if (!cur)
         return -ENOMEM;
     FrameDesc f;
@@ -753,7 +756,7 @@ static int reconstruct(Vp9CudaCtx *c, DevRecords &d, uint8_t *const out_planes[3
     f.cur = surf_desc(cur);
     for (int i = 0; i < 3; i++) {
         Surface *r = c->ref[h.ref_slot[i] & 7];
-        if (d.n_blk && (!r || r->bpp != h.bpp)) {
+        if (d.n_blk && (!r || r->bpp != h.bpp || r->ss != h.ss_h)) {
             surface_unref(cur);
             return -EINVAL;
         }
@@ -796,10 +799,29 @@ static int reconstruct(Vp9CudaCtx *c, DevRecords &d, uint8_t *const out_planes[3
     if (c->trace)
         fprintf(stderr, "vp9cuda: frame %dx%d bpp %d blk %u itx %u lf %d fuse %d\n", h.w, h.h, h.bpp, d.n_blk, d.n_itx,
                 h.lf_level, (int)(c->fuse_wave && d.n_itx && h.lf_level));
-    int r = h.bpp > 8 ? launch_frame<uint16_t, true>(c, f, d) : launch_frame<uint8_t, false>(c, f, d);
-    if (r == 0 && d.dev_free) {
-        CK(cudaEventRecord(d.dev_free, c->stream));
-        d.has_free = true;
+    int r = 0;
+    if (h.ss_h) {
+        f.mono = -1;
+        r = h.bpp > 8 ? launch_frame<uint16_t, true>(c, f, d) : launch_frame<uint8_t, false>(c, f, d);
+        if (r == 0 && d.dev_free) {
+            CK(cudaEventRecord(d.dev_free, c->stream));
+            d.has_free = true;
+        }
+    } else {
+        /* 4:4:4: every plane is a luma-like picture of its own (FrameDesc.mono): three passes over the same records, each
+         * with its plane in the place of plane 0.  The passes share the frame's scratch, so one starts its pre-passes when
+         * the kernels of the one before are done (dev_free). */
+        for (int p = 0; p < 3 && r == 0; p++) {
+            FrameDesc fp = f;
+            fp.mono = p;
+            fp.cur.pl[0] = f.cur.pl[p]; fp.cur.stride[0] = f.cur.stride[p];
+            for (int i = 0; i < 3; i++) { fp.ref[i].pl[0] = f.ref[i].pl[p]; fp.ref[i].stride[0] = f.ref[i].stride[p]; }
+            r = h.bpp > 8 ? launch_frame<uint16_t, true>(c, fp, d) : launch_frame<uint8_t, false>(c, fp, d);
+            if (r == 0 && d.dev_free) {
+                CK(cudaEventRecord(d.dev_free, c->stream));
+                d.has_free = true;
+            }
+        }
     }
     c->prev_surf = r == 0 ? cur : nullptr;
     if (r < 0)
@@ -1087,9 +1109,9 @@ extern "C" int vp9cuda_begin_frame(Vp9CudaCtx *c, const Vp9CudaFrameHeader *hdr,
     /* the previous user's H2D must be over before the producer scribbles on the pinned slab */
     if (cudaEventSynchronize(r->consumed) != cudaSuccess)
         return fail(-EIO);
-    const int ceb = coef_entry_bytes(hdr->bpp);
+    const int ceb = coef_entry_bytes(hdr->bpp), k = cap_scale(hdr);
     const int cols = (hdr->w + 7) >> 3, rows = (hdr->h + 7) >> 3, sb_rows = (hdr->h + 63) >> 6;
-    if (ringset_reserve(c, r, n_sb, cols, rows, sb_rows, ceb) < 0)
+    if (ringset_reserve(c, r, n_sb, cols, rows, sb_rows, ceb, k) < 0)
         return fail(-ENOMEM);
     DevRecords &d = r->dev;
     if (d.has_free) {                       /* the kernels of this landing zone's previous frame */
@@ -1101,15 +1123,15 @@ extern "C" int vp9cuda_begin_frame(Vp9CudaCtx *c, const Vp9CudaFrameHeader *hdr,
     for (int l = 0; l < hdr->n_lanes; l++) {
         const uint32_t sbs = hdr->lane_sbs[l];
         Vp9CudaLaneRing &g = r->ring[l];
-        char *base = (char *)r->mem.p + (size_t)sb0 * ring_bytes_per_sb(ceb);
-        g.blk_cap = sbs * CAP_BLK; g.tx_cap = sbs * CAP_TX; g.itx_cap = sbs * CAP_ITX; g.coef_cap = sbs * CAP_COEF;
+        char *base = (char *)r->mem.p + (size_t)sb0 * ring_bytes_per_sb(ceb, k);
+        g.blk_cap = sbs * CAP_BLK; g.tx_cap = sbs * k * CAP_TX; g.itx_cap = sbs * k * CAP_ITX; g.coef_cap = sbs * k * CAP_COEF;
         g.blk = (Vp9CudaInterBlock *)base;              base += (size_t)g.blk_cap * sizeof(Vp9CudaInterBlock);
         g.tx = (Vp9CudaTx *)base;                       base += (size_t)g.tx_cap * sizeof(Vp9CudaTx);
         g.itx = (Vp9CudaIntraTx *)base;                 base += (size_t)g.itx_cap * sizeof(Vp9CudaIntraTx);
         g.coef = base;
-        g.coef_base = sb0 * CAP_COEF;
+        g.coef_base = sb0 * k * CAP_COEF;
         g.reserved = 0;
-        d.lane_blk_base[l] = sb0 * CAP_BLK; d.lane_tx_base[l] = sb0 * CAP_TX; d.lane_itx_base[l] = sb0 * CAP_ITX;
+        d.lane_blk_base[l] = sb0 * CAP_BLK; d.lane_tx_base[l] = sb0 * k * CAP_TX; d.lane_itx_base[l] = sb0 * k * CAP_ITX;
         memset(&r->counts[l], 0, sizeof(r->counts[l]));
         memset(&r->sent[l], 0, sizeof(r->sent[l]));
         sb0 += sbs;
@@ -1300,7 +1322,7 @@ extern "C" int vp9cuda_map_frame(Vp9CudaCtx *c, int slot, Vp9CudaMappedFrame *ou
         out->strides[p] = (ptrdiff_t)s->stride[p] * bytes;
     }
     out->w = s->w; out->h = s->h; out->bpp = s->bpp;
-    out->ss_h = out->ss_v = 1;
+    out->ss_h = out->ss_v = s->ss;
     return 0;
 }
 
@@ -1541,7 +1563,7 @@ extern "C" int vp9cuda_frame_checksum(Vp9CudaCtx *c, int slot, uint64_t *sum)
         return -ENOMEM;
     CK(cudaMemsetAsync(c->sum_buf.p, 0, 8, c->stream));
     for (int p = 0; p < 3; p++) {
-        int sh = p ? 1 : 0, w = (s->w + sh) >> sh, h = (s->h + sh) >> sh;
+        int sh = p ? s->ss : 0, w = (s->w + sh) >> sh, h = (s->h + sh) >> sh;
         if (s->bpp > 8)
             k_checksum<uint16_t><<<296, 256, 0, c->stream>>>((const uint16_t *)s->pl[p], s->stride[p], w, h,
                                                              (unsigned long long *)c->sum_buf.p, p * 0x01000000u);

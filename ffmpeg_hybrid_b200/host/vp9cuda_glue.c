@@ -227,6 +227,8 @@ static int dump_begin_frame(Vp9CudaCtx *c, const Vp9CudaFrameHeader *h, Vp9CudaF
     DumpSet *q = NULL;
     unsigned n_sb = ((h->w + 63) >> 6) * ((h->h + 63) >> 6);
     uint32_t sb0 = 0;
+    /* per-superblock capacities as in the library (csrc/vp9cuda.cu: cap_scale): 4:4:4 carries twice the samples */
+    const unsigned k = (h->ss_h && h->ss_v) ? 1 : 2;
 
     pthread_mutex_lock(&d->mu);
     while (!q) {
@@ -255,22 +257,22 @@ static int dump_begin_frame(Vp9CudaCtx *c, const Vp9CudaFrameHeader *h, Vp9CudaF
     for (int l = 0; l < h->n_lanes; l++) {
         unsigned sbs = h->lane_sbs[l];
         Vp9CudaLaneRing *r = &q->ring[l];
-        if (sbs > q->lane_sbs[l]) {
+        if (sbs * k > q->lane_sbs[l]) {
             av_freep(&r->blk);
             av_freep(&r->tx);
             av_freep(&r->itx);
             av_freep(&r->coef);
             r->blk = av_malloc_array(sbs * CAP_BLK, sizeof(*r->blk));
-            r->tx = av_malloc_array(sbs * CAP_TX, sizeof(*r->tx));
-            r->itx = av_malloc_array(sbs * CAP_ITX, sizeof(*r->itx));
-            r->coef = av_malloc_array(sbs * CAP_COEF, sizeof(Vp9CudaCoef32));
-            q->lane_sbs[l] = sbs;
+            r->tx = av_malloc_array(sbs * k * CAP_TX, sizeof(*r->tx));
+            r->itx = av_malloc_array(sbs * k * CAP_ITX, sizeof(*r->itx));
+            r->coef = av_malloc_array(sbs * k * CAP_COEF, sizeof(Vp9CudaCoef32));
+            q->lane_sbs[l] = sbs * k;
         }
         r->blk_cap = sbs * CAP_BLK;
-        r->tx_cap = sbs * CAP_TX;
-        r->itx_cap = sbs * CAP_ITX;
-        r->coef_cap = sbs * CAP_COEF;
-        r->coef_base = sb0 * CAP_COEF;
+        r->tx_cap = sbs * k * CAP_TX;
+        r->itx_cap = sbs * k * CAP_ITX;
+        r->coef_cap = sbs * k * CAP_COEF;
+        r->coef_base = sb0 * k * CAP_COEF;
         sb0 += sbs;
         memset(&q->cnt[l], 0, sizeof(q->cnt[l]));
     }
@@ -619,8 +621,8 @@ int ff_vp9cuda_prepare_frame(AVCodecContext *avctx)
         g->sh->api.abort_frame(g->sh->ctx, g->fring.frame_id);
         g->in_frame = 0;
     }
-    if (s->ss_h != 1 || s->ss_v != 1) {
-        av_log(avctx, AV_LOG_ERROR, "vp9cuda: only 4:2:0 is implemented\n");
+    if (s->ss_h != s->ss_v) {
+        av_log(avctx, AV_LOG_ERROR, "vp9cuda: 4:2:2 and 4:4:0 are not implemented (4:2:0 and 4:4:4 are)\n");
         return AVERROR_PATCHWELCOME;
     }
     if (!g->sh && (ret = shared_create(avctx, g)) < 0)
@@ -692,7 +694,7 @@ int ff_vp9cuda_begin_frame(AVCodecContext *avctx)
         memset(&g->cnt[i], 0, sizeof(g->cnt[i]));
     }
     for (int p = 0; p < 3; p++) {
-        int w = (s->cols * 2) >> !!p, hh = (s->rows * 2) >> !!p;
+        int w = (s->cols * 2) >> (p ? s->ss_h : 0), hh = (s->rows * 2) >> (p ? s->ss_v : 0);
         size_t n = (size_t)w * hh;
         if (n > g->lvl_cap[p]) {
             av_freep(&g->lvl[p]);
@@ -824,8 +826,8 @@ void ff_vp9cuda_emit_block(VP9TileData *td)
         const int have_left_blk = col > td->tile_col_start;
         unsigned first = c->itx;
         unsigned n_tx = ((end_x + step1d - 1) >> b->tx) * ((end_y + step1d - 1) >> b->tx) +
-                        2 * (((end_x >> 1) + uvstep1d - 1) >> b->uvtx) *
-                            (((end_y >> 1) + uvstep1d - 1) >> b->uvtx);
+                        2 * (((end_x >> s->ss_h) + uvstep1d - 1) >> b->uvtx) *
+                            (((end_y >> s->ss_v) + uvstep1d - 1) >> b->uvtx);
         Vp9CudaIntraTx *o;
         if (c->itx + n_tx > r->itx_cap) {
             atomic_store(&g->overflow, 1);
@@ -854,15 +856,15 @@ void ff_vp9cuda_emit_block(VP9TileData *td)
                                                eob, bytesperpixel, &o->ncoef) : 0;
             }
         }
-        w4 >>= 1;
-        end_x >>= 1;
-        end_y >>= 1;
+        w4 >>= s->ss_h;
+        end_x >>= s->ss_h;
+        end_y >>= s->ss_v;
         for (p = 0; p < 2; p++) {
             for (n = 0, y = 0; y < end_y; y += uvstep1d) {
                 for (x = 0; x < end_x; x += uvstep1d, n += uvstep, o++) {
                     int eob = b->skip ? 0 : b->uvtx > TX_8X8 ? AV_RN16A(&td->uveob[p][n]) : td->uveob[p][n];
-                    o->x4 = col + x;
-                    o->y4 = row + y;
+                    o->x4 = ((col * 2) >> s->ss_h) + x;
+                    o->y4 = ((row * 2) >> s->ss_v) + y;
                     o->eob = eob;
                     o->plane = 1 + p;
                     o->tx = b->uvtx;
@@ -942,8 +944,8 @@ void ff_vp9cuda_emit_block(VP9TileData *td)
                                              eob, bytesperpixel, &t->ncoef);
                 }
             }
-            end_x >>= 1;
-            end_y >>= 1;
+            end_x >>= s->ss_h;
+            end_y >>= s->ss_v;
             for (p = 0; p < 2; p++) {
                 for (n = 0, y = 0; y < end_y; y += uvstep1d) {
                     for (x = 0; x < end_x; x += uvstep1d, n += uvstep) {
@@ -955,8 +957,8 @@ void ff_vp9cuda_emit_block(VP9TileData *td)
                             return;
                         }
                         t = &r->tx[c->tx++];
-                        t->x4 = col + x;
-                        t->y4 = row + y;
+                        t->x4 = ((col * 2) >> s->ss_h) + x;
+                        t->y4 = ((row * 2) >> s->ss_v) + y;
                         t->eob = eob;
                         t->plane = 1 + p;
                         t->tx = b->uvtx;

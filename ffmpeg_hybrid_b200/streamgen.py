@@ -173,7 +173,9 @@ class FrameSpec:
 class StreamSpec:
     width: int
     height: int
-    profile: int = 0          # 0: 8-bit 4:2:0, 2: 10/12-bit 4:2:0
+    profile: int = 0          # 0: 8-bit 4:2:0, 2: 10/12-bit 4:2:0, 1 / 3: the same depths with other chroma formats
+    ss_h: int = 1             # chroma subsampling (profiles 1 / 3: anything but 1, 1)
+    ss_v: int = 1
     bitdepth: int = 8
     seed: int = 1
     frames: List[FrameSpec] = field(default_factory=list)
@@ -204,7 +206,13 @@ def _color_config(bw: BitWriter, st: StreamSpec) -> None:
         bw.u(1, 0 if st.bitdepth == 10 else 1)
     bw.u(3, 2)   # BT.709
     bw.u(1, 0)   # studio range
-    assert st.profile in (0, 2), "4:2:0 profiles only"
+    if st.profile & 1:                    # profiles 1 and 3: 4:4:4, 4:2:2 or 4:4:0 (vp9.c:497-510)
+        assert (st.ss_h, st.ss_v) != (1, 1), "4:2:0 is profile 0 / 2"
+        bw.u(1, st.ss_h)
+        bw.u(1, st.ss_v)
+        bw.u(1, 0)                        # reserved
+    else:
+        assert (st.ss_h, st.ss_v) == (1, 1)
 
 
 _INV_MAP = [7 + 13 * k for k in range(20)]
@@ -383,6 +391,8 @@ def encode_frame(st: StreamSpec, fs: FrameSpec, cur_w: int, cur_h: int,
     bw.u(2, 2)
     bw.u(1, st.profile & 1)
     bw.u(1, st.profile >> 1)
+    if st.profile == 3:
+        bw.u(1, 0)                        # reserved_zero (vp9.c:535)
     if fs.show_existing >= 0:
         bw.u(1, 1)                        # show_existing_frame
         bw.u(3, fs.show_existing)

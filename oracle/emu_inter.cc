@@ -59,14 +59,23 @@ static long run_wave(FrameDesc &f, const Vp9CudaFrameHeader &h, const std::vecto
     if (f.lf_level)
         emu::launch(dim3(n_sb), LF_SCHED_THREADS, 0, [&] { k_lf_sched(f); });
     if (fused) {
-        emu::launch(dim3(4 * f.sb_rows), INTRA_THREADS, WaveSmem<P>::BYTES, [&] { k_wave<P>(f); });
+        emu::launch(dim3((f.mono >= 0 ? 2 : 4) * f.sb_rows), INTRA_THREADS, WaveSmem<P>::BYTES, [&] { k_wave<P>(f); });
     } else {
         if (f.n_itx)
             emu::launch(dim3(f.sb_rows), INTRA_THREADS, IntraSmem<P>::BYTES, [&] { k_intra<P>(f); });
         if (f.lf_level)
-            emu::launch(dim3(3 * f.sb_rows), LF_THREADS, 0, [&] { k_lf<P>(f); });
+            emu::launch(dim3((f.mono >= 0 ? 1 : 3) * f.sb_rows), LF_THREADS, 0, [&] { k_lf<P>(f); });
     }
-    /* the whole picture against the restatement's (all four phases) */
+    (void)cur; (void)m;
+    return 0;
+}
+
+/* the whole picture against the restatement's (all four phases) */
+template <class P>
+static long compare_full(const FrameDesc &f, const Vp9CudaFrameHeader &h, const std::vector<Lane> &lanes,
+                         const std::vector<Vp9CudaSbIndex> &sbi, const std::vector<Vp9CudaLoopFilterSb> &lf,
+                         std::vector<P> *cur, Model &m)
+{
     Model mf = m;
     Vp9CudaFrameHeader h2 = h;
     if (getenv("EMU_NOLF")) h2.lf_level = 0;
@@ -92,7 +101,7 @@ static long run_frame(Model &m, const Vp9CudaFrameHeader &h, const std::vector<L
     /* expected: phases 1 and 2 of the restatement on a fresh picture */
     Model mx = m;
     mx.cur = std::make_shared<Surf>();
-    mx.cur->alloc(h.w, h.h, h.bpp);
+    mx.cur->alloc(h.w, h.h, h.bpp, h.ss_h);
     std::vector<int32_t> dense;
     for (const Lane &l : lanes)
         for (const auto &b : l.blk)
@@ -151,13 +160,25 @@ static long run_frame(Model &m, const Vp9CudaFrameHeader &h, const std::vector<L
     f.cellmap = cellmap.data();
     if (blk.empty() && !g_full)
         return 0;
-    if (!blk.empty())
-        emu::launch(dim3(sb_cols, sb_rows), ISB_THREADS, IsbSmem<P>::BYTES, [&] { k_inter_sb<P, HBD>(f, 1); });
     long bad = 0;
+    /* 4:2:0: one pass over all planes.  4:4:4: three passes, each with one plane in the place of plane 0
+     * (FrameDesc.mono), exactly what csrc/vp9cuda.cu: reconstruct() launches */
+    for (int pass = 0; pass < (h.ss_h ? 1 : 3); pass++) {
+        FrameDesc fp = f;
+        fp.mono = h.ss_h ? -1 : pass;
+        if (!h.ss_h) {
+            fp.cur.pl[0] = f.cur.pl[pass]; fp.cur.stride[0] = f.cur.stride[pass];
+            for (int i = 0; i < 3; i++) { fp.ref[i].pl[0] = f.ref[i].pl[pass]; fp.ref[i].stride[0] = f.ref[i].stride[pass]; }
+        }
+        if (!blk.empty())
+            emu::launch(dim3(sb_cols, sb_rows), ISB_THREADS, IsbSmem<P>::BYTES, [&] { k_inter_sb<P, HBD>(fp, 1); });
+        if (g_full)
+            run_wave<P, HBD>(fp, h, lanes, sbi, lf, cur, m);
+    }
     if (g_full)
-        bad += run_wave<P, HBD>(f, h, lanes, sbi, lf, cur, m);
+        bad += compare_full<P>(f, h, lanes, sbi, lf, cur, m);
     for (int pl = 0; pl < 3 && !g_full; pl++) {
-        const int ch = pl > 0, cs = 8 >> ch;
+        const int ch = pl > 0 && h.ss_h, cs = 8 >> ch;
         for (int y = 0; y < (rows * 8) >> ch; y++)
             for (int x = 0; x < (cols * 8) >> ch; x++) {
                 if (cellmap[(size_t)(y / cs) * cols + x / cs] < 0)

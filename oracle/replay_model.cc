@@ -38,12 +38,12 @@ struct Surf {
     int w = 0, h = 0, bpp = 8;
     int pw[3], ph[3], stride[3];          /* visible plane size, stride in pixels */
     std::vector<uint16_t> p[3];
-    void alloc(int w_, int h_, int bpp_)
+    void alloc(int w_, int h_, int bpp_, int ss = 1)     /* ss: chroma subsampling in both directions (4:2:0) or none (4:4:4) */
     {
         w = w_; h = h_; bpp = bpp_;
         int aw = (w + 63) & ~63, ah = (h + 63) & ~63;
         for (int i = 0; i < 3; i++) {
-            int s = i ? 1 : 0;
+            int s = i ? ss : 0;
             pw[i] = (w + s) >> s; ph[i] = (h + s) >> s;
             stride[i] = aw >> s;
             p[i].assign((size_t)stride[i] * (ah >> s), 0);
@@ -216,7 +216,9 @@ static void inter_block(Model &m, const Vp9CudaFrameHeader &h, const Vp9CudaInte
     const int cols = (h.w + 7) >> 3, rows = (h.h + 7) >> 3;
     const int sub8 = b.bs > 9;
     for (int pl = 0; pl < 3; pl++) {
-        const int ch = pl > 0;
+        /* 4:4:4 chroma is predicted exactly like luma: full-size planes, luma vector units, every 4x4 of a sub-8x8
+         * block with its own vector (vp9_mc_template.c:78-121 with ss_h == ss_v == 0) */
+        const int ch = pl > 0 && h.ss_h;
         const int vis_w = (cols * 8) >> ch, vis_h = (rows * 8) >> ch;
         const int obx = (b.col * 8) >> ch, oby = (b.row * 8) >> ch;
         int ncall = (sub8 && !ch) ? 4 : 1;
@@ -276,8 +278,9 @@ static void decode_frame(Model &m, const Vp9CudaFrameHeader &h, const std::vecto
     const int cols = (h.w + 7) >> 3, rows = (h.h + 7) >> 3;
     const int sb_cols = (h.w + 63) >> 6, sb_rows = (h.h + 63) >> 6;
     m.cur = std::make_shared<Surf>();
-    m.cur->alloc(h.w, h.h, h.bpp);
+    m.cur->alloc(h.w, h.h, h.bpp, h.ss_h);
     Surf &c = *m.cur;
+    if (h.ss_h != h.ss_v) { fprintf(stderr, "4:2:2 / 4:4:0 are not restated\n"); exit(3); }
     /* phase 1: inter prediction; phase 2: inter residual */
     for (const Lane &l : lanes)
         for (const auto &b : l.blk)
@@ -294,7 +297,7 @@ static void decode_frame(Model &m, const Vp9CudaFrameHeader &h, const std::vecto
             const Lane &l = lanes[sbi[s].lane];
             for (unsigned k = 0; k < sbi[s].tx_count; k++) {
                 const Vp9CudaTx &r = l.tx[sbi[s].tx_start + k];
-                const int ch = r.plane > 0, sx = (r.x4 * 4) >> (ch ? 5 : 6), sy = (r.y4 * 4) >> (ch ? 5 : 6);
+                const int ch = r.plane > 0 && h.ss_h, sx = (r.x4 * 4) >> (ch ? 5 : 6), sy = (r.y4 * 4) >> (ch ? 5 : 6);
                 if (sy * sb_cols + sx != s) { fprintf(stderr, "superblock %d lists a residual block of superblock %d\n", s, sy * sb_cols + sx); exit(4); }
             }
             seen[sbi[s].lane] += sbi[s].tx_count;
@@ -308,14 +311,14 @@ static void decode_frame(Model &m, const Vp9CudaFrameHeader &h, const std::vecto
     std::vector<int> lvmap[3];
     int lvw[3], lvh[3];
     for (int p = 0; p < 3; p++) {
-        lvw[p] = (cols * 2) >> !!p; lvh[p] = (rows * 2) >> !!p;
+        lvw[p] = (cols * 2) >> (p && h.ss_h); lvh[p] = (rows * 2) >> (p && h.ss_v);
         lvmap[p].assign((size_t)lvw[p] * lvh[p], -1);
     }
     for (int s = 0; s < sb_rows * sb_cols; s++) {
         const Lane &l = lanes[sbi[s].lane];
         for (unsigned k = 0; k < sbi[s].itx_count; k++) {
             const Vp9CudaIntraTx &r = l.itx[sbi[s].itx_start + k];
-            int pl = r.plane, ch = pl > 0;
+            int pl = r.plane, ch = pl > 0 && h.ss_h;
             int bx = r.x4 * 4, by = r.y4 * 4;
             int avail_w = ((cols * 8) >> ch) - bx, avail_h = ((rows * 8) >> ch) - by;
             {
@@ -351,7 +354,7 @@ static void decode_frame(Model &m, const Vp9CudaFrameHeader &h, const std::vecto
             for (int sc = 0; sc < sb_cols; sc++) {
                 const LfSb &f = *(const LfSb *)&lf[sr * sb_cols + sc];
                 for (int pl = 0; pl < 3; pl++) {
-                    int ch = pl > 0;
+                    int ch = pl > 0 && h.ss_h;       /* 4:4:4: the chroma planes take the luma masks (vp9lpf.c:214) */
                     lf_decode_cols(f, ch, sc == 0, ops);
                     lf_apply(c.p[pl].data(), c.stride[pl], (sc * 64) >> ch, (sr * 64) >> ch, ch, ops, false,
                              h.lim_lut, h.mblim_lut, h.bpp);

@@ -47,7 +47,8 @@ def test_tile_threaded_records(workdir):
     assert p.returncode == 0, p.stderr[-1500:]
 
 
-@pytest.mark.parametrize("name,frames", [("tiny", 4), ("hbd12", 3), ("lossless", 2), ("intraonly", 3), ("c4_small", 1)])
+@pytest.mark.parametrize("name,frames", [("tiny", 4), ("hbd12", 3), ("lossless", 2), ("intraonly", 3), ("c4_small", 1),
+                                         ("p1_444", 3), ("p3_444_12", 5)])
 def test_whole_gpu_pipeline_emulated(name, frames, workdir):
     """-full: every kernel of a frame (k_inter_sb, k_intra_prep, k_intra_res, k_lf_sched and the intra /
     loop-filter wavefronts of k_wave, CTAs in block-index order) on the host; the finished picture must equal

@@ -19,6 +19,8 @@ import record_coverage  # noqa: E402
 def cov(workdir):
     paths = []
     for name, spec in configs.small_variants().items():
+        if (spec.ss_h, spec.ss_v) != (1, 1):
+            continue                          # the slot inventory is the 4:2:0 one (chroma block sizes and vector units)
         ivf = parity.write_stream(spec, workdir / f"cov_{name}.ivf")
         parity.dump_records(ivf, workdir / f"cov_{name}.v9r")
         paths.append(workdir / f"cov_{name}.v9r")
