@@ -132,7 +132,7 @@ __device__ __forceinline__ int rounded_div(int a, int b)
 #define VP9_TIGHT_NS 0      /* sleep (ns) inside the compute warps' waits for their loader warps */
 #endif
 #ifdef VP9_EMU
-#define VP9_SPIN(cond, ns, tag, a, b) do { while (cond) std::this_thread::yield(); } while (0)
+#define VP9_SPIN(cond, ns, tag, a, b) do { for (int i_ = 0; (cond); i_++) { if (i_ < 8) std::this_thread::yield(); else usleep(20); } } while (0)
 #elif defined(VP9CUDA_WATCHDOG)
 __device__ int *g_wd_buf;            /* host-mapped: [0] = count, then {line, id, at, block} per report */
 #define VP9_SPIN(cond, ns, tag, a, b) do { long long t0_ = clock64(); bool rep_ = false; while (cond) { if ((ns) > 0) __nanosleep(ns); \

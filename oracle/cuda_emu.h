@@ -3,7 +3,7 @@
  * kernel of ffmpeg_hybrid_b200/csrc/*.cuh on the host, unchanged, inside the CPU test-suite:
  * every CUDA thread of a CTA is an OS thread, __syncthreads() / __syncwarp(mask) are real barriers,
  * __shared__ variables are function-local statics (one CTA runs at a time), cp.async is a memcpy.
- * CTAs run one after the other, so kernels whose CTAs wait for each other cannot be run this way.
+ * CTAs run one after the other in block-index order, so kernels whose CTAs wait for LATER CTAs cannot be run this way.
  *
  * Used by oracle/emu_inter.cc to pin the shared-memory inter-prediction kernel (k_inter_sb.cuh)
  * against the oracle restatement before it ever runs on a GPU.  Only tests/ execute it.
@@ -12,6 +12,10 @@
 #define VP9_CUDA_EMU_H
 
 #include <atomic>
+#include <climits>
+#include <linux/futex.h>
+#include <sys/syscall.h>
+#include <unistd.h>
 #include <condition_variable>
 #include <cstdint>
 #include <cstring>
@@ -41,19 +45,24 @@ static inline uint2 make_uint2(unsigned a, unsigned b) { return uint2{ a, b }; }
 
 namespace emu {
 
-/* reusable barrier for a fixed number of threads */
+/* reusable barrier for a fixed number of threads: a counter and a generation word the waiters sleep on
+ * (futex) -- one system call per waiter and phase; a mutex + condition variable cost several, contended */
 struct Barrier {
-    std::mutex mu;
-    std::condition_variable cv;
-    int need, count = 0;
-    unsigned gen = 0;
+    std::atomic<int> count{ 0 };
+    std::atomic<unsigned> gen{ 0 };
+    int need;
     explicit Barrier(int n) : need(n) {}
     void wait()
     {
-        std::unique_lock<std::mutex> lk(mu);
-        const unsigned g = gen;
-        if (++count == need) { count = 0; gen++; cv.notify_all(); }
-        else cv.wait(lk, [&] { return gen != g; });
+        const unsigned g = gen.load(std::memory_order_acquire);
+        if (count.fetch_add(1, std::memory_order_acq_rel) + 1 == need) {
+            count.store(0, std::memory_order_relaxed);
+            gen.store(g + 1, std::memory_order_release);
+            syscall(SYS_futex, (unsigned *)&gen, FUTEX_WAKE_PRIVATE, INT_MAX, nullptr, nullptr, 0);
+        } else {
+            while (gen.load(std::memory_order_acquire) == g)
+                syscall(SYS_futex, (unsigned *)&gen, FUTEX_WAIT_PRIVATE, g, nullptr, nullptr, 0);
+        }
     }
 };
 
@@ -189,7 +198,7 @@ static inline void named_barrier(int id, int n)
     Barrier *b;
     {
         std::lock_guard<std::mutex> lk(g_cta->mu);
-        Barrier *&q = g_cta->warp_bar[(uint64_t)0xffff0000u << 32 | (unsigned)id];
+        Barrier *&q = g_cta->warp_bar[(uint64_t)0xffff0000u << 32 | (unsigned)n << 8 | (unsigned)id]   /* the Cta outlives one CTA: key by size too */;
         if (!q) q = new Barrier(n);
         b = q;
     }

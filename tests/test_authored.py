@@ -68,7 +68,7 @@ def test_model_and_emulated_kernel_on_authored_streams(name, streams, workdir):
     subprocess.run([str(parity.REF_BIN), "-raw", str(ref_yuv), str(streams[name])], check=True, capture_output=True)
     subprocess.run([str(parity.MODEL_BIN), str(dump), str(mod_yuv)], check=True, capture_output=True)
     assert ref_yuv.read_bytes() == mod_yuv.read_bytes()
-    p = subprocess.run([str(ROOT / "oracle" / "_ref" / "emu_inter"), str(dump), "4"], capture_output=True, text=True, timeout=900)
+    p = subprocess.run([str(ROOT / "oracle" / "_ref" / "emu_inter"), str(dump), "3"], capture_output=True, text=True, timeout=900)
     assert p.returncode == 0 and " 0 differing" in p.stderr, p.stderr[-800:]
 
 

@@ -40,7 +40,7 @@ def test_baseline_configs_bit_exact(name, full, workdir):
     ivf.unlink()
 
 
-@pytest.mark.parametrize("name,threads", [("c2_small", 4), ("manytiles", 16), ("segment", 4)])
+@pytest.mark.parametrize("name,threads", [("c2_small", 4), ("manytiles", 16), ("segment", 4), ("p1_444", 2)])
 def test_tile_threaded_host_is_bit_exact(name, threads, workdir):
     """slice threading: one producer lane per tile column (vp9.c:1442-1520)"""
     ivf = parity.write_stream(configs.small_variants()[name], workdir / "mt.ivf")

@@ -176,7 +176,7 @@ def test_abort_frame_gives_the_ring_set_back(workdir):
 
 
 FRAME_MT = ["c1_small", "c2_small", "c3_small", "c3p_small", "c4_small", "hbd12", "intraonly", "parallel", "superframe",
-            "segment", "scale_mix", "keyresize", "tiny", "manytiles"]
+            "segment", "scale_mix", "keyresize", "tiny", "manytiles", "p1_444", "p3_444_10", "p3_444_12"]
 
 
 @pytest.mark.parametrize("threads", [2, 8, 16])
