@@ -23,6 +23,7 @@ API = [
     "vp9cuda_stage_frame", "vp9cuda_run_staged", "vp9cuda_free_staged", "vp9cuda_frame_checksum",
     "vp9cuda_kernel_stats", "vp9cuda_set_option", "vp9cuda_elapsed_ms", "vp9cuda_phase_clocks", "vp9cuda_slot_itxfm_add",
     "vp9cuda_slot_intra_pred", "vp9cuda_slot_mc", "vp9cuda_slot_loop_filter", "vp9cuda_map_frame", "vp9cuda_unmap_frame",
+    "vp9cuda_checksum_noalloc",
 ]
 
 
@@ -95,6 +96,8 @@ def load() -> C.CDLL:
         lib.vp9cuda_abort_frame.argtypes = [C.c_void_p, C.c_uint32]
         lib.vp9cuda_kernel_stats.argtypes = [C.c_void_p, C.POINTER(C.c_char_p), C.POINTER(C.c_double),
                                              C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.c_int]
+        lib.vp9cuda_checksum_noalloc.argtypes = [C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_ssize_t), C.c_int, C.c_int,
+                                                 C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
         _lib = lib
     return _lib
 

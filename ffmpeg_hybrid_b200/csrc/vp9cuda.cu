@@ -1774,3 +1774,124 @@ extern "C" int vp9cuda_slot_loop_filter(int device, int bpp, int n, const uint8_
     CK(cudaGetLastError());
     return 0;
 }
+
+/* ------------------------------------------------------------------------------------------
+ * vp9cuda_checksum_noalloc: the frame checksum of vp9cuda_frame_checksum for callers that must not
+ * allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).  No counterpart in
+ * the reference.
+ *
+ * The kernel's scratch -- one partial sum per picture row and a ticket the CTAs take when they are
+ * done -- lives in a file-scope __device__ array of VP9CUDA_NOALLOC_MAX_ROWS rows (128 KiB + 256 B
+ * on every GPU that loads the library, until exit).  g_noalloc_scratch is a host-side stand-in in
+ * host code, not a device address: the address the kernel gets comes from cudaGetSymbolAddress, once
+ * per device, with that device current.  Every call shares the array: calls that overlap on the GPU
+ * (different streams, different host threads) race; calls on one stream do not.
+ * ---------------------------------------------------------------------------------------- */
+#define NOALLOC_TICKET VP9CUDA_NOALLOC_MAX_ROWS       /* index of the ticket word behind the row sums */
+static __device__ __align__(256) unsigned long long g_noalloc_scratch[VP9CUDA_NOALLOC_MAX_ROWS + 32];
+
+struct NoAllocPlanes {
+    const void *pl[3];
+    long long stride[3];               /* pixels */
+    int w[3], h[3];
+};
+
+__device__ __forceinline__ unsigned long long noalloc_block_sum(unsigned long long acc, unsigned long long *part)
+{
+    for (int o = 16; o; o >>= 1)
+        acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    __syncthreads();                                   /* part[] of the previous round has been read */
+    if ((threadIdx.x & 31) == 0)
+        part[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    unsigned long long s = 0;
+    for (int i = 0; i < (int)(blockDim.x >> 5); i++)
+        s += part[i];
+    return s;
+}
+
+/* same sum as k_checksum over the three planes (salt = plane << 24; the additions commute), taken row by row:
+ * a CTA leaves the sum of each of its rows in scratch[row]; the CTA that takes the last ticket adds the rows up */
+template <class P>
+__global__ void k_checksum_rows(NoAllocPlanes a, unsigned long long *scratch, unsigned long long *out)
+{
+    __shared__ unsigned long long part[32];
+    __shared__ int last;
+    const int total = a.h[0] + a.h[1] + a.h[2];
+    for (int r = blockIdx.x; r < total; r += gridDim.x) {
+        const int p = r < a.h[0] ? 0 : r < a.h[0] + a.h[1] ? 1 : 2;
+        const int y = r - (p ? a.h[0] : 0) - (p > 1 ? a.h[1] : 0);
+        const P *row = (const P *)a.pl[p] + (size_t)y * a.stride[p];
+        const int w = a.w[p];
+        const unsigned salt = (unsigned)p * 0x01000000u;
+        unsigned long long acc = 0;
+        for (int x = threadIdx.x; x < w; x += blockDim.x) {
+            const int i = y * w + x;
+            const unsigned long long v = row[x];
+            acc += (v + 1) * (0x9E3779B97F4A7C15ull ^ ((unsigned long long)(i + salt) * 0xD6E8FEB86659FD93ull));
+        }
+        const unsigned long long s = noalloc_block_sum(acc, part);
+        if (threadIdx.x == 0)
+            scratch[r] = s;
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0)
+        last = atomicAdd((unsigned *)&scratch[NOALLOC_TICKET], 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (!last)
+        return;
+    __threadfence();
+    unsigned long long acc = 0;
+    for (int r = threadIdx.x; r < total; r += blockDim.x)
+        acc += __ldcg(&scratch[r]);
+    const unsigned long long s = noalloc_block_sum(acc, part);
+    if (threadIdx.x == 0) {
+        *out = s;
+        scratch[NOALLOC_TICKET] = 0;                   /* the next call starts from zero even without its own clear */
+    }
+}
+
+#define NOALLOC_MAX_DEVICES 64
+static std::mutex g_noalloc_mu;
+static unsigned long long *g_noalloc_ptr[NOALLOC_MAX_DEVICES];      /* device address of g_noalloc_scratch, per device */
+
+extern "C" int vp9cuda_checksum_noalloc(int device, const void *const planes[3], const ptrdiff_t strides[3],
+                                        int w, int h, int bpp, int ss_h, int ss_v, uint64_t *sum_dev, void *stream)
+{
+    if (!planes || !strides || !sum_dev || !planes[0] || !planes[1] || !planes[2] || w < 1 || h < 1 || w > 65536 ||
+        (bpp != 8 && bpp != 10 && bpp != 12) || (ss_h & ~1) || (ss_v & ~1) || device < 0 || device >= NOALLOC_MAX_DEVICES)
+        return -EINVAL;
+    const int pb = bpp > 8 ? 2 : 1;
+    NoAllocPlanes a;
+    long long rows = 0;
+    for (int p = 0; p < 3; p++) {
+        a.pl[p] = planes[p];
+        if (strides[p] % pb)
+            return -EINVAL;
+        a.stride[p] = strides[p] / pb;
+        a.w[p] = p ? (w + ss_h) >> ss_h : w;
+        a.h[p] = p ? (h + ss_v) >> ss_v : h;
+        rows += a.h[p];
+    }
+    if (rows > VP9CUDA_NOALLOC_MAX_ROWS) {
+        fprintf(stderr, "vp9cuda_checksum_noalloc: a %dx%d picture has %lld rows in its three planes, the static scratch "
+                        "holds VP9CUDA_NOALLOC_MAX_ROWS = %d\n", w, h, rows, VP9CUDA_NOALLOC_MAX_ROWS);
+        return -E2BIG;
+    }
+    CK(cudaSetDevice(device));
+    unsigned long long *scratch;
+    {
+        std::lock_guard<std::mutex> lk(g_noalloc_mu);
+        if (!g_noalloc_ptr[device])                    /* once per device, with that device current */
+            CK(cudaGetSymbolAddress((void **)&g_noalloc_ptr[device], g_noalloc_scratch));
+        scratch = g_noalloc_ptr[device];
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    CK(cudaMemsetAsync(scratch + NOALLOC_TICKET, 0, 256, st));      /* the ticket must start at zero */
+    const int grid = (int)(rows < 592 ? rows : 592);
+    if (bpp > 8) k_checksum_rows<uint16_t><<<grid, 256, 0, st>>>(a, scratch, (unsigned long long *)sum_dev);
+    else         k_checksum_rows<uint8_t><<<grid, 256, 0, st>>>(a, scratch, (unsigned long long *)sum_dev);
+    CK(cudaGetLastError());
+    return 0;
+}

@@ -303,6 +303,28 @@ int  vp9cuda_slot_loop_filter(int device, int bpp, int n, const uint8_t *wd /* 4
                               const int32_t *E, const int32_t *I, const int32_t *H,
                               void *pix /* edge at (32,32) of each tile */);
 
+/* ---- allocation-free entry point --------------------------------------------------------------
+ * No counterpart in the reference: added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  Computes the checksum vp9cuda_frame_checksum defines (same value, bit for bit) of a picture
+ * the CALLER holds in device memory -- e.g. the planes vp9cuda_map_frame returned -- and leaves it in
+ * *sum_dev (DEVICE memory, 8 bytes, 8-aligned), in stream order on `stream` (a cudaStream_t, NULL =
+ * the default stream); the call does not wait for the GPU.  It makes no cudaMalloc / cudaFree and
+ * calls no allocating library routine: the kernel's scratch (one partial sum per picture row + a
+ * ticket word) is a static __device__ array of VP9CUDA_NOALLOC_MAX_ROWS rows, about 128 KiB that
+ * every GPU which loads the library holds until exit.  Its device address is looked up once per
+ * device on the first call for that device (make that call outside a capture).
+ *   planes / strides : device pointers and strides in BYTES of the three planes; w, h luma size;
+ *                      bpp 8 (uint8_t samples) or 10 / 12 (uint16_t); ss_h, ss_v chroma shifts (0 / 1).
+ * Returns 0, -EINVAL (arguments), -E2BIG when h + 2 * ((h + ss_v) >> ss_v) exceeds
+ * VP9CUDA_NOALLOC_MAX_ROWS (also reported on stderr), -EIO (CUDA error).
+ * Every call on a device shares the one scratch array: calls that overlap on the GPU (different
+ * streams or host threads without ordering between them) race; calls ordered on one stream do not.
+ * The call leaves `device` current on the calling thread, like the other entry points. */
+#define VP9CUDA_NOALLOC_MAX_ROWS 16384      /* 8192x4320 4:2:0 has 8640, 4:4:4 12960 */
+int  vp9cuda_checksum_noalloc(int device, const void *const planes[3], const ptrdiff_t strides[3],
+                              int w, int h, int bpp, int ss_h, int ss_v, uint64_t *sum_dev, void *stream);
+
 #if defined(__GNUC__)
 #pragma GCC visibility pop
 #endif
