@@ -121,7 +121,7 @@ typedef struct Vp9CudaLoopFilterSb {
 typedef struct Vp9CudaFrameHeader {
     uint32_t w, h;               /* coded frame size in pixels */
     uint8_t  bpp;                /* 8, 10 or 12 */
-    uint8_t  ss_h, ss_v;         /* only 4:2:0 (1,1) is implemented in this round */
+    uint8_t  ss_h, ss_v;         /* 4:2:0 (1,1) or 4:4:4 (0,0); ss_h != ss_v is refused */
     uint8_t  keyframe, intraonly, lossless, invisible;
     uint8_t  lf_level;           /* s->s.h.filter.level; 0 = loop filter off */
     uint8_t  refreshrefmask;     /* vp9.c:1687-1692 */
@@ -189,7 +189,7 @@ int  vp9cuda_flush(Vp9CudaCtx *ctx);
  * DECODE ORDER (one thread at a time; under frame threading: before ff_thread_finish_setup).
  * Blocks while all frames_in_flight ring sets are in use.  Fills *ring.
  * -EINVAL for a frame the back end cannot take (size 0, more than 16384 pixels wide, a bit
- * depth other than 8/10/12, chroma other than 4:2:0). */
+ * depth other than 8/10/12, chroma other than 4:2:0 / 4:4:4). */
 int  vp9cuda_begin_frame(Vp9CudaCtx *ctx, const Vp9CudaFrameHeader *hdr, Vp9CudaFrameRing *ring);
 /* Pinned ring of one lane of frame frame_id. */
 int  vp9cuda_tile_ring(Vp9CudaCtx *ctx, uint32_t frame_id, int lane, Vp9CudaLaneRing *ring);
