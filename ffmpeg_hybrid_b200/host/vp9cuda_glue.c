@@ -773,23 +773,49 @@ static av_always_inline int lvl_get(const VP9CudaGlue *g, int p, int x, int y)
     return (v >> 16) == g->lvl_tag ? (int)(v & 0xffff) : -1;
 }
 
+/* Edges the predictor of `mode` reads once check_intra_mode() has replaced the mode for the edges
+ * that do not exist (mode_conv, vp9recon.c:49-70): bit 0 left column, bit 1 top row, bit 2 top-left
+ * sample, bit 3 the top-right extension.  D135 / D117 / D153 keep their mode and read synthetic
+ * values (127 / 129) in the place of a missing edge. */
+static av_always_inline int intra_needs(int mode, int have_left, int have_top)
+{
+    switch (mode) {
+    case VERT_PRED:
+        return have_top ? 2 : 0;
+    case DIAG_DOWN_LEFT_PRED:
+    case VERT_LEFT_PRED:
+        return have_top ? 2 | 8 : 0;
+    case HOR_PRED:
+    case HOR_UP_PRED:
+        return have_left ? 1 : 0;
+    case DC_PRED:
+        return (have_left ? 1 : 0) | (have_top ? 2 : 0);
+    case TM_VP8_PRED:
+        return have_left ? (have_top ? 1 | 2 | 4 : 1) : (have_top ? 2 : 0);
+    default:
+        return (have_left ? 1 : 0) | (have_top ? 2 : 0) | (have_left && have_top ? 4 : 0);
+    }
+}
+
 /* Dependency depth of one intra transform block (n x n cells at cell x,y of plane p) and
- * registration of its cells.  The neighbour set is the superset of what check_intra_mode()
- * may read (vp9recon.c:37-221): left column incl. top-left when have_left, top row when
- * have_top, one more cell to the right for 4x4 blocks with have_right.  All of them precede
- * the block in coding order and lie in the same tile column, so tile threads never race. */
-static av_always_inline int intra_level(VP9CudaGlue *g, int p, int x, int y, int n, int have_left,
-                                        int have_top, int topright)
+ * registration of its cells.  The neighbour set is what the block's predictor reads
+ * (check_intra_mode, vp9recon.c:37-221, by mode: intra_needs): the left column, the top-left
+ * cell, the top row, and one more cell to the right for 4x4 blocks with have_right whose mode
+ * reads the top-right extension.  All of them precede the block in coding order and lie in the
+ * same tile column, so tile threads never race. */
+static av_always_inline int intra_level(VP9CudaGlue *g, int p, int x, int y, int n, int needs, int topright)
 {
     const int w = g->lvl_w[p], h = g->lvl_h[p];
     int lv = 0, i, j, xe, ye;
-    if (have_left) {
+    if (needs & 1) {
         ye = FFMIN(y + n, h);
-        for (j = have_top ? y - 1 : y; j < ye; j++)
+        for (j = y; j < ye; j++)
             lv = FFMAX(lv, lvl_get(g, p, x - 1, j) + 1);
     }
-    if (have_top) {
-        xe = FFMIN(x + (topright ? 2 : n), w);
+    if (needs & 4)
+        lv = FFMAX(lv, lvl_get(g, p, x - 1, y - 1) + 1);
+    if (needs & 2) {
+        xe = FFMIN(x + ((needs & 8) && topright ? 2 : n), w);
         for (i = x; i < xe; i++)
             lv = FFMAX(lv, lvl_get(g, p, i, y - 1) + 1);
     }
@@ -850,8 +876,9 @@ void ff_vp9cuda_emit_block(VP9TileData *td)
                            (x < w4 - 1 ? VP9CUDA_ITX_HAVE_RIGHT : 0);
                 o->pad = 0;
                 o->ncoef = 0;
-                o->level = intra_level(g, 0, o->x4, o->y4, step1d, o->flags & VP9CUDA_ITX_HAVE_LEFT,
-                                       o->y4 > 0, b->tx == TX_4X4 && (o->flags & VP9CUDA_ITX_HAVE_RIGHT));
+                o->level = intra_level(g, 0, o->x4, o->y4, step1d,
+                                       intra_needs(mode, o->flags & VP9CUDA_ITX_HAVE_LEFT, o->y4 > 0),
+                                       b->tx == TX_4X4 && (o->flags & VP9CUDA_ITX_HAVE_RIGHT));
                 o->coef_off = eob ? take_coefs(g, lane, td->block + 16 * n * bytesperpixel, yscans[txtp],
                                                eob, bytesperpixel, &o->ncoef) : 0;
             }
@@ -874,8 +901,9 @@ void ff_vp9cuda_emit_block(VP9TileData *td)
                                (x < w4 - 1 ? VP9CUDA_ITX_HAVE_RIGHT : 0);
                     o->pad = 0;
                     o->ncoef = 0;
-                    o->level = intra_level(g, 1 + p, o->x4, o->y4, uvstep1d, o->flags & VP9CUDA_ITX_HAVE_LEFT,
-                                           o->y4 > 0, b->uvtx == TX_4X4 && (o->flags & VP9CUDA_ITX_HAVE_RIGHT));
+                    o->level = intra_level(g, 1 + p, o->x4, o->y4, uvstep1d,
+                                           intra_needs(b->uvmode, o->flags & VP9CUDA_ITX_HAVE_LEFT, o->y4 > 0),
+                                           b->uvtx == TX_4X4 && (o->flags & VP9CUDA_ITX_HAVE_RIGHT));
                     o->coef_off = eob ? take_coefs(g, lane, td->uvblock[p] + 16 * n * bytesperpixel, uvscan,
                                                    eob, bytesperpixel, &o->ncoef) : 0;
                 }

@@ -72,9 +72,12 @@ typedef struct Vp9CudaIntraTx {
     uint16_t x4, y4;
     uint16_t eob;            /* 0 = prediction only */
     uint16_t level;          /* depth of this block's dependency chain in the frame: 0 when no
-                                neighbour it may read (left column incl. top-left, top row, and
-                                top-right for 4x4) is an intra block of this frame, else 1 + the
-                                largest level among those neighbours.  Blocks of equal level are
+                                neighbour its predictor reads is an intra block of this frame,
+                                else 1 + the largest level among those neighbours.  The
+                                neighbours are taken by mode, after check_intra_mode's
+                                conversion for missing edges (vp9recon.c:49-70): left column,
+                                top-left cell, top row, and the top-right cell for 4x4 blocks
+                                with HAVE_RIGHT whose mode reads it.  Blocks of equal level are
                                 independent; the GPU dispatches in level order. */
     uint8_t  plane;          /* 0 Y, 1 U, 2 V */
     uint8_t  tx;             /* enum TxfmMode 0..3 */

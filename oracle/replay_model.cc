@@ -307,7 +307,7 @@ static void decode_frame(Model &m, const Vp9CudaFrameHeader &h, const std::vecto
     }
     /* phase 3: intra blocks, superblocks in raster order, coding order inside.  Along the way
      * the records' dependency levels are re-derived and checked (exactly 1 + max over the intra
-     * neighbours the block may read), which is what the GPU's level-ordered dispatch relies on. */
+     * neighbours the block's predictor reads, by mode), which is what the GPU's level-ordered dispatch relies on. */
     std::vector<int> lvmap[3];
     int lvw[3], lvh[3];
     for (int p = 0; p < 3; p++) {
@@ -324,12 +324,15 @@ static void decode_frame(Model &m, const Vp9CudaFrameHeader &h, const std::vecto
             {
                 const int n = 1 << r.tx, x = r.x4, y = r.y4, w = lvw[pl], hh = lvh[pl];
                 const bool hl = r.flags & VP9CUDA_ITX_HAVE_LEFT, ht = y > 0;
+                const int needs = intra_mode_needs(intra_mode_conv(r.mode, hl, ht));      /* edges this block's predictor reads */
                 int lv = 0;
-                if (hl)
-                    for (int j = ht ? y - 1 : y; j < std::min(y + n, hh); j++)
+                if (hl && (needs & 1))
+                    for (int j = y; j < std::min(y + n, hh); j++)
                         lv = std::max(lv, lvmap[pl][(size_t)j * w + x - 1] + 1);
-                if (ht)
-                    for (int i = x; i < std::min(x + ((r.tx == 0 && (r.flags & VP9CUDA_ITX_HAVE_RIGHT)) ? 2 : n), w); i++)
+                if (hl && ht && (needs & 4))
+                    lv = std::max(lv, lvmap[pl][(size_t)(y - 1) * w + x - 1] + 1);
+                if (ht && (needs & 2))
+                    for (int i = x; i < std::min(x + ((r.tx == 0 && (needs & 8) && (r.flags & VP9CUDA_ITX_HAVE_RIGHT)) ? 2 : n), w); i++)
                         lv = std::max(lv, lvmap[pl][(size_t)(y - 1) * w + i] + 1);
                 if (lv != r.level) {
                     fprintf(stderr, "level mismatch plane %d cell %d,%d: record %d, derived %d\n", pl, x, y, r.level, lv);
