@@ -102,7 +102,7 @@ struct FrameDesc {
     LfSched *lfsched;              /* [sb][plane] loop-filter edge ops sorted by dependency step */
     int *progress;                 /* [3 planes][sb_rows] loop-filter wavefront counters, then [3][sb_rows] "row done" */
     int *mv_reach;                 /* max vertical motion vector component of this frame, 1/8 pel (k_cellmap) */
-    int tile_y0;                   /* k_inter: first 32-row tile row of this launch (the frame may be launched in bands) */
+    int tile_y0;                   /* first row of this launch when the frame is launched in bands: k_inter 32-row tile rows, k_inter_sb superblock rows */
     unsigned long long *phase_clk; /* optional: per-phase clock accumulation (profiling), or NULL */
     int *err;                      /* context error word (device memory): non-zero = a wavefront wait gave up */
     int *err_host;                 /* the same, host-mapped: what vp9cuda_wait reads */

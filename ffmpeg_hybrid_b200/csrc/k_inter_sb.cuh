@@ -398,7 +398,7 @@ __global__ void __launch_bounds__(ISB_THREADS, 3) k_inter_sb(const __grid_consta
     P *tile = (P *)(sm + L::O_TILE);
     IUnit *units = (IUnit *)(sm + L::O_UNITS);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int sbx = blockIdx.x, sby = blockIdx.y;
+    const int sbx = blockIdx.x, sby = blockIdx.y + f.tile_y0;       /* tile_y0: first superblock row of a banded launch */
     unsigned char *arena = sm + L::O_ARENA + warp * ISB_ARENA;
     UGeom *geom = (UGeom *)(sm + L::O_GEOM) + warp * ISB_MAX_BATCH;
 

@@ -253,7 +253,7 @@ struct Vp9CudaCtx {
     int inter_bands = 6;                   /* set_option "inter_bands" */
     int n_sm = 0;
     size_t ring_rr = 0;
-    bool overlap_inter = false;            /* set_option "overlap_inter": measured +3 % (C3) .. -6 % (C2), off by default */
+    bool overlap_inter = false;            /* set_option "overlap_inter": measured +2 % (C3, 3 bands) .. -30 % (C2), off by default */
     bool fresh_surface = false;            /* surface_get just allocated (its clearing memset is on the compute stream) */
     int follow_mask = 3;                   /* debugging: 1 = wait for intra write-back, 2 = wait for the intra row below */
     bool trace = false;                    /* VP9CUDA_TRACE: one stderr line per submitted / finished frame */
@@ -628,7 +628,21 @@ static int launch_frame(Vp9CudaCtx *c, FrameDesc &f, DevRecords &d)
         }
         kstat_begin(c, si);
         const int gx = (f.cols * 8 + 63) / 64, gy = (f.rows * 8 + 31) / 32;
-        if (overlap && depends) {
+        if (overlap && depends && c->inter_sb) {
+            /* in bands of superblock rows, each behind a one-warp gate on the previous frame's loop-filter rows */
+            const int dep_rows = c->prev_sb_rows, dep_whole = c->prev_w != f.w || c->prev_h != f.h;
+            const int *dep_done = (const int *)c->prev_dev->progress.p + 3 * dep_rows;
+            const int band = dep_whole ? f.sb_rows : std::max(2, (f.sb_rows + c->inter_bands - 1) / c->inter_bands);
+            for (int y0 = 0; y0 < f.sb_rows; y0 += band) {
+                const int n = std::min(band, f.sb_rows - y0);
+                k_inter_gate<<<1, 32, 0, si>>>(dep_done, dep_rows, dep_whole, f.mv_reach, (y0 + n) * 64 - 1, f.err, f.err_host);
+                f.tile_y0 = y0;
+                k_inter_sb<P, HBD><<<dim3(f.sb_cols, n), ISB_THREADS, IsbSmem<P>::BYTES, si>>>(f, 1);
+            }
+            f.tile_y0 = 0;
+            kstat_end(c, KS_INTER, 2 * ((f.sb_rows + band - 1) / band), 2 * P_bytes + d.n_coef * sizeof(typename ItxTypes<HBD>::E), si);
+            residual_done = true;
+        } else if (overlap && depends) {
             /* in bands of tile rows, each behind a one-warp gate on the previous frame's loop-filter rows */
             const int dep_rows = c->prev_sb_rows, dep_whole = c->prev_w != f.w || c->prev_h != f.h;
             const int *dep_done = (const int *)c->prev_dev->progress.p + 3 * dep_rows;
