@@ -279,6 +279,8 @@ struct Vp9CudaCtx {
     std::set<uint64_t> aborted;            /* frames given back before it was their turn */
     int max_w = 0, max_h = 0, max_bpp = 0;
     std::atomic<uint64_t> n_allocs{0}, n_frames{0}, n_aborted{0}, h2d_bytes{0}, early_h2d_bytes{0}, d2h_bytes{0};
+    /* host time spent inside the entry points a decoder calls per frame (ns, all calling threads summed) */
+    std::atomic<uint64_t> ns_begin{0}, ns_submit{0}, ns_finish{0}, ns_wait{0}, n_submit{0}, n_submit_copies{0};
     KStat ks[KS_N];
     bool timing = false;
     /* per-stage timing without host syncs: event pairs from a pool, resolved in kernel_stats() */
@@ -1030,10 +1032,24 @@ extern "C" int vp9cuda_flush(Vp9CudaCtx *c)
     return 0;
 }
 
+namespace {
+struct HostTimer {          /* adds the wall time of the enclosing scope to a counter */
+    std::atomic<uint64_t> &acc;
+    std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
+    explicit HostTimer(std::atomic<uint64_t> &a) : acc(a) {}
+    ~HostTimer() { acc += (uint64_t)std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now() - t0).count(); }
+};
+}
+
 extern "C" void vp9cuda_destroy(Vp9CudaCtx *c)
 {
     if (!c)
         return;
+    if (getenv("VP9CUDA_HOSTPROF"))
+        fprintf(stderr, "vp9cuda host time inside the library: frames %llu, begin_frame %.3f ms, submit_tile %.3f ms (%llu calls, %llu with a copy), "
+                        "finish_frame %.3f ms, wait %.3f ms (all calling threads summed)\n", (unsigned long long)c->n_frames.load(),
+                c->ns_begin.load() * 1e-6, c->ns_submit.load() * 1e-6, (unsigned long long)c->n_submit.load(),
+                (unsigned long long)c->n_submit_copies.load(), c->ns_finish.load() * 1e-6, c->ns_wait.load() * 1e-6);
     cudaSetDevice(c->device);
     if (c->stream)
         sync_all(c);
@@ -1097,6 +1113,7 @@ extern "C" int vp9cuda_begin_frame(Vp9CudaCtx *c, const Vp9CudaFrameHeader *hdr,
     uint32_t n_sb = 0;
     if (!c || !hdr || !ring || check_header(hdr, &n_sb) < 0)
         return -EINVAL;
+    HostTimer ht(c->ns_begin);
     cudaSetDevice(c->device);
     std::unique_lock<std::mutex> lk(c->mu);
     /* round robin, so that consecutive frames land in different device scratch and the next
@@ -1175,6 +1192,8 @@ extern "C" int vp9cuda_submit_tile(Vp9CudaCtx *c, uint32_t frame_id, int lane, c
 {
     if (!c || !counts)
         return -EINVAL;
+    HostTimer ht(c->ns_submit);
+    c->n_submit++;
     RingSet *r;
     {
         std::lock_guard<std::mutex> lk(c->mu);
@@ -1196,6 +1215,7 @@ extern "C" int vp9cuda_submit_tile(Vp9CudaCtx *c, uint32_t frame_id, int lane, c
                            (uint64_t)(counts->coef - r->sent[lane].coef) * coef_entry_bytes(r->hdr.bpp);
     if (fresh < 64 * 1024)
         return 0;
+    c->n_submit_copies++;
     cudaSetDevice(c->device);
     uint64_t bytes = 0;
     int ret = copy_lane_range(c, r->dev, g, lane, r->sent[lane], *counts, coef_entry_bytes(r->hdr.bpp), &bytes);
@@ -1225,6 +1245,7 @@ extern "C" int vp9cuda_finish_frame(Vp9CudaCtx *c, uint32_t frame_id, uint8_t *c
 {
     if (!c)
         return -EINVAL;
+    HostTimer ht(c->ns_finish);
     cudaSetDevice(c->device);
     RingSet *r;
     {
@@ -1271,6 +1292,7 @@ extern "C" int vp9cuda_wait(Vp9CudaCtx *c, uint64_t ticket)
 {
     if (!c || !ticket || ticket >= c->next_ticket)
         return -EINVAL;
+    HostTimer ht(c->ns_wait);
     cudaSetDevice(c->device);
     if (c->next_ticket - ticket > c->ticket_ev.size()) {
         CK(cudaStreamSynchronize(c->stream));     /* event slot already recycled: everything older is done */
@@ -1433,6 +1455,10 @@ extern "C" int vp9cuda_get_stat(Vp9CudaCtx *c, const char *key, uint64_t *value)
     if (!strcmp(key, "allocs")) *value = c->n_allocs;
     else if (!strcmp(key, "frames")) *value = c->n_frames;
     else if (!strcmp(key, "aborted")) *value = c->n_aborted;
+    else if (!strcmp(key, "ns_begin_frame")) *value = c->ns_begin;
+    else if (!strcmp(key, "ns_submit_tile")) *value = c->ns_submit;
+    else if (!strcmp(key, "ns_finish_frame")) *value = c->ns_finish;
+    else if (!strcmp(key, "ns_wait")) *value = c->ns_wait;
     else if (!strcmp(key, "h2d_bytes")) *value = c->h2d_bytes;
     else if (!strcmp(key, "early_h2d_bytes")) *value = c->early_h2d_bytes;
     else if (!strcmp(key, "d2h_bytes")) *value = c->d2h_bytes;

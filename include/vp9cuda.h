@@ -285,7 +285,10 @@ int  vp9cuda_elapsed_ms(Vp9CudaCtx *ctx, int mark_a, int mark_b, double *ms);
 /* counters: "allocs" = device / pinned allocations made so far (constant once the stream is in
  * its steady state), "frames" = frames reconstructed, "aborted" = frames given back unfinished,
  * "h2d_bytes" / "d2h_bytes" = record bytes copied in / picture bytes copied out so far,
- * "early_h2d_bytes" = the part of h2d_bytes that submit_tile sent before finish_frame */
+ * "early_h2d_bytes" = the part of h2d_bytes that submit_tile sent before finish_frame,
+ * "ns_begin_frame" / "ns_submit_tile" / "ns_finish_frame" / "ns_wait" = host time spent inside
+ * those entry points so far, nanoseconds, all calling threads summed ($VP9CUDA_HOSTPROF=1 prints
+ * them when the context is destroyed) */
 int  vp9cuda_get_stat(Vp9CudaCtx *ctx, const char *key, uint64_t *value);
 const char *vp9cuda_version(void);
 

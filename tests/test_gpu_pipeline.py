@@ -100,6 +100,8 @@ def test_no_allocation_on_the_frame_path(workdir):
     assert ctx.stat("allocs") == allocs, "allocation in the steady state"
     assert len(set(sums)) == 1
     assert 0 < ctx.stat("early_h2d_bytes") < ctx.stat("h2d_bytes")
+    # host time spent inside the per-frame entry points is accounted (ns)
+    assert all(ctx.stat(k) > 0 for k in ("ns_begin_frame", "ns_submit_tile", "ns_finish_frame", "ns_wait"))
     ctx.close()
 
 
