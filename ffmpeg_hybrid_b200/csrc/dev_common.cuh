@@ -101,6 +101,9 @@ struct FrameDesc {
     int16_t *ires;                 /* [sb][6144] intra residual tiles (k_intra_res -> k_intra) */
     LfSched *lfsched;              /* [sb][plane] loop-filter edge ops sorted by dependency step */
     int *progress;                 /* [3 planes][sb_rows] loop-filter wavefront counters, then [3][sb_rows] "row done" */
+    unsigned long long *lf_ll;     /* [3 planes][sb_rows][sb_cols][LF_LL_WORDS]: the 8 filtered rows a loop-filter row hands down,
+                                      as (4 bytes of pixels | launch tag << 32) words: data and "ready" arrive in one 8-byte store */
+    unsigned ll_tag;               /* tag of this launch's words (never 0, unique per context and launch) */
     int *mv_reach;                 /* max vertical motion vector component of this frame, 1/8 pel (k_cellmap) */
     int tile_y0;                   /* first row of this launch when the frame is launched in bands: k_inter 32-row tile rows, k_inter_sb superblock rows */
     unsigned long long *phase_clk; /* optional: per-phase clock accumulation (profiling), or NULL */
@@ -168,6 +171,13 @@ __device__ int *g_wd_buf;
             else if (now_ - t0_ > VP9_SPIN_BUDGET) { \
                 atomicExch(f.err, __LINE__); *(volatile int *)f.err_host = __LINE__; __threadfence_system(); break; } } } } while (0)
 #endif
+
+#define LF_LL_WORDS 256                 /* 8 rows x 64 pixels x 2 bytes / 4 */
+__device__ __forceinline__ void ll_store(unsigned long long *p, unsigned data, unsigned tag)
+{
+    *(volatile unsigned long long *)p = (unsigned long long)tag << 32 | data;
+}
+__device__ __forceinline__ unsigned long long ll_load(const unsigned long long *p) { return *(const volatile unsigned long long *)p; }
 
 /* 16-byte asynchronous global -> shared copies (LDGSTS.128) and named barriers, with host stand-ins for
  * the emulation build (oracle/cuda_emu.h) */

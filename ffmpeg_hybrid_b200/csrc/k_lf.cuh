@@ -189,12 +189,10 @@ __device__ void lf_row(const FrameDesc &f, int pl, int row, unsigned char *ring,
     const int stride = f.cur.stride[pl];
     P *plane = (P *)f.cur.pl[pl];
     const int y0 = row * S;
-    int *prog = f.progress + pl * f.sb_rows;
     /* Running beside the intra wavefront (k_wave): superblock (row, j) may be read once the intra
-     * pass has written it back completely, and column block c may be written once the intra row
-     * below has fetched its border row (pre-filter bottom line of this row) for columns c and c+1. */
+     * pass has written it back completely (which also means the intra row has fetched its border
+     * line above columns j and j + 1, so that this row may overwrite it). */
     const volatile int *const intra_full = (f.lf_follow & 1) ? f.iprogress + f.sb_rows + row : nullptr;
-    const volatile int *const intra_below = (f.lf_follow & 2) && row + 1 < f.sb_rows ? f.iprogress + row + 1 : nullptr;
 
     if (warp < LF_CW) {
         /* ------------------------------- compute warps ------------------------------- */
@@ -335,34 +333,44 @@ __device__ void lf_row(const FrameDesc &f, int pl, int row, unsigned char *ring,
     } else if (warp == LF_CW + 1) {
         /* ------------------------------- top loader ------------------------------- */
         if (has_top) {
-            const volatile int *above = prog + row - 1;
+            /* the 8 rows above come as tagged words from the row above's storer (lf_ll): data and "ready" in one load */
+            constexpr int LLW = 8 * S * (int)sizeof(P) / 4, WPR = S * (int)sizeof(P) / 4, NW = LLW / 32;
+            const unsigned long long *in = f.lf_ll + ((size_t)pl * f.sb_rows + row - 1) * ncol * LF_LL_WORDS;
+            const unsigned tag = f.ll_tag;
             for (int c = 0; c < ncol; c++) {
-                if (lane == 0) {
+                if (lane == 0)
                     VP9_SPIN(c >= 4 && sig->stored < c - 3, 20, "lf top loader: ring", row * 3 + pl, c);
-                    VP9_SPIN(*above < c + 1, 20, "lf top loader: row above", row * 3 + pl, c);
-                    __threadfence();
-                }
                 __syncwarp();
-                const unsigned char *src = (const unsigned char *)(plane + (size_t)(y0 - 8) * stride + c * S);
+                const unsigned long long *src = in + (size_t)c * LF_LL_WORDS + lane;
+                unsigned long long w[NW];
+                auto fetch = [&]() {
+                    bool ready = true;
+#pragma unroll
+                    for (int j = 0; j < NW; j++) w[j] = ll_load(src + 32 * j);
+#pragma unroll
+                    for (int j = 0; j < NW; j++) ready &= (unsigned)(w[j] >> 32) == tag;
+                    return ready;
+                };
+                VP9_SPIN(!fetch(), 0, "lf top loader: row above", row * 3 + pl, c);
                 unsigned char *dst = ring + (c & 3) * SLOT;
-                for (int i = lane; i < 8 * CPR; i += 32) {
-                    const int r = i / CPR, k = i % CPR;
-                    lf_cp16(dst + r * RSB + 16 * k, src + (size_t)r * stride * sizeof(P) + 16 * k);
+#pragma unroll
+                for (int j = 0; j < NW; j++) {
+                    const int i = lane + 32 * j;
+                    *(unsigned *)(dst + (i / WPR) * RSB + 4 * (i % WPR)) = (unsigned)w[j];
                 }
-                lf_cp_commit();
-                lf_cp_wait<0>();
                 __syncwarp();
                 if (lane == 0) { __threadfence_block(); sig->top = c + 1; }
             }
         }
     } else {
         /* ------------------------------- storer ------------------------------- */
+        constexpr int LLW = 8 * S * (int)sizeof(P) / 4, WPR = S * (int)sizeof(P) / 4;
+        const bool last_row = row + 1 == f.sb_rows;
+        unsigned long long *out = f.lf_ll + ((size_t)pl * f.sb_rows + row) * ncol * LF_LL_WORDS;
         for (int c = 0; c < ncol; c++) {
             if (lane == 0) {
                 VP9_SPIN(sig->done < c + 1, 20, "lf storer: done", row * 3 + pl, c);
-                if (intra_below)
-                    VP9_SPIN(*intra_below < min(c + 2, ncol), 40, "lf storer: intra row below", row * 3 + pl, c);
-                __threadfence();
+                __threadfence_block();
             }
             __syncwarp();
             unsigned char *dst = (unsigned char *)(plane + (size_t)(y0 - 8) * stride + c * S);
@@ -374,11 +382,16 @@ __device__ void lf_row(const FrameDesc &f, int pl, int row, unsigned char *ring,
                     *(uint4 *)(dst + (ptrdiff_t)r * stride * (int)sizeof(P) + 16 * k) = *(const uint4 *)(src + r * RSB + 16 * k);
                 }
             };
-            store_rows(S, S + 8);           /* the rows handed down to the next superblock row */
-            __syncwarp();
-            if (lane == 0) {
-                __threadfence();
-                *(volatile int *)(prog + row) = c + 1;
+            /* The last 8 rows go to the row below as tagged words: it filters across them and writes them to the
+             * picture with its own column block c, after the intra row below has long fetched their pre-filter
+             * bottom line -- so this row never overwrites what the intra wavefront still reads (the job
+             * intra_pred_data does in the reference, vp9.c:1404-1416).  The last row writes them itself. */
+            if (!last_row) {
+#pragma unroll
+                for (int i = lane; i < LLW; i += 32)
+                    ll_store(out + (size_t)c * LF_LL_WORDS + i, *(const unsigned *)(src + (S + i / WPR) * RSB + 4 * (i % WPR)), f.ll_tag);
+            } else {
+                store_rows(S, S + 8);
             }
             store_rows(has_top ? 0 : 8, S);
             __syncwarp();

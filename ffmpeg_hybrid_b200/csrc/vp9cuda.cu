@@ -148,7 +148,7 @@ struct HBuf {
  * staged path: lanes packed back to back). */
 struct DevRecords {
     DBuf blk, tx, itx, coef, sb_index, lf;
-    DBuf cellmap, isb, irec, iblk, ires, itab, iprogress, lfops, progress, misc;
+    DBuf cellmap, isb, irec, iblk, ires, itab, iprogress, lfops, progress, misc, ll;
     uint32_t lane_blk_base[VP9CUDA_MAX_LANES] = { 0 }, lane_tx_base[VP9CUDA_MAX_LANES] = { 0 },
              lane_itx_base[VP9CUDA_MAX_LANES] = { 0 };
     uint32_t lane_blk_cnt[VP9CUDA_MAX_LANES] = { 0 }, lane_tx_cnt[VP9CUDA_MAX_LANES] = { 0 };
@@ -194,6 +194,12 @@ struct DevRecords {
         r |= iprogress.reserve((size_t)2 * sb_rows * 4, allocs);
         r |= lfops.reserve((size_t)n_sb * 3 * sizeof(LfSched), allocs);
         r |= progress.reserve((size_t)6 * sb_rows * 4, allocs);
+        {   /* hand-down words of the loop-filter rows: must not hold a tag of this context when they are new */
+            const void *was = ll.p;
+            r |= ll.reserve((size_t)3 * n_sb * LF_LL_WORDS * 8, allocs);
+            if (!r && ll.p != was && cudaMemset(ll.p, 0, ll.cap) != cudaSuccess)
+                r = -1;
+        }
         r |= misc.reserve(64, allocs);
         return r ? -ENOMEM : make_events();
     }
@@ -207,7 +213,7 @@ struct DevRecords {
         uploaded = dev_free = prepped = cellmapped = inter_done = nullptr;
         blk.release(); tx.release(); itx.release(); coef.release(); sb_index.release(); lf.release();
         misc.release(); cellmap.release(); isb.release(); irec.release(); iblk.release(); ires.release(); itab.release(); iprogress.release(); lfops.release();
-        progress.release();
+        progress.release(); ll.release();
     }
 };
 
@@ -255,6 +261,7 @@ struct Vp9CudaCtx {
     size_t ring_rr = 0;
     bool overlap_inter = false;            /* set_option "overlap_inter": measured +2 % (C3, 3 bands) .. -30 % (C2), off by default */
     bool fresh_surface = false;            /* surface_get just allocated (its clearing memset is on the compute stream) */
+    unsigned ll_tag = 0;                   /* last tag given to a launch's loop-filter hand-down words */
     int follow_mask = 3;                   /* debugging: 1 = wait for intra write-back, 2 = wait for the intra row below */
     bool trace = false;                    /* VP9CUDA_TRACE: one stderr line per submitted / finished frame */
     bool fuse_wave = true;                 /* set_option "fuse_wave": loop filter beside the intra wavefront */
@@ -563,6 +570,9 @@ static int launch_frame(Vp9CudaCtx *c, FrameDesc &f, DevRecords &d)
     const uint64_t P_bytes = (uint64_t)f.w * f.h * (f.mono >= 0 ? 2 : 3) / 2 * sizeof(P);
     const bool fused = c->fuse_wave && f.n_itx && f.lf_level;
     f.lf_follow = fused ? c->follow_mask : 0;
+    if (++c->ll_tag == 0)               /* the hand-down words of this launch carry a tag no earlier launch of the context used */
+        c->ll_tag = 1;
+    f.ll_tag = c->ll_tag;
     if (fused && c->inject_stall) {
         f.lf_follow |= 4;
         c->inject_stall = false;
@@ -805,6 +815,7 @@ static int reconstruct(Vp9CudaCtx *c, DevRecords &d, uint8_t *const out_planes[3
     memcpy(f.lane_itx_base, d.lane_itx_base, sizeof(f.lane_itx_base));
     f.lfsched = (LfSched *)d.lfops.p;
     f.progress = (int *)d.progress.p;
+    f.lf_ll = (unsigned long long *)d.ll.p;
     f.mv_reach = (int *)d.misc.p;
     f.phase_clk = c->phase_on ? (unsigned long long *)c->phase_clk.p : nullptr;
     f.err = (int *)c->err_dev.p;

@@ -49,6 +49,9 @@ static long run_wave(FrameDesc &f, const Vp9CudaFrameHeader &h, const std::vecto
     std::vector<LfSched> lfs((size_t)n_sb * 3);
     f.isb = isb.data(); f.irec = irec.data(); f.iblk = iblk.data(); f.iprogress = iprogress.data();
     f.itab = itab.data(); f.ires = ires.data(); f.lfsched = lfs.data(); f.progress = progress.data();
+    std::vector<unsigned long long> ll((size_t)3 * n_sb * LF_LL_WORDS, 0);
+    static unsigned ll_tag = 0;
+    f.lf_ll = ll.data(); f.ll_tag = ++ll_tag;
     const bool fused = f.n_itx && f.lf_level && !getenv("EMU_NOFUSE");
     f.lf_follow = fused ? 3 : 0;
     if (f.n_itx) {
