@@ -103,6 +103,8 @@ struct FrameDesc {
     int *progress;                 /* [3 planes][sb_rows] loop-filter wavefront counters, then [3][sb_rows] "row done" */
     unsigned long long *lf_ll;     /* [3 planes][sb_rows][sb_cols][LF_LL_WORDS]: the 8 filtered rows a loop-filter row hands down,
                                       as (4 bytes of pixels | launch tag << 32) words: data and "ready" arrive in one 8-byte store */
+    unsigned long long *intra_ll;  /* [sb_rows][sb_cols][INTRA_LL_WORDS]: the bottom pixel line of every superblock the intra wavefront
+                                      reconstructed (luma at 0, U at 32, V at 48), as tagged words for the intra row below */
     unsigned ll_tag;               /* tag of this launch's words (never 0, unique per context and launch) */
     int *mv_reach;                 /* max vertical motion vector component of this frame, 1/8 pel (k_cellmap) */
     int tile_y0;                   /* first row of this launch when the frame is launched in bands: k_inter 32-row tile rows, k_inter_sb superblock rows */
@@ -173,6 +175,7 @@ __device__ int *g_wd_buf;
 #endif
 
 #define LF_LL_WORDS 256                 /* 8 rows x 64 pixels x 2 bytes / 4 */
+#define INTRA_LL_WORDS 64               /* one line: 64 luma + 2 x 32 chroma pixels x 2 bytes / 4 */
 __device__ __forceinline__ void ll_store(unsigned long long *p, unsigned data, unsigned tag)
 {
     *(volatile unsigned long long *)p = (unsigned long long)tag << 32 | data;

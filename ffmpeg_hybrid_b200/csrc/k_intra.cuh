@@ -574,8 +574,53 @@ __device__ __forceinline__ void intra_row(const FrameDesc &f, const int row, uns
                     if (lane == 0) sig.top = c + 1;
                     continue;
                 }
+                /* Fast path: the superblock above (and the one above-left, for the top-left sample) went through the intra
+                 * wavefront itself, so its bottom line arrives as tagged words (intra_ll) -- pixels and "ready" in one load. */
+                int fast = 0;
                 if (lane == 0) {
                     VP9_SPIN(sig.done < c - 2 || sig.stored < c - 3, 20, "intra top loader: ring", row, c);
+                    const IntraSb *up = f.isb + (size_t)(row - 1) * ncol + c;
+                    fast = info[c].needs_top && up[0].count > 0 && (c == 0 || up[-1].count > 0);
+                }
+                fast = __shfl_sync(0xffffffffu, fast, 0);
+                if (fast) {
+                    constexpr int WY = 64 * (int)sizeof(P) / 4, WC = 32 * (int)sizeof(P) / 4;     /* words per line */
+                    const int k0 = c > 0 ? -4 : 0;                                             /* 16 bytes to the left: the top-left sample */
+                    const int ny = WY - k0, nc = f.mono >= 0 ? 0 : WC - k0, total = ny + 2 * nc;
+                    const unsigned long long *in = f.intra_ll + ((size_t)(row - 1) * ncol + c) * INTRA_LL_WORDS;
+                    const unsigned tag = f.ll_tag;
+                    const unsigned long long *src[3];
+                    unsigned char *dst[3];
+#pragma unroll
+                    for (int j = 0; j < 3; j++) {
+                        const int t = lane + 32 * j;
+                        src[j] = nullptr; dst[j] = nullptr;
+                        if (t < total) {
+                            const int pl = t < ny ? 0 : t < ny + nc ? 1 : 2;
+                            const int k = (pl == 0 ? t : pl == 1 ? t - ny : t - ny - nc) + k0;
+                            const int W = pl ? WC : WY, S = pl ? 32 : 64, base = pl == 0 ? 0 : pl == 1 ? 32 : 48;
+                            src[j] = k >= 0 ? in + base + k : in - INTRA_LL_WORDS + base + W + k;
+                            dst[j] = tile(pl) + (((c & 3) * S * (int)sizeof(P) + 4 * k) & (4 * S * (int)sizeof(P) - 1));
+                        }
+                    }
+                    unsigned long long w[3];
+                    auto fetch = [&]() {
+                        bool ready = true;
+#pragma unroll
+                        for (int j = 0; j < 3; j++) w[j] = src[j] ? ll_load(src[j]) : (unsigned long long)tag << 32;
+#pragma unroll
+                        for (int j = 0; j < 3; j++) ready &= (unsigned)(w[j] >> 32) == tag;
+                        return ready;
+                    };
+                    VP9_SPIN(!fetch(), 0, "intra top loader: row above (words)", row, c);
+#pragma unroll
+                    for (int j = 0; j < 3; j++)
+                        if (dst[j]) *(unsigned *)dst[j] = (unsigned)w[j];
+                    __syncwarp();
+                    if (lane == 0) { __threadfence_block(); sig.top = c + 1; }
+                    continue;
+                }
+                if (lane == 0) {
                     if (info[c].needs_top)
                         VP9_SPIN(*above < c + 1, 20, "intra top loader: row above", row, c);
                     __threadfence();
@@ -625,6 +670,16 @@ __device__ __forceinline__ void intra_row(const FrameDesc &f, const int row, uns
                         *(uint4 *)(dst + (ptrdiff_t)r * stride * (int)sizeof(P) + 16 * k) = *(const uint4 *)(src + r * rsb + 16 * k);
                     }
                 };
+                if (row + 1 < f.sb_rows) {      /* the bottom line as tagged words for the intra row below (its fast path) */
+                    constexpr int WY = 64 * (int)sizeof(P) / 4, WC = 32 * (int)sizeof(P) / 4;
+                    unsigned long long *out = f.intra_ll + ((size_t)row * ncol + c) * INTRA_LL_WORDS;
+                    if (lane < WY)
+                        ll_store(out + lane, *(const unsigned *)(tile(0) + 64 * L::RSBY + (c & 3) * 64 * (int)sizeof(P) + 4 * lane), f.ll_tag);
+                    if (f.mono < 0 && lane < WC) {
+                        ll_store(out + 32 + lane, *(const unsigned *)(tile(1) + 32 * L::RSBC + (c & 3) * 32 * (int)sizeof(P) + 4 * lane), f.ll_tag);
+                        ll_store(out + 48 + lane, *(const unsigned *)(tile(2) + 32 * L::RSBC + (c & 3) * 32 * (int)sizeof(P) + 4 * lane), f.ll_tag);
+                    }
+                }
                 store_rows(0, 64, 65); store_rows(1, 32, 33); store_rows(2, 32, 33);
                 __syncwarp();
                 if (lane == 0) {

@@ -148,7 +148,7 @@ struct HBuf {
  * staged path: lanes packed back to back). */
 struct DevRecords {
     DBuf blk, tx, itx, coef, sb_index, lf;
-    DBuf cellmap, isb, irec, iblk, ires, itab, iprogress, lfops, progress, misc, ll;
+    DBuf cellmap, isb, irec, iblk, ires, itab, iprogress, lfops, progress, misc, ll, ill;
     uint32_t lane_blk_base[VP9CUDA_MAX_LANES] = { 0 }, lane_tx_base[VP9CUDA_MAX_LANES] = { 0 },
              lane_itx_base[VP9CUDA_MAX_LANES] = { 0 };
     uint32_t lane_blk_cnt[VP9CUDA_MAX_LANES] = { 0 }, lane_tx_cnt[VP9CUDA_MAX_LANES] = { 0 };
@@ -199,6 +199,10 @@ struct DevRecords {
             r |= ll.reserve((size_t)3 * n_sb * LF_LL_WORDS * 8, allocs);
             if (!r && ll.p != was && cudaMemset(ll.p, 0, ll.cap) != cudaSuccess)
                 r = -1;
+            const void *iwas = ill.p;
+            r |= ill.reserve((size_t)n_sb * INTRA_LL_WORDS * 8, allocs);
+            if (!r && ill.p != iwas && cudaMemset(ill.p, 0, ill.cap) != cudaSuccess)
+                r = -1;
         }
         r |= misc.reserve(64, allocs);
         return r ? -ENOMEM : make_events();
@@ -213,7 +217,7 @@ struct DevRecords {
         uploaded = dev_free = prepped = cellmapped = inter_done = nullptr;
         blk.release(); tx.release(); itx.release(); coef.release(); sb_index.release(); lf.release();
         misc.release(); cellmap.release(); isb.release(); irec.release(); iblk.release(); ires.release(); itab.release(); iprogress.release(); lfops.release();
-        progress.release(); ll.release();
+        progress.release(); ll.release(); ill.release();
     }
 };
 
@@ -816,6 +820,7 @@ static int reconstruct(Vp9CudaCtx *c, DevRecords &d, uint8_t *const out_planes[3
     f.lfsched = (LfSched *)d.lfops.p;
     f.progress = (int *)d.progress.p;
     f.lf_ll = (unsigned long long *)d.ll.p;
+    f.intra_ll = (unsigned long long *)d.ill.p;
     f.mv_reach = (int *)d.misc.p;
     f.phase_clk = c->phase_on ? (unsigned long long *)c->phase_clk.p : nullptr;
     f.err = (int *)c->err_dev.p;

@@ -51,7 +51,8 @@ static long run_wave(FrameDesc &f, const Vp9CudaFrameHeader &h, const std::vecto
     f.itab = itab.data(); f.ires = ires.data(); f.lfsched = lfs.data(); f.progress = progress.data();
     std::vector<unsigned long long> ll((size_t)3 * n_sb * LF_LL_WORDS, 0);
     static unsigned ll_tag = 0;
-    f.lf_ll = ll.data(); f.ll_tag = ++ll_tag;
+    std::vector<unsigned long long> ill((size_t)n_sb * INTRA_LL_WORDS, 0);
+    f.lf_ll = ll.data(); f.intra_ll = ill.data(); f.ll_tag = ++ll_tag;
     const bool fused = f.n_itx && f.lf_level && !getenv("EMU_NOFUSE");
     f.lf_follow = fused ? 3 : 0;
     if (f.n_itx) {
