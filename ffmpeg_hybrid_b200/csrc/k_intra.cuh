@@ -568,10 +568,12 @@ __device__ __forceinline__ void intra_row(const FrameDesc &f, const int row, uns
         /* ------------------------------- top loader ------------------------------- */
         if (has_top) {
             const volatile int *above = f.iprogress + row - 1;
+            int prev_fast = 0;                      /* the previous turn took its border from the tagged words */
             for (int c = 0; c < ncol; c++) {
                 if (info[c].count == 0) {
                     __syncwarp();
                     if (lane == 0) sig.top = c + 1;
+                    prev_fast = 0;
                     continue;
                 }
                 /* Fast path: the superblock above (and the one above-left, for the top-left sample) went through the intra
@@ -618,6 +620,7 @@ __device__ __forceinline__ void intra_row(const FrameDesc &f, const int row, uns
                         if (dst[j]) *(unsigned *)dst[j] = (unsigned)w[j];
                     __syncwarp();
                     if (lane == 0) { __threadfence_block(); sig.top = c + 1; }
+                    prev_fast = 1;
                     continue;
                 }
                 if (lane == 0) {
@@ -634,8 +637,11 @@ __device__ __forceinline__ void intra_row(const FrameDesc &f, const int row, uns
                     const int cpr = S * (int)sizeof(P) / 16;
                     const int stride = f.cur.stride[pl];
                     const unsigned char *src = (const unsigned char *)((const P *)f.cur.pl[pl] + ((size_t)row * S - 1) * stride + c * S);
-                    /* one extra chunk to the left: the top-left pixel lives in the previous ring slot */
-                    const int k0 = c > 0 ? -1 : 0;
+                    /* One extra chunk to the left: the top-left pixel lives in the previous ring slot.  Not after a turn
+                     * that took its border from the tagged words: that slot then holds the final line already, while the
+                     * picture may not show it yet (the words leave before the picture store), and a turn that does not
+                     * wait for the row above would put stale pixels under the previous turn's blocks. */
+                    const int k0 = (c > 0 && !prev_fast) ? -1 : 0;
                     if (lane - 1 >= k0 && lane - 1 < cpr) {
                         const int k = lane - 1;
                         const int col = ((c & 3) * S * (int)sizeof(P) + 16 * k) & (4 * S * (int)sizeof(P) - 1);
@@ -646,6 +652,7 @@ __device__ __forceinline__ void intra_row(const FrameDesc &f, const int row, uns
                 cp_wait<0>();
                 __syncwarp();
                 if (lane == 0) { __threadfence_block(); sig.top = c + 1; }
+                prev_fast = 0;
             }
         }
     } else {

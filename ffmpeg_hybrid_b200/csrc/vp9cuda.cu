@@ -197,11 +197,11 @@ struct DevRecords {
         {   /* hand-down words of the loop-filter rows: must not hold a tag of this context when they are new */
             const void *was = ll.p;
             r |= ll.reserve((size_t)3 * n_sb * LF_LL_WORDS * 8, allocs);
-            if (!r && ll.p != was && cudaMemset(ll.p, 0, ll.cap) != cudaSuccess)
-                r = -1;
+            if (!r && ll.p != was && (cudaMemset(ll.p, 0, ll.cap) != cudaSuccess || cudaDeviceSynchronize() != cudaSuccess))
+                r = -1;                     /* (the context's streams do not wait for the default stream by themselves) */
             const void *iwas = ill.p;
             r |= ill.reserve((size_t)n_sb * INTRA_LL_WORDS * 8, allocs);
-            if (!r && ill.p != iwas && cudaMemset(ill.p, 0, ill.cap) != cudaSuccess)
+            if (!r && ill.p != iwas && (cudaMemset(ill.p, 0, ill.cap) != cudaSuccess || cudaDeviceSynchronize() != cudaSuccess))
                 r = -1;
         }
         r |= misc.reserve(64, allocs);

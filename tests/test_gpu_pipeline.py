@@ -337,3 +337,18 @@ def test_oversubscribed_wavefronts_many_contexts(workdir):
     for fl in frames.values():
         for f in fl:
             f.free()
+
+
+def test_soak_repeated_decode_is_deterministic():
+    """tools/soak.py for half a minute: six contexts side by side decode C2 and C5 at full size over and over from
+    resident records; the checksum of every frame of every pass must equal the first pass.  A hand-over race between
+    concurrently running wavefront CTAs shows as a checksum that changes from pass to pass (the first version of the
+    tagged-word intra hand-over failed this within seconds while every single-pass parity test passed)."""
+    import json
+    import subprocess
+    import sys
+    p = subprocess.run([sys.executable, str(ROOT / "tools" / "soak.py"), "--seconds", "30", "--workloads", "c2,c5", "--contexts", "3"],
+                       capture_output=True, text=True, timeout=600)
+    out = json.loads(p.stdout.strip().splitlines()[-1])
+    assert out["errors"] == [] and out["mismatches"] == 0, out
+    assert out["frames_checked"] > 5000

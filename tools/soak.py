@@ -52,7 +52,10 @@ def main():
                 if first is None:
                     first = sums
                 else:
-                    stats[name]["mismatches"] += sum(a != b for a, b in zip(first, sums))
+                    bad = [i for i, (a, b) in enumerate(zip(first, sums)) if a != b]
+                    stats[name]["mismatches"] += len(bad)
+                    if bad and len(stats[name].setdefault("first_bad", [])) < 8:
+                        stats[name]["first_bad"].append({"pass": stats[name]["passes"], "frame": bad[0], "n": len(bad)})
                 stats[name]["passes"] += 1
                 stats[name]["frames"] += len(sums)
             ctx.close()
