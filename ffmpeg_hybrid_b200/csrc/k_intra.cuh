@@ -18,12 +18,14 @@
  *   k_intra : one CTA per superblock ROW.  The row's pixels slide through a shared-memory ring
  *       of four superblock columns per plane (row 0 of each ring = the pixel row above).  A
  *       body-loader warp streams tiles, records and residual tiles in with cp.async up to two
- *       turns ahead; a top-loader warp polls the row above's progress counter and fetches the
- *       border row; eight compute warps run the turn's dependency steps (edges -> prediction +
- *       residual, all in shared memory, one barrier per step; 32x32 blocks are split four ways);
- *       a storer warp writes the finished tile back, bottom pixel row first, then fence +
- *       progress counter for the row below.  Superblocks without intra blocks cost one flag
- *       update.
+ *       turns ahead; a top-loader warp brings in the border line above -- as tagged words
+ *       (pixels | launch tag, FrameDesc.intra_ll: data and "ready" in one 8-byte load) when the
+ *       superblocks above went through the wavefront, else from the picture behind the row
+ *       above's progress counter; twenty compute warps run the turn's dependency steps (edges ->
+ *       prediction + residual, all in shared memory, one barrier per step); a storer warp sends
+ *       the bottom line out as tagged words, then writes the finished tile back, bottom pixel
+ *       row first, then fence + progress counter.  Superblocks without intra blocks cost one
+ *       flag update.
  *
  * Replaces intra_recon + check_intra_mode (vp9recon.c:37-364) and the intra_pred slots
  * (vp9dsp_template.c:33-1153).  Reads the pre-loop-filter picture everywhere, which is what

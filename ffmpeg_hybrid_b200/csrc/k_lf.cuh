@@ -23,9 +23,11 @@
  *
  * Pixels live in a shared-memory ring of 4 superblock columns x (S+8) rows.  Three helper warps
  * keep the turn free of global-memory latency: a body loader (cp.async of pre-filter pixels and
- * the schedule, up to 3 superblocks ahead), a top loader (polls the row above's progress
- * counter, fetches the 8 handed-down rows), and a storer (writes a finished column block back,
- * hand-down rows first, then fence + progress counter for the row below).
+ * the schedule, up to 3 superblocks ahead), a top loader (polls the 8 handed-down rows, which
+ * travel as tagged 8-byte words -- 4 bytes of pixels | launch tag, FrameDesc.lf_ll -- so that
+ * pixels and "ready" arrive in one load), and a storer (sends the last 8 rows down as tagged
+ * words, then writes rows [y0-8, y0+S-8) of the column block back: the 8 rows above included,
+ * its own last 8 rows left to the row below, the last row writes its own).
  *
  * Replaces ff_vp9_loopfilter_sb (vp9lpf.c:183-230) + loop_filter_8/16/mix2 slots
  * (vp9dsp_template.c:1780-1967).  Algorithmic bytes: 2*P (read + write of the picture).
