@@ -266,7 +266,7 @@ struct Vp9CudaCtx {
     bool overlap_inter = false;            /* set_option "overlap_inter": measured +2 % (C3, 3 bands) .. -30 % (C2), off by default */
     bool fresh_surface = false;            /* surface_get just allocated (its clearing memset is on the compute stream) */
     unsigned ll_tag = 0;                   /* last tag given to a launch's loop-filter hand-down words */
-    int follow_mask = 3;                   /* debugging: 1 = wait for intra write-back, 2 = wait for the intra row below */
+    int follow_mask = 3;                   /* debugging: bit 0 = the loop filter waits for the intra write-back (bit 1 is unused since the tagged-word hand-over) */
     bool trace = false;                    /* VP9CUDA_TRACE: one stderr line per submitted / finished frame */
     bool fuse_wave = true;                 /* set_option "fuse_wave": loop filter beside the intra wavefront */
     bool inject_stall = false;             /* set_option "inject_stall": the next wavefront launch never satisfies one wait (test) */
