@@ -100,7 +100,7 @@ struct FrameDesc {
     uint16_t *itab;                /* [sb][768] per-step chunk tables (k_intra_prep) */
     int16_t *ires;                 /* [sb][6144] intra residual tiles (k_intra_res -> k_intra) */
     LfSched *lfsched;              /* [sb][plane] loop-filter edge ops sorted by dependency step */
-    int *progress;                 /* [3 planes][sb_rows] loop-filter wavefront counters, then [3][sb_rows] "row done" */
+    int *progress;                 /* [3 planes][sb_rows] unused since the tagged-word hand-over, then [3][sb_rows] loop-filter "row done" */
     unsigned long long *lf_ll;     /* [3 planes][sb_rows][sb_cols][LF_LL_WORDS]: the 8 filtered rows a loop-filter row hands down,
                                       as (4 bytes of pixels | launch tag << 32) words: data and "ready" arrive in one 8-byte store */
     unsigned long long *intra_ll;  /* [sb_rows][sb_cols][INTRA_LL_WORDS]: the bottom pixel line of every superblock the intra wavefront

@@ -456,9 +456,10 @@ __global__ void __launch_bounds__(LF_THREADS) k_lf(const __grid_constant__ Frame
  *
  * CTAs [0, sb_rows) run intra_row, CTAs [sb_rows, 4*sb_rows) run lf_cta.  The loop filter of
  * superblock row r follows the intra pass at a distance of about three superblocks: it reads
- * block (r, j) once the intra pass has written it back (ifull[r] > j) and writes column block c
- * once the intra row below has taken its pre-filter border row for columns c and c+1
- * (iprogress[r+1] >= c+2) -- the role intra_pred_data plays in the reference (vp9.c:1404-1416).
+ * block (r, j) once the intra pass has written it back (ifull[r] > j) and writes rows
+ * [y0 - 8, y0 + 56) of column block c: never its own last 8 rows, whose pre-filter bottom line the
+ * intra row below still reads -- they go down as tagged words and the row below writes them, which
+ * is the role intra_pred_data plays in the reference (vp9.c:1404-1416).
  * Every wait points at a CTA with a lower block index, so in-order CTA dispatch rules out
  * deadlock even when the grid is larger than the machine (8K frames). */
 template <class P> struct WaveSmem {
